@@ -1,0 +1,394 @@
+// N7: bf16 "TN" GEMM on the 5th-generation tensor cores.
+//
+//   out[M, N] = epilogue( A[M, K] · W[N, K]^T + bias[N] )        A, W bf16 row-major (K-major)
+//
+// This is every Linear of the model (reference: HF DistilBERT q/k/v/out/ffn Linears reached from
+// encoder.py:27; text head encoder.py:20-22; user-encoder projections attention.py:72-74, :16).
+// nn.Linear stores W as [N, K], i.e. already K-major, so both operands are loaded by TMA with the
+// 128-byte swizzle straight into the layout tcgen05.mma wants; no transposes anywhere.
+//
+// Structure: persistent, warp-specialised, one CTA per SM.
+//   warp 0      TMA producer   (one elected lane)  global → smem ring, kStages deep
+//   warp 1      MMA issuer     (one elected lane)  tcgen05.mma 128 x BN x 16, fp32 accumulators in TMEM
+//   warps 2..9  epilogue       tcgen05.ld → bias / GELU / tanh / residual → bf16|fp32 → global
+// TMEM holds two accumulator stages (2 x BN columns) so the epilogue of tile i overlaps the MMAs of
+// tile i+1. M may be supplied from device memory (m_dev) so a CUDA-graph-captured step can run on the
+// de-duplicated row count of the current batch without a host round trip.
+#include "sm100.cuh"
+#include <cuda.h>
+#include <mutex>
+#include <unordered_map>
+
+namespace fr {
+using namespace sm100;
+
+constexpr int BM = 128;
+constexpr int BK = 64;        // 64 bf16 = 128 bytes = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = 32 * (2 + kEpiWarps);
+
+enum Epilogue { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESID = 2, EPI_BIAS_TANH = 3 };
+
+struct GemmParams {
+  const float* bias;          // [N] or null
+  const __nv_bfloat16* resid; // [M, ldr] or null
+  void* out;                  // bf16 or fp32 [M, ldo]
+  const int* m_dev;           // optional: effective M = min(M, *m_dev * m_scale)
+  int m_scale;
+  int M, N, K;
+  int ldo, ldr;
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int kStages = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kABytes = BM * BK * 2;
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;   // BN in {64,128,256} → 128/256/512
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+// erf via Abramowitz–Stegun 7.1.26 (|err| < 1.5e-7): two MUFU ops + a short polynomial, so the GELU
+// epilogue keeps up with the tensor pipe (libdevice erff is ~3x the instructions).
+__device__ __forceinline__ float fast_erf(float x) {
+  const float ax = fabsf(x);
+  const float t = __frcp_rn(fmaf(0.3275911f, ax, 1.0f));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  poly *= t;
+  const float r = 1.0f - poly * __expf(-ax * ax);
+  return copysignf(r, x);
+}
+__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + fast_erf(x * 0.70710678118654752f)); }
+__device__ __forceinline__ float tanh_fast(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <int BN, int EPI, bool OUT_F32>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const GemmParams p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint64_t* empty_bar = full_bar + C::kStages;
+  uint64_t* tmem_full = empty_bar + C::kStages;   // [2]
+  uint64_t* tmem_empty = tmem_full + 2;           // [2]
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  int M = p.M;
+  if (p.m_dev) {
+    const long long md = (long long)(*p.m_dev) * p.m_scale;
+    if (md < M) M = (int)md;
+  }
+  const int m_blocks = (M + BM - 1) / BM;
+  const int n_blocks = (p.N + BN - 1) / BN;
+  const int k_blocks = (p.K + BK - 1) / BK;
+  const int num_tiles = m_blocks * n_blocks;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_b);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < C::kStages; ++i) {
+        mbar_init(&full_bar[i], 1);
+        mbar_init(&empty_bar[i], 1);
+      }
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&tmem_full[i], 1);
+        mbar_init(&tmem_empty[i], kEpiWarps);
+      }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_base_slot, C::kTmemCols);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_base_slot;
+
+  if (warp == 0) {
+    // ------------------------------- TMA producer -------------------------------
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile / n_blocks) * BM;
+        const int n0 = (tile % n_blocks) * BN;
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          uint8_t* sb = sa + C::kABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BK, m0);
+          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BK, n0);
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ------------------------------- MMA issuer ---------------------------------
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < k_blocks; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
+          const uint64_t da = make_smem_desc_sw128(sa);
+          const uint64_t db = make_smem_desc_sw128(sa + C::kABytes);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // advance 32 bytes (16 bf16) along K inside the swizzle row: +2 in 16-byte units
+            umma_bf16_ss(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+          }
+          umma_commit(&empty_bar[stage]);          // smem slot free once these MMAs retire
+          if (++stage == C::kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tmem_full[acc]);              // accumulator complete → epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ------------------------------- epilogue -----------------------------------
+    const int ew = warp - 2;                 // 0..7
+    const int quarter = warp & 3;            // TMEM lane quarter this warp may touch
+    const int half = ew >> 2;                // which half of the BN columns
+    constexpr int kColsPerWarp = BN / 2;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile / n_blocks) * BM;
+      const int n0 = (tile % n_blocks) * BN;
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = m0 + quarter * 32 + lane;
+      const bool row_ok = row < M;
+#pragma unroll 1
+      for (int cc = 0; cc < kColsPerWarp; cc += 32) {
+        const int col0 = n0 + half * kColsPerWarp + cc;
+        if (col0 >= p.N) break;              // warp-uniform
+        uint32_t r[32];
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + half * kColsPerWarp + cc);
+        tmem_ld_32x32(taddr, r);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+        const int ncols = min(32, p.N - col0);       // multiple of 8 (N % 8 == 0)
+        if (p.bias) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            if (j < ncols) {
+              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
+              v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+            }
+          }
+        }
+        if (EPI == EPI_BIAS_RESID) {
+          if (row_ok) {
+            const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)row * p.ldr + col0);
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              if (j < ncols) {
+                const uint4 q = __ldg(rp + j / 8);
+                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) {
+                  const float2 f = __bfloat1622float2(h[t]);
+                  v[j + 2 * t] += f.x;
+                  v[j + 2 * t + 1] += f.y;
+                }
+              }
+            }
+          }
+        }
+        if (EPI == EPI_BIAS_GELU) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+        }
+        if (EPI == EPI_BIAS_TANH) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = tanh_fast(v[j]);
+        }
+        if (row_ok) {
+          if (OUT_F32) {
+            float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0);
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              if (j < ncols) op[j / 4] = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + col0);
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              if (j < ncols) {
+                uint4 q;
+                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+                for (int t = 0; t < 4; ++t) h[t] = __floats2bfloat162_rn(v[j + 2 * t], v[j + 2 * t + 1]);
+                op[j / 8] = q;
+              }
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host side: tensor-map construction (driver entry point fetched through the runtime, so the
+// library does not link libcuda) and launch.
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                    const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* f = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)f;
+  });
+  return fn;
+}
+
+// [rows, cols] bf16 row-major with leading dimension ld (elements); box = box_rows x 64 cols, 128B swizzle.
+int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+  PFN_encodeTiled enc = get_encode();
+  FR_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  FR_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0, "TMA operand must be 16-byte aligned with ld %% 8 == 0 (ld=%lld)", ld);
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  FR_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld ld=%lld box_rows=%d)",
+             (int)r, rows, cols, ld, box_rows);
+  return 0;
+}
+
+template <int BN, int EPI, bool OUT_F32>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int max_ctas, cudaStream_t s) {
+  auto kern = gemm_bf16_tn_kernel<BN, EPI, OUT_F32>;
+  static bool attr_set = false;   // per instantiation
+  if (!attr_set) {
+    FR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
+    attr_set = true;
+  }
+  const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
+  int grid = tiles < max_ctas ? tiles : max_ctas;
+  if (grid < 1) grid = 1;
+  kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, p);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int BN, bool OUT_F32>
+static int dispatch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int max_ctas,
+                        cudaStream_t s) {
+  switch (epi) {
+    case EPI_BIAS: return launch<BN, EPI_BIAS, OUT_F32>(ta, tb, p, max_ctas, s);
+    case EPI_BIAS_GELU: return launch<BN, EPI_BIAS_GELU, OUT_F32>(ta, tb, p, max_ctas, s);
+    case EPI_BIAS_RESID: return launch<BN, EPI_BIAS_RESID, OUT_F32>(ta, tb, p, max_ctas, s);
+    case EPI_BIAS_TANH: return launch<BN, EPI_BIAS_TANH, OUT_F32>(ta, tb, p, max_ctas, s);
+  }
+  fr::set_error("fr_gemm_bf16: unknown epilogue %d", epi);
+  return -1;
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (n <= 0) n = kNumSMs;
+  }
+  return n;
+}
+
+}  // namespace fr
+
+using namespace fr;
+
+// out = epi(A · W^T + bias).  A [M,K] ld=lda, W [N,K] ld=ldw (both bf16, K-major), out bf16 or fp32 ld=ldo.
+// block_n: 0 = choose, else 64/128/256.  m_dev (optional, device int): effective M = min(M, *m_dev*m_scale).
+FR_API int fr_gemm_bf16(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32,
+                        int M, int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n,
+                        const int* m_dev, int m_scale, void* stream) {
+  FR_REQUIRE(M >= 1 && N >= 8 && K >= 8, "fr_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
+  FR_REQUIRE(N % 8 == 0 && K % 8 == 0, "fr_gemm_bf16: N=%d and K=%d must be multiples of 8", N, K);
+  FR_REQUIRE(ldo % 8 == 0 && ((uintptr_t)out & 15) == 0, "fr_gemm_bf16: out must be 16-byte aligned, ldo %% 8 == 0");
+  FR_REQUIRE(epi != EPI_BIAS_RESID || (resid && ldr % 8 == 0 && ((uintptr_t)resid & 15) == 0),
+             "fr_gemm_bf16: residual epilogue needs an aligned resid pointer");
+  FR_REQUIRE(!bias || ((uintptr_t)bias & 15) == 0, "fr_gemm_bf16: bias must be 16-byte aligned");
+  if (block_n == 0) {
+    // fewest wasted columns first, then the widest tile (fewer A re-reads)
+    int best = 256, best_waste = ((N + 255) / 256) * 256 - N;
+    for (int bn : {128, 64}) {
+      const int waste = ((N + bn - 1) / bn) * bn - N;
+      if (waste < best_waste) { best = bn; best_waste = waste; }
+    }
+    block_n = best;
+  }
+  FR_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "fr_gemm_bf16: block_n=%d", block_n);
+  CUtensorMap ta, tb;
+  if (int e = make_tmap_bf16_2d(&ta, A, M, K, lda, BM)) return e;
+  if (int e = make_tmap_bf16_2d(&tb, W, N, K, ldw, block_n)) return e;
+  GemmParams p;
+  p.bias = bias; p.resid = (const __nv_bfloat16*)resid; p.out = out; p.m_dev = m_dev; p.m_scale = m_scale;
+  p.M = M; p.N = N; p.K = K; p.ldo = ldo; p.ldr = ldr;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int ctas = sm_count();
+  if (out_fp32) {
+    switch (block_n) {
+      case 64: return dispatch_epi<64, true>(epi, ta, tb, p, ctas, s);
+      case 128: return dispatch_epi<128, true>(epi, ta, tb, p, ctas, s);
+      default: return dispatch_epi<256, true>(epi, ta, tb, p, ctas, s);
+    }
+  }
+  switch (block_n) {
+    case 64: return dispatch_epi<64, false>(epi, ta, tb, p, ctas, s);
+    case 128: return dispatch_epi<128, false>(epi, ta, tb, p, ctas, s);
+    default: return dispatch_epi<256, false>(epi, ta, tb, p, ctas, s);
+  }
+}

@@ -1,0 +1,304 @@
+"""Federated orchestration: the five upstream entrypoints as modes of one round engine.
+
+Upstream: ``main.py`` (DDP baseline), ``Gradient_Averaging_main.py``
+(DDP + a 4-byte loss all-reduce, :146), ``Parameter_Averaging_main.py`` (local step, then
+116 per-tensor all-reduces, :144-148), ``client.py`` / ``server.py`` (control-flag
+broadcast, per-tensor model broadcast, local epochs, state_dict upload over TCP, server
+mean; client.py:256-292, server.py:72-105).
+
+Here a *round* is: every client draws a batch of ``batch_size`` impressions from its own
+shard, runs ``local_steps`` fused steps, and then one aggregation kernel runs:
+
+``ddp`` / ``grad_avg``  gradients of all 16 trainable tensors are averaged (optionally
+                        clipped and noised per client) **before** Adam;
+``param_avg``           Adam runs locally for ``local_steps`` steps, then parameters are
+                        FedAvg-averaged (uniform by default = upstream) and every rank
+                        receives the result;
+``client_server``       rank ``server_rank`` holds no data; each round it publishes the
+                        continue/stop flag and the global model, clients train locally
+                        with optional LDP noise, and the "upload + mean + redistribute"
+                        is the same FedAvg kernel with server weight 0.
+"""
+from __future__ import annotations
+
+import math
+import os
+import time
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..config import FedRecConfig
+from ..data import BatchSampler, ImpressionTable, load_user_data, make_synthetic_mind
+from ..models import ServerUserModel, UserModel
+from ..parallel import GradAggregator, ParamAggregator, init_distributed, shutdown_distributed
+from ..utils import checkpoint as ckpt
+from ..utils.health import FaultInjector, Heartbeat
+from ..utils.logging import MetricsLogger
+from ..utils.privacy import get_noise_multiplier
+from ..utils.trace import Tracer
+from .step import TrainStep
+from .trainer import Trainer
+
+
+class FederatedRunner:
+    def __init__(self, cfg: FedRecConfig, bert_config=None, news_index=None, nid2index=None,
+                 train_sam=None, valid_sam=None):
+        self.cfg = cfg
+        self.info = init_distributed(cfg.backend, cfg.timeout_s, cfg.device)
+        self.rank, self.W, self.device = self.info.rank, self.info.world_size, self.info.device
+        self.is_server = cfg.mode == "client_server" and self.W > 1 and self.rank == cfg.server_rank
+        torch.manual_seed(cfg.seed)                       # identical initial weights on every rank
+        # ---- data: each rank is one client with its own shard (README.md:22) ----------
+        if news_index is None:
+            if cfg.synthetic or not os.path.isdir(cfg.data_dir):
+                d = make_synthetic_mind(cfg.num_news, cfg.num_train, cfg.num_valid, cfg.title_len,
+                                        cfg.max_his_len, seed=cfg.seed, client=self.rank)
+                nid2index, news_index, train_sam, valid_sam = d.nid2index, d.news_index, d.train_sam, d.valid_sam
+            else:
+                nid2index, news_index, train_sam, valid_sam = load_user_data(cfg.data_dir)
+        self.nid2index, self.news_index = nid2index, news_index
+        self.train_sam, self.valid_sam = train_sam, valid_sam
+        # ---- peer-mapped memory for the aggregation kernels ----------------------------------
+        self.symm = None
+        allocator = None
+        if self.device.type == "cuda" and self.W > 1 and cfg.transport == "nvlink":
+            from ..parallel.symm import SymmetricHeap
+            self.symm = SymmetricHeap.create(self.info)
+            allocator = self.symm.alloc_f32
+        # ---- model -------------------------------------------------------------------
+        if self.is_server:
+            self.model = ServerUserModel(self.device, config=cfg, bert_config=bert_config, flat_allocator=allocator)
+        else:
+            self.model = UserModel(None, news_index, self.device, config=cfg, bert_config=bert_config,
+                                   flat_allocator=allocator)
+        if self.symm is not None:
+            self.symm.finalize()
+        self.step = None if self.is_server else TrainStep(self.model, cfg)
+        transport = "nvlink" if self.symm is not None else "collective"
+        participants = [r for r in range(self.W) if not (cfg.mode == "client_server" and self.W > 1 and r == cfg.server_rank)]
+        self.grad_agg = GradAggregator(self.model.flat, self.W, self.rank, transport, cfg.clip_norm,
+                                       cfg.noise_multiplier, cfg.seed, self.symm, participants=participants)
+        self.param_agg = ParamAggregator(self.W, self.rank, transport, self.symm)
+        self.sampler = None
+        if not self.is_server and train_sam:
+            table = ImpressionTable(train_sam, nid2index, cfg.max_his_len)
+            self.sampler = BatchSampler(table, cfg.batch_size, cfg.npratio, seed=cfg.seed + 101 * self.rank,
+                                        pin=self.device.type == "cuda")
+            self._dev_cand = torch.zeros(cfg.batch_size, cfg.num_candidates, dtype=torch.int32, device=self.device)
+            self._dev_his = torch.zeros(cfg.batch_size, cfg.max_his_len, dtype=torch.int32, device=self.device)
+        self.logger = MetricsLogger(cfg.log_dir, cfg.run_name, self.rank, enabled=bool(cfg.log_dir))
+        self.tracer = Tracer(enabled=os.environ.get("FEDREC_TRACE") == "1", device=self.device)
+        self.faults = FaultInjector()
+        self.heartbeat: Optional[Heartbeat] = None
+        if cfg.heartbeat_s > 0 and self.W > 1:
+            store = dist.distributed_c10d._get_default_store()
+            self.heartbeat = Heartbeat(store, self.rank, self.W, period_s=cfg.heartbeat_s,
+                                       stale_s=max(10 * cfg.heartbeat_s, 30.0), on_stale=self._on_stale).start()
+        self.round = 0
+        self.epochs_run = 0
+        if cfg.snapshot_path and os.path.exists(cfg.snapshot_path):
+            info = ckpt.load_snapshot(cfg.snapshot_path, self.model)
+            self.epochs_run = info["EPOCHS_RUN"]
+            self.round = int(info.get("ROUND", self.epochs_run))
+            print(f"Resuming training from snapshot at Epoch {self.epochs_run}")
+        if self.W > 1:
+            self._sync_initial_state()
+
+    # ------------------------------------------------------------------------------------------
+    def _on_stale(self, ranks: List[int]) -> None:
+        print(f"[fedrec r{self.rank}] no progress from rank(s) {ranks} for >{self.heartbeat.stale_s:.0f}s — "
+              f"a client has failed or is a straggler; the job will time out after {self.cfg.timeout_s:.0f}s "
+              f"and can be resumed from {self.cfg.snapshot_path}", flush=True)
+
+    def _sync_initial_state(self) -> None:
+        """Everyone starts from rank 0's weights (DDP constructor broadcast)."""
+        src = self.cfg.server_rank if self.cfg.mode == "client_server" else 0
+        src = src if src < self.W else 0
+        self.param_agg.broadcast_(self.model.flat.param, src)
+        # the frozen trunk is seeded identically on every rank; broadcast only when asked to
+        if self.cfg.average_frozen:
+            for p in self.model.text_encoder.DistillBert.parameters():
+                dist.broadcast(p.data, src=src)
+            self.model.on_weights_changed()
+
+    def next_batch(self):
+        cand, his = self.sampler.next()
+        self._dev_cand.copy_(cand, non_blocking=True)
+        self._dev_his.copy_(his, non_blocking=True)
+        return self._dev_cand, self._dev_his
+
+    def local_step(self) -> torch.Tensor:
+        cand, his = self.next_batch()
+        with self.tracer.span("step"):
+            return self.step.run(cand, his, train=True)
+
+    def fedavg_weights(self) -> Optional[List[float]]:
+        cfg = self.cfg
+        if cfg.client_weights is not None:
+            w = list(cfg.client_weights)
+            if len(w) != self.W:
+                raise ValueError(f"client_weights has {len(w)} entries for world size {self.W}")
+        else:
+            w = [1.0] * self.W
+        if cfg.mode == "client_server" and self.W > 1:
+            w[cfg.server_rank] = 0.0
+        return w
+
+    def validate(self):
+        if self.is_server or not self.valid_sam:
+            return None
+        t = Trainer.__new__(Trainer)
+        t.model, t.step = self.model, self.step
+        return Trainer.validate(t, self.valid_sam, self.nid2index)
+
+    def save(self, epoch: int) -> None:
+        ckpt.save_snapshot(self.cfg.snapshot_path, self.model, next_epoch=epoch + 1, rank=self.rank,
+                           extra={"ROUND": self.round})
+
+    # ---- modes ---------------------------------------------------------------------------------------
+    def run_gradient_averaging(self) -> float:
+        cfg = self.cfg
+        loss = torch.zeros((), device=self.device)
+        for epoch in range(self.epochs_run, cfg.total_epochs):
+            self.faults.maybe_fire(self.rank, epoch)
+            loss = self.local_step()
+            with self.tracer.span("aggregate"):
+                self.grad_agg.allreduce_mean_()
+            with self.tracer.span("adam"):
+                self.model.adam_step()
+            self.round += 1
+            if self.heartbeat:
+                self.heartbeat.beat(self.round)
+            self._end_of_epoch(epoch, loss, reduce_loss=cfg.mode == "grad_avg")
+        return float(loss)
+
+    def run_parameter_averaging(self) -> float:
+        cfg = self.cfg
+        loss = torch.zeros((), device=self.device)
+        weights = self.fedavg_weights()
+        for epoch in range(self.epochs_run, cfg.total_epochs):
+            self.faults.maybe_fire(self.rank, epoch)
+            for _ in range(max(cfg.local_steps, 1)):
+                loss = self.local_step()
+                self.model.adam_step()
+            if (epoch + 1) % cfg.save_every == 0 and cfg.snapshot_path:
+                self.save(epoch)                                  # saved before averaging, as PA:140-141
+            with self.tracer.span("aggregate"):
+                self.param_agg.average_(self.model.flat.param, weights)
+                if cfg.average_frozen and self.W > 1:
+                    self._average_frozen(weights)
+            self.round += 1
+            if self.heartbeat:
+                self.heartbeat.beat(self.round)
+            self._end_of_epoch(epoch, loss, reduce_loss=False, save=False)
+        return float(loss)
+
+    def _average_frozen(self, weights) -> None:
+        tot = sum(weights)
+        for p in self.model.text_encoder.DistillBert.parameters():
+            p.data.mul_(weights[self.rank] / tot)
+            dist.all_reduce(p.data)
+        self.model.on_weights_changed()
+
+    def run_client_server(self) -> float:
+        """Both roles; ``global_epochs`` rounds of ``total_epochs`` local steps (client.py:258-292, server.py:72-105)."""
+        cfg = self.cfg
+        flag = torch.zeros(1, device=self.device)
+        weights = self.fedavg_weights()
+        src = cfg.server_rank if self.W > 1 else 0
+        sigma = None
+        if cfg.dp_epsilon > 0 and not self.is_server:
+            sample_rate = min(1.0, cfg.batch_size / max(len(self.train_sam), 1))
+            sigma = get_noise_multiplier(cfg.dp_epsilon, cfg.dp_delta, sample_rate, epochs=cfg.dp_epochs)
+            cfg.news_grad_noise = sigma                          # client.py:87-89: noise on news-vector grads
+            print(f"Applying sigma {sigma:.4f} for DP")
+        loss = torch.zeros((), device=self.device)
+        rnd = self.epochs_run
+        while True:
+            if self.rank == src:
+                flag.fill_(1.0 if rnd < cfg.global_epochs else 0.0)
+            if self.W > 1:
+                dist.broadcast(flag, src=src)                     # X7 control flag
+            elif rnd >= cfg.global_epochs:
+                flag.zero_()
+            if int(flag.item()) == 0:
+                break
+            self.faults.maybe_fire(self.rank, rnd)
+            self.param_agg.broadcast_(self.model.flat.param, src)  # X8 model sync
+            if not self.is_server:
+                for _ in range(max(cfg.total_epochs, 1)):
+                    loss = self.local_step()
+                    self.model.adam_step()
+                v = self.validate()
+                rec = {"round": rnd, "training_loss": float(loss)}
+                if v:
+                    rec.update({"validation_loss": v[0], "valid_auc": v[1], "valid_mrr": v[2],
+                                "val_ndcg@5": v[3], "val_ndcg@10": v[4]})
+                self.logger.log(rec, step=rnd)
+            with self.tracer.span("aggregate"):
+                self.param_agg.average_(self.model.flat.param, weights)   # X9 + K23 in one kernel
+            rnd += 1
+            self.round = rnd
+            if self.heartbeat:
+                self.heartbeat.beat(rnd)
+            if cfg.snapshot_path and rnd % cfg.save_every == 0 and self.rank == src:
+                ckpt.save_snapshot(cfg.snapshot_path, self.model, next_epoch=rnd, rank=0, extra={"ROUND": rnd})
+        return float(loss)
+
+    def _end_of_epoch(self, epoch: int, loss: torch.Tensor, reduce_loss: bool, save: bool = True) -> None:
+        cfg = self.cfg
+        rec = {"epoch": epoch, "training_loss": float(loss)}
+        if reduce_loss and self.W > 1:
+            tot = loss.detach().clone()
+            dist.all_reduce(tot)                                   # GA:146
+            rec["loss_sum_all_clients"] = float(tot)
+        self.logger.log(rec, step=epoch)
+        if save and cfg.snapshot_path and (epoch + 1) % cfg.save_every == 0:
+            self.save(epoch)
+
+    def run(self) -> float:
+        mode = self.cfg.mode
+        try:
+            if mode in ("ddp", "grad_avg"):
+                return self.run_gradient_averaging()
+            if mode == "param_avg":
+                return self.run_parameter_averaging()
+            if mode == "client_server":
+                return self.run_client_server()
+            raise ValueError(f"unknown mode {mode!r}")
+        finally:
+            self.close()
+
+    def close(self) -> None:
+        if self.heartbeat:
+            self.heartbeat.stop()
+        if self.tracer.enabled:
+            os.makedirs(self.cfg.log_dir or ".", exist_ok=True)
+            self.tracer.export_chrome(os.path.join(self.cfg.log_dir or ".", f"trace.rank{self.rank}.json"))
+        self.logger.close()
+        if self.symm is not None:
+            self.symm.close()
+        shutdown_distributed(self.info)
+
+
+_POSITIONAL = {
+    "ddp": ["total_epochs", "batch_size", "save_every"],
+    "grad_avg": ["total_epochs", "batch_size", "save_every"],
+    "param_avg": ["total_epochs", "batch_size", "save_every"],
+    "client": ["total_epochs", "batch_size", "save_every", "dp_epsilon", "run_name"],
+    "server": ["global_epochs"],
+}
+
+
+def run_entrypoint(kind: str, argv: List[str]) -> float:
+    """Shared ``__main__`` of the five reference-named scripts."""
+    mode = {"client": "client_server", "server": "client_server"}.get(kind, kind)
+    cfg = FedRecConfig.from_argv(argv, _POSITIONAL[kind], mode=mode)
+    if kind == "server":
+        rank = int(os.environ.get("RANK", "0"))
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        if world > 1 and rank != cfg.server_rank:
+            raise SystemExit(f"server.py must run as rank {cfg.server_rank} (got {rank}); clients run client.py")
+    return FederatedRunner(cfg).run()

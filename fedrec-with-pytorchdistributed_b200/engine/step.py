@@ -1,0 +1,99 @@
+"""One local training step: batch of impressions → gradients in the flat buffer.
+
+Reference flow being replaced: ``UserModel.forward`` (2·B DistilBERT
+calls through numpy), ``loss.backward()``, leaf grads to CPU, ``process_news_grad``
+Python loop, ``collect``, then ``update_news_grad`` re-running DistilBERT with grad.
+
+Two implementations with identical results up to dtype:
+
+``torch``  end-to-end autograd in fp32: unique ids → frozen trunk (no_grad) → head →
+           gather → user encoder → score → CE → backward. This is the in-repo oracle
+           and the CPU path. Differentiating through the gather *is* the segment-sum
+           of news gradients followed by the injected head backward.
+``fused``  the sm_100a kernel pipeline in ``engine/fused.py`` (bf16 tensor-core trunk
+           and head, fused user-encoder forward/backward, device-side de-dup).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+import torch.nn.functional as F
+
+from ..config import FedRecConfig
+
+
+class TrainStep:
+    def __init__(self, model, cfg: Optional[FedRecConfig] = None, impl: Optional[str] = None):
+        self.model = model
+        self.cfg = cfg or model.cfg
+        dev = model.device
+        if impl is None:
+            impl = "fused" if (dev.type == "cuda" and self.cfg.fused) else "torch"
+        self.impl = impl
+        self._fused = None
+        if impl == "fused":
+            from .fused import FusedStep
+            self._fused = FusedStep(model, self.cfg)
+            model._fused = self._fused
+        self._gen = torch.Generator(device=dev)
+        self._gen.manual_seed(self.cfg.seed + 17)
+
+    # ---------------------------------------------------------------------------------
+    def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
+        """``cand [B,C]``, ``his [B,L]`` integer news rows on the model device → scalar loss tensor.
+
+        Leaves d(loss)/d(trainable) in ``model.flat.grad`` (overwritten, not accumulated).
+        """
+        if self._fused is not None:
+            return self._fused.run(cand, his, train=train)
+        return self._run_torch(cand, his, train)
+
+    def scores(self, cand: torch.Tensor, his: torch.Tensor) -> torch.Tensor:
+        """Inference: ``sigmoid(cand · user)`` ``[B, C]`` without touching gradients."""
+        if self._fused is not None:
+            return self._fused.scores(cand, his)
+        m = self.model
+        was = m.training
+        m.eval()
+        with torch.no_grad():
+            score, _, _ = m(cand, his, None, compute_loss=False)
+        m.train(was)
+        return score
+
+    # ---------------------------------------------------------------------------------
+    def _run_torch(self, cand, his, train):
+        m, cfg = self.model, self.cfg
+        B, C = cand.shape
+        L = his.shape[1]
+        m.train(train)
+        ids = torch.cat([his.reshape(-1), cand.reshape(-1)]).long()
+        if cfg.dedup:
+            uniq, inv = torch.unique(ids, return_inverse=True)
+        else:
+            uniq, inv = ids, torch.arange(ids.numel(), device=ids.device)
+        if cfg.trunk_dropout_in_update and train:
+            # upstream quirk (model.py:73): the gradient pass re-runs DistilBERT in train mode
+            m.text_encoder.DistillBert.train()
+            with torch.no_grad():
+                hidden = m.text_encoder.trunk(m.news_tokens[uniq].long(), m.news_mask[uniq])
+            vec = m.text_encoder.head(hidden, m.news_mask[uniq])
+        else:
+            vec = m.encode_unique(uniq, keep_cache=False, with_grad=True)
+        his_vec = vec[inv[: B * L]].view(B, L, -1)
+        cand_vec = vec[inv[B * L:]].view(B, C, -1)
+        if train and cfg.news_grad_noise > 0:
+            std = cfg.news_grad_noise
+
+            def _noise(g):
+                return g + torch.randn(g.shape, device=g.device, dtype=g.dtype, generator=self._gen) * std
+            his_vec.register_hook(_noise)
+            cand_vec.register_hook(_noise)
+        his_mask = (his != 0) if cfg.mask_padding else None
+        user = m.user_encoder(his_vec, his_mask)
+        score = torch.sigmoid(torch.bmm(cand_vec, user.unsqueeze(-1)).squeeze(-1))
+        loss = F.cross_entropy(score, torch.zeros(B, dtype=torch.long, device=score.device))
+        if train:
+            m.flat.zero_grad()
+            loss.backward()
+        return loss.detach()

@@ -1,0 +1,172 @@
+"""Device dispatch: CUDA tensors → sm_100a kernels (mandatory), CPU tensors → ``ops.reference``."""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import reference as ref
+from .native import check, require_native
+
+_LAUNCHES = 0   # kernels launched through this layer (bench.py reports it as gpu_launches)
+
+
+def launch_count() -> int:
+    return _LAUNCHES
+
+
+def count_launches(n: int = 1) -> None:
+    global _LAUNCHES
+    _LAUNCHES += n
+
+
+def stream_ptr(device=None) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _f32c(t: torch.Tensor) -> torch.Tensor:
+    if t.dtype != torch.float32 or not t.is_contiguous():
+        t = t.contiguous().float()
+    return t
+
+
+# ----------------------------------------------------------------------------------------------
+class _ScoreCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, cand, user, labels):
+        lib = require_native()
+        cand, user = _f32c(cand), _f32c(user)
+        B, C, D = cand.shape
+        score = torch.empty(B, C, device=cand.device, dtype=torch.float32)
+        loss = torch.empty((), device=cand.device, dtype=torch.float32)
+        d_cand = torch.empty_like(cand)
+        d_user = torch.empty_like(user)
+        lab = labels.to(torch.int32).contiguous() if labels is not None else None
+        check(lib.fr_score_ce(cand.data_ptr(), user.data_ptr(), _p(lab), score.data_ptr(), None, loss.data_ptr(),
+                              d_cand.data_ptr(), d_user.data_ptr(), 1.0, B, C, D, stream_ptr(cand.device)), "fr_score_ce")
+        count_launches(1)
+        ctx.save_for_backward(d_cand, d_user)
+        ctx.mark_non_differentiable(score)
+        return loss, score
+
+    @staticmethod
+    def backward(ctx, g_loss, _g_score):
+        d_cand, d_user = ctx.saved_tensors
+        return d_cand * g_loss, d_user * g_loss, None
+
+
+def score_ce(cand: torch.Tensor, user: torch.Tensor, labels: Optional[torch.Tensor] = None):
+    if cand.is_cuda:
+        return _ScoreCE.apply(cand, user, labels)
+    return ref.score_ce(cand, user, labels)
+
+
+def segment_sum(vals: torch.Tensor, seg: torch.Tensor, num_segments: int) -> torch.Tensor:
+    if not vals.is_cuda:
+        return ref.segment_sum(vals, seg, num_segments)
+    lib = require_native()
+    vals = _f32c(vals)
+    seg = seg.to(torch.int32).contiguous()
+    K, D = vals.shape
+    out = torch.empty(num_segments, D, device=vals.device, dtype=torch.float32)
+    check(lib.fr_segment_sum(vals.data_ptr(), seg.data_ptr(), out.data_ptr(), K, num_segments, D,
+                             stream_ptr(vals.device)), "fr_segment_sum")
+    count_launches(1)
+    return out
+
+
+def adam_flat(flat, lr: float, b1: float, b2: float, eps: float, grad_scale: float = 1.0) -> None:
+    """One Adam step over ``flat.param`` using ``flat.grad`` (torch.optim.Adam defaults)."""
+    flat.step += 1
+    if not flat.param.is_cuda:
+        with torch.no_grad():
+            ref.adam_(flat.param, flat.grad, flat.exp_avg, flat.exp_avg_sq, flat.step, lr, b1, b2, eps, grad_scale)
+        return
+    lib = require_native()
+    bc1 = 1.0 - b1 ** flat.step
+    bc2 = 1.0 - b2 ** flat.step
+    check(lib.fr_adam_flat(flat.param.data_ptr(), flat.grad.data_ptr(), flat.exp_avg.data_ptr(),
+                           flat.exp_avg_sq.data_ptr(), flat.numel, lr, b1, b2, eps, bc1, bc2, None, grad_scale,
+                           stream_ptr(flat.param.device)), "fr_adam_flat")
+    count_launches(1)
+
+
+def grad_sq_norm(x: torch.Tensor) -> torch.Tensor:
+    if not x.is_cuda:
+        return (x.float() ** 2).sum()
+    lib = require_native()
+    out = torch.empty((), device=x.device, dtype=torch.float32)
+    check(lib.fr_sq_norm(x.data_ptr(), x.numel(), out.data_ptr(), stream_ptr(x.device)), "fr_sq_norm")
+    count_launches(1)
+    return out
+
+
+def clip_noise_(x: torch.Tensor, clip: float, noise_std: float, seed: int = 0, stream_id: int = 0,
+                generator=None) -> torch.Tensor:
+    """In place: scale ``x`` to L2 norm ≤ ``clip`` (0 = off), then add ``N(0, noise_std²)``."""
+    if clip <= 0 and noise_std <= 0:
+        return x
+    if not x.is_cuda:
+        return ref.clip_noise_(x, clip, noise_std, generator)
+    lib = require_native()
+    sq = grad_sq_norm(x) if clip > 0 else None
+    check(lib.fr_clip_noise(x.data_ptr(), x.numel(), _p(sq), float(clip), float(noise_std), int(seed) & (2**64 - 1),
+                            int(stream_id) & 0xFFFFFFFF, stream_ptr(x.device)), "fr_clip_noise")
+    count_launches(1)
+    return x
+
+
+def dedup(ids: torch.Tensor, table_rows: int, workspace: Optional[torch.Tensor] = None
+          ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Sync-free unique: returns ``(uniq[K] padded with 0, count[1] int32 device, inv[K])``."""
+    flat = ids.reshape(-1)
+    K = flat.numel()
+    if not ids.is_cuda:
+        u, inv = ref.dedup(flat)
+        uniq = torch.zeros(K, dtype=torch.int32)
+        uniq[: u.numel()] = u.to(torch.int32)
+        return uniq, torch.tensor([u.numel()], dtype=torch.int32), inv.to(torch.int32)
+    lib = require_native()
+    flat = flat.to(torch.int32).contiguous()
+    need = lib.fr_dedup_workspace_ints(table_rows)
+    if workspace is None or workspace.numel() < need:
+        workspace = torch.empty(need, dtype=torch.int32, device=ids.device)
+    uniq = torch.empty(K, dtype=torch.int32, device=ids.device)
+    inv = torch.empty(K, dtype=torch.int32, device=ids.device)
+    count = torch.empty(1, dtype=torch.int32, device=ids.device)
+    check(lib.fr_dedup(flat.data_ptr(), K, table_rows, workspace.data_ptr(), uniq.data_ptr(), count.data_ptr(),
+                       inv.data_ptr(), stream_ptr(ids.device)), "fr_dedup")
+    count_launches(5)
+    return uniq, count, inv
+
+
+_EPI = {"none": 0, "bias": 0, "gelu": 1, "resid": 2, "tanh": 3}
+
+
+def linear_bf16(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, epi: str = "bias",
+                resid: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
+                out_dtype: torch.dtype = torch.bfloat16, block_n: int = 0,
+                m_dev: Optional[torch.Tensor] = None, m_scale: int = 1) -> torch.Tensor:
+    """``epi(x @ w.T + bias)`` on the tcgen05 GEMM. ``x [M,K]`` and ``w [N,K]`` bf16 with unit inner stride."""
+    assert x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    assert x.dim() == 2 and w.dim() == 2 and x.stride(1) == 1 and w.stride(1) == 1
+    lib = require_native()
+    M, K = x.shape
+    N = w.shape[0]
+    if out is None:
+        out = torch.empty(M, N, device=x.device, dtype=out_dtype)
+    assert out.stride(1) == 1
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.is_contiguous()
+    if resid is not None:
+        assert resid.dtype == torch.bfloat16 and resid.stride(1) == 1
+    check(lib.fr_gemm_bf16(x.data_ptr(), w.data_ptr(), _p(bias), _p(resid), out.data_ptr(),
+                           1 if out.dtype == torch.float32 else 0, M, N, K, x.stride(0), w.stride(0), out.stride(0),
+                           resid.stride(0) if resid is not None else 0, _EPI[epi], block_n, _p(m_dev), m_scale,
+                           stream_ptr(x.device)), "fr_gemm_bf16")
+    count_launches(1)
+    return out

@@ -1,0 +1,101 @@
+"""Per-round aggregation: gradient averaging and parameter averaging.
+
+What is being replaced: DDP's bucketed gradient all-reduce (X3), the
+4-byte loss all-reduce (X5), the 116 per-tensor parameter all-reduces of
+Parameter_Averaging_main.py:144-148 (X6), and the client→server state_dict upload +
+server mean + per-tensor broadcast of client.py/server.py (X7-X9, K23).
+
+Two transports implement the same interface:
+
+``collective``  torch.distributed (gloo on CPU, NCCL on GPU) over the flat buffer:
+                one all-reduce instead of 16 or 116. This is the *baseline* path and
+                the one CPU tests use.
+``nvlink``      the fused sm_100a kernels in ``csrc/aggregate.cu``: each rank's flat
+                buffer lives in peer-mapped memory; one kernel does L2-clip, Gaussian
+                noise, the cross-GPU reduction over NVLink loads, the 1/N (or FedAvg
+                weight) scaling and the write-back/broadcast. No NCCL call.
+
+Semantics adopted: every trainable gradient is averaged
+before the optimiser step; clipping bounds each client's flat gradient to L2 norm C;
+noise is N(0, (sigma·C)²) per coordinate per client, added before averaging.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .. import ops
+
+
+class GradAggregator:
+    def __init__(self, flat, world_size: int, rank: int, transport: str = "collective",
+                 clip_norm: float = 0.0, noise_multiplier: float = 0.0, seed: int = 0, symm=None,
+                 group=None, participants: Optional[Sequence[int]] = None):
+        self.flat = flat
+        self.W, self.rank = world_size, rank
+        self.transport = transport
+        self.clip, self.sigma = float(clip_norm), float(noise_multiplier)
+        self.seed = seed
+        self.symm = symm
+        self.group = group
+        self.round = 0
+        self.participants = list(participants) if participants is not None else list(range(world_size))
+
+    @property
+    def noise_std(self) -> float:
+        # sigma is relative to the clip bound when clipping is on (DP-SGD convention)
+        return self.sigma * (self.clip if self.clip > 0 else 1.0)
+
+    def allreduce_mean_(self, buf: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Clip + noise this client's gradient, then replace it by the mean over participants."""
+        g = self.flat.grad if buf is None else buf
+        self.round += 1
+        if self.transport == "nvlink" and self.symm is not None and self.W > 1:
+            self.symm.grad_allreduce_(g, clip=self.clip, noise_std=self.noise_std,
+                                      seed=self.seed + 7919 * self.round, scale=1.0 / len(self.participants))
+            return g
+        ops.clip_noise_(g, self.clip, self.noise_std, seed=self.seed + 7919 * self.round, stream_id=self.rank)
+        if self.W > 1:
+            if self.rank not in self.participants:
+                g.zero_()
+            dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group)
+            g.mul_(1.0 / len(self.participants))
+        return g
+
+
+class ParamAggregator:
+    """Weighted FedAvg of a flat parameter buffer + broadcast of the result to every rank."""
+
+    def __init__(self, world_size: int, rank: int, transport: str = "collective", symm=None, group=None):
+        self.W, self.rank = world_size, rank
+        self.transport = transport
+        self.symm = symm
+        self.group = group
+
+    def average_(self, buf: torch.Tensor, weights: Optional[Sequence[float]] = None) -> torch.Tensor:
+        """``buf ← Σ_i w_i·buf_i / Σ_i w_i`` on every rank (weight 0 = aggregation-only server rank)."""
+        if self.W == 1:
+            return buf
+        w = [1.0] * self.W if weights is None else [float(x) for x in weights]
+        tot = sum(w)
+        if tot <= 0:
+            raise ValueError("FedAvg weights must have a positive sum")
+        mine = w[self.rank] / tot
+        if self.transport == "nvlink" and self.symm is not None:
+            self.symm.param_average_(buf, [x / tot for x in w])
+            return buf
+        buf.mul_(mine)
+        dist.all_reduce(buf, op=dist.ReduceOp.SUM, group=self.group)
+        return buf
+
+    def broadcast_(self, buf: torch.Tensor, src: int) -> torch.Tensor:
+        if self.W > 1:
+            if self.transport == "nvlink" and self.symm is not None:
+                w = [0.0] * self.W
+                w[src] = 1.0
+                self.symm.param_average_(buf, w)
+            else:
+                dist.broadcast(buf, src=src, group=self.group)
+        return buf

@@ -1,0 +1,124 @@
+"""gloo, world_size=2, CPU: the aggregation plumbing of BASELINE.json config #1."""
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, mode, tmp, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    from fedrec_b200.models.distilbert import DistilBertConfigLite
+    bert = DistilBertConfigLite(n_layers=1, dim=32, hidden_dim=64, n_heads=2, hidden_size=32)
+    cfg = FedRecConfig(mode=mode, synthetic=True, num_news=128, num_train=32, num_valid=4, title_len=8,
+                       batch_size=4, total_epochs=2, global_epochs=2, local_steps=2, dropout=0.0, device="cpu",
+                       backend="gloo", snapshot_path=os.path.join(tmp, f"snap_{mode}.pt"), log_dir="",
+                       server_rank=1, lr=1e-2)
+    r = FederatedRunner(cfg, bert_config=bert)
+    res = {}
+    if mode == "grad_avg":
+        loss = r.local_step()
+        local = r.model.flat.grad.clone()
+        gathered = [torch.zeros_like(local) for _ in range(world)]
+        dist.all_gather(gathered, local)
+        r.grad_agg.allreduce_mean_()
+        res["mean_ok"] = bool(torch.allclose(r.model.flat.grad, sum(gathered) / world, atol=1e-7))
+        res["differs"] = bool(not torch.allclose(gathered[0], gathered[1]))
+        r.model.adam_step()
+        p = r.model.flat.param.clone()
+        ps = [torch.zeros_like(p) for _ in range(world)]
+        dist.all_gather(ps, p)
+        res["params_equal"] = bool(torch.equal(ps[0], ps[1]))
+        res["loss"] = float(loss)
+        r.close()
+    else:
+        res["loss"] = r.run() if False else None
+        # run() closes the group; gather state before that by running the mode body directly
+    q.put((rank, res))
+
+
+def _run_mode(rank, world, port, mode, tmp, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    from fedrec_b200.models.distilbert import DistilBertConfigLite
+    bert = DistilBertConfigLite(n_layers=1, dim=32, hidden_dim=64, n_heads=2, hidden_size=32)
+    cfg = FedRecConfig(mode=mode, synthetic=True, num_news=128, num_train=32, num_valid=4, title_len=8,
+                       batch_size=4, total_epochs=2, global_epochs=2, local_steps=2, dropout=0.0, device="cpu",
+                       backend="gloo", snapshot_path=os.path.join(tmp, f"snap_{mode}.pt"), log_dir="",
+                       server_rank=1, lr=1e-2, client_weights=[3.0, 1.0] if mode == "param_avg" else None)
+    r = FederatedRunner(cfg, bert_config=bert)
+    init = r.model.flat.param.clone()
+    if mode == "param_avg":
+        # one manual round to check the weighted mean in closed form
+        for _ in range(2):
+            r.local_step()
+            r.model.adam_step()
+        p = r.model.flat.param.clone()
+        ps = [torch.zeros_like(p) for _ in range(world)]
+        dist.all_gather(ps, p)
+        r.param_agg.average_(r.model.flat.param, r.fedavg_weights())
+        ok = torch.allclose(r.model.flat.param, 0.75 * ps[0] + 0.25 * ps[1], atol=1e-6)
+        q.put((rank, {"weighted_ok": bool(ok), "moved": bool(not torch.equal(init, p))}))
+        r.close()
+        return
+    loss = None
+    if mode == "client_server":
+        try:
+            loss = r.run_client_server()
+            p = r.model.flat.param.clone()
+            ps = [torch.zeros_like(p) for _ in range(world)]
+            dist.all_gather(ps, p)
+            q.put((rank, {"equal": bool(torch.equal(ps[0], ps[1])), "moved": bool(not torch.equal(init, p)),
+                          "is_server": r.is_server, "loss": loss}))
+        finally:
+            r.close()
+
+
+@pytest.mark.parametrize("mode", ["grad_avg"])
+def test_gradient_averaging_two_ranks(tmp_path, mode):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, mode, str(tmp_path), q)) for r in range(2)]
+    [p.start() for p in procs]
+    out = dict(q.get(timeout=240) for _ in range(2))
+    [p.join(60) for p in procs]
+    for r in range(2):
+        assert out[r]["mean_ok"] and out[r]["params_equal"], out
+    assert out[0]["differs"]                              # the clients really had different gradients
+
+
+@pytest.mark.parametrize("mode", ["param_avg", "client_server"])
+def test_parameter_modes_two_ranks(tmp_path, mode):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_run_mode, args=(r, 2, port, mode, str(tmp_path), q)) for r in range(2)]
+    [p.start() for p in procs]
+    out = dict(q.get(timeout=240) for _ in range(2))
+    [p.join(60) for p in procs]
+    if mode == "param_avg":
+        assert all(out[r]["weighted_ok"] and out[r]["moved"] for r in range(2)), out
+    else:
+        assert out[0]["equal"] and out[1]["equal"] and out[1]["is_server"] and not out[0]["is_server"], out
+        assert out[0]["moved"] and out[1]["moved"]        # the server received the clients' average

@@ -1,0 +1,62 @@
+import numpy as np
+import pytest
+import torch
+
+from conftest import load_reference_module
+from fedrec_b200.utils import metrics as M
+
+
+def test_golden_values():
+    # values computed from the upstream evaluation_functions.py during the survey
+    a = M.compute_amn([1, 0, 0, 1, 0], [.1, .4, .35, .8, .2])
+    assert a == pytest.approx((0.5, 0.6, 0.850345, 0.850345), abs=1e-5)
+    b = M.compute_amn([1, 0, 0, 0, 0], [.55, .6, .5, .52, .51])
+    assert b == pytest.approx((0.75, 0.5, 0.630930, 0.630930), abs=1e-5)
+
+
+def test_against_upstream_module():
+    up = load_reference_module("evaluation_functions")
+    if up is None:
+        pytest.skip("upstream sources not available")
+    rng = np.random.default_rng(0)
+    for _ in range(50):
+        n = int(rng.integers(3, 40))
+        y = (rng.random(n) < 0.3).astype(int)
+        if y.sum() in (0, n):
+            y[0], y[1] = 1, 0
+        s = rng.random(n)
+        assert M.compute_amn(y, s) == pytest.approx(up.compute_amn(y, s), abs=1e-9)
+
+
+def test_auc_ties_match_sklearn():
+    from sklearn.metrics import roc_auc_score
+    y = [1, 0, 1, 0, 0, 1]
+    s = [0.5, 0.5, 0.7, 0.1, 0.7, 0.2]
+    assert M.roc_auc_score(y, s) == pytest.approx(roc_auc_score(y, s))
+
+
+def test_batched_matches_numpy():
+    rng = np.random.default_rng(1)
+    S, C = 64, 5
+    scores = rng.random((S, C)).astype(np.float32)
+    labels = np.zeros((S, C), dtype=np.float32)
+    labels[:, 0] = 1
+    out = M.batched_ranking_metrics(torch.tensor(scores), torch.tensor(labels))
+    for i in range(S):
+        a = M.compute_amn(labels[i], scores[i])
+        got = (out["auc"][i].item(), out["mrr"][i].item(), out["ndcg5"][i].item(), out["ndcg10"][i].item())
+        assert got == pytest.approx(a, abs=1e-5)
+
+
+def test_evaluation_split():
+    rng = np.random.default_rng(2)
+    nid2index = {f"N{i}": i for i in range(20)}
+    news_vecs = rng.standard_normal((20, 8))
+    user_vecs = rng.standard_normal((3, 8))
+    samples = [(0, ["N1", "N2"], ["N3", "N4", "N5"], [], "u"), (1, ["N6"], ["N7", "N8"], [], "u"),
+               (2, ["N9"], ["N10"], [], "u")]
+    out = M.evaluation_split(news_vecs, user_vecs, samples, nid2index)
+    assert out.shape == (3, 4)
+    up = load_reference_module("evaluation_functions")
+    if up is not None:
+        np.testing.assert_allclose(out, up.evaluation_split(news_vecs, user_vecs, samples, nid2index), atol=1e-9)
