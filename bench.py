@@ -1,0 +1,290 @@
+#!/usr/bin/env python
+"""Headline benchmark: training impressions/sec on N GPUs of one box (BASELINE.json).
+
+Config (BASELINE.json #2 + #4): `Gradient_Averaging_main` semantics, one federated client per GPU,
+50 users (impressions) per client per round, history 50, 4 negatives per positive, title length 30,
+full-size DistilBERT text encoder + user encoder, per-client L2 clip + LDP Gaussian noise inside the
+gradient aggregation, bf16 tensor-core compute, synthetic MIND-shaped data, random-init weights.
+One step = one round: forward, backward, gradient aggregation across clients, Adam. Weak scaling.
+
+  python bench.py --gpus 1 --steps 20 --warmup 3
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+         --master-port 29500 bench.py --gpus 8 --steps 20 --warmup 3
+  python bench.py --impl reference ...      # the unmodified upstream code from baseline/_ref
+
+Rank 0 prints exactly one JSON line on stdout.
+"""
+from __future__ import annotations
+
+import argparse
+import contextlib
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_USERS, HIS_LEN, NPRATIO, TITLE_LEN, NUM_NEWS = 50, 50, 4, 30, 65536
+CLIP, SIGMA = 2.0, 0.05
+
+
+# ---- clocks -----------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.path = tempfile.mktemp(prefix="fedrec_clocks_", suffix=".csv")
+        self.proc = None
+        self.idx = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=open(self.path, "w"),
+                                         stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+        return self
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 9:
+                    continue
+                try:
+                    sm.append(float(f[1])); mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for nm, val in zip(names, f[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(nm)
+            os.remove(self.path)
+        except OSError:
+            pass
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def dist_env():
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+
+
+def synthetic_news_index(np, seed=0):
+    from fedrec_b200.data import make_synthetic_mind
+    return make_synthetic_mind(num_news=NUM_NEWS, num_train=8, num_valid=1, title_len=TITLE_LEN, seed=seed).news_index
+
+
+def make_batches(np, n_batches, rank, seed=0):
+    """Zipf-popular news ids like MIND impressions: [n, B, 1+K] candidates and [n, B, L] histories (int64, host)."""
+    rng = np.random.default_rng(seed + 1000 * rank)
+    p = 1.0 / np.arange(1, NUM_NEWS) ** 1.05
+    p /= p.sum()
+    cand = rng.choice(np.arange(1, NUM_NEWS), size=(n_batches, B_USERS, 1 + NPRATIO), p=p)
+    his = rng.choice(np.arange(1, NUM_NEWS), size=(n_batches, B_USERS, HIS_LEN), p=p)
+    lens = rng.integers(10, HIS_LEN + 1, size=(n_batches, B_USERS))
+    his[np.arange(HIS_LEN)[None, None, :] >= lens[:, :, None]] = 0
+    return cand.astype(np.int64), his.astype(np.int64)
+
+
+def finish(args, impl, rank, world, ms_per_step, e2e_ms, h2d, d2h, launches, clocks, extra_cfg):
+    import torch
+    import torch.distributed as dist
+    if world > 1:
+        t = torch.tensor([ms_per_step, e2e_ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_per_step, e2e_ms = float(t[0]), float(t[1])
+    if rank != 0:
+        return
+    value = world * B_USERS / (ms_per_step * 1e-3)
+    e2e_val = world * B_USERS / (e2e_ms * 1e-3)
+    cfg = {"model": "FedRec joint DistilBERT-base text encoder + user encoder (MHA 20x20 + additive attention)",
+           "mode": "Gradient_Averaging_main: per-round gradient averaging, clip C=%g + LDP sigma=%g" % (CLIP, SIGMA),
+           "global_batch": world * B_USERS, "users_per_client_per_round": B_USERS, "seq_len": TITLE_LEN,
+           "history_len": HIS_LEN, "negatives_per_positive": NPRATIO, "num_news": NUM_NEWS,
+           "parallelism": f"dp{world} (one federated client per GPU)",
+           "l2_policy": "working set per step (>1 GB activations + 130 MB bf16 weights) exceeds the 126 MB L2; "
+                        "a fresh batch of ids every step"}
+    cfg.update(extra_cfg)
+    out = {"metric": "training impressions/sec/box", "value": round(value, 2), "unit": "impressions/s",
+           "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if impl == "ours" else "fp32",
+           "data": "synthetic MIND-shaped impressions (Zipf news popularity), random-init weights",
+           "impl": impl, "config": cfg, "clocks": clocks,
+           "e2e": {"value": round(e2e_val, 2), "unit": "impressions/s", "ms_per_step": round(e2e_ms, 4),
+                   "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+           "gpu_launches": int(launches)}
+    print(json.dumps(out), flush=True)
+
+
+# ---- our framework -------------------------------------------------------------------------------------
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": "ours", "unavailable": "no CUDA device visible"}))
+        return
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run"
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    from fedrec_b200.ops import dispatch as D
+    cfg = FedRecConfig(mode="grad_avg", batch_size=B_USERS, max_his_len=HIS_LEN, npratio=NPRATIO, title_len=TITLE_LEN,
+                       num_news=NUM_NEWS, clip_norm=CLIP, noise_multiplier=SIGMA, synthetic=True, snapshot_path="",
+                       log_dir="", transport=args.transport, num_train=8, num_valid=1, seed=1234)
+    news_index = synthetic_news_index(np)
+    runner = FederatedRunner(cfg, news_index=news_index, nid2index={"<unk>": 0}, train_sam=[], valid_sam=[])
+    dev = runner.device
+    total = args.warmup + args.steps
+    cand_h, his_h = make_batches(np, total, rank)
+    cand_pin = torch.from_numpy(cand_h).to(torch.int32).pin_memory()
+    his_pin = torch.from_numpy(his_h).to(torch.int32).pin_memory()
+    cand_d, his_d = cand_pin.to(dev), his_pin.to(dev)
+
+    def one_step(c, h):
+        loss = runner.step.run(c, h, train=True)
+        runner.grad_agg.allreduce_mean_()
+        runner.model.adam_step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-timed: ids already on the device ----
+    for i in range(args.warmup):
+        one_step(cand_d[i], his_d[i])
+    barrier()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    l0 = D.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.warmup, total):
+        loss = one_step(cand_d[i], his_d[i])
+    e1.record()
+    barrier()
+    launches = D.launch_count() - l0
+    ms = e0.elapsed_time(e1) / args.steps
+    # ---- end to end: pinned host ids in, loss out, every step ----
+    stage_c = torch.empty_like(cand_d[0]); stage_h = torch.empty_like(his_d[0])
+    barrier()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    host_loss = 0.0
+    for i in range(args.warmup, total):
+        stage_c.copy_(cand_pin[i], non_blocking=True)
+        stage_h.copy_(his_pin[i], non_blocking=True)
+        host_loss = float(one_step(stage_c, stage_h).item())
+    t1.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    e2e_ms = t0.elapsed_time(t1) / args.steps
+    h2d = cand_pin[0].numel() * 4 + his_pin[0].numel() * 4
+    finish(args, "ours", rank, world, ms, e2e_ms, h2d, 4, launches, clocks,
+           {"transport": runner.grad_agg.transport, "step_impl": runner.step.impl, "last_loss": host_loss})
+    runner.close()
+
+
+# ---- the upstream code, unmodified, from baseline/_ref ---------------------------------------------------------
+def run_reference(args):
+    ref_dir = os.path.join(ROOT, "baseline", "_ref")
+    if not os.path.isfile(os.path.join(ref_dir, "Gradient_Averaging_main.py")):
+        print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is missing (run baseline/install_ref.sh)"}))
+        return
+    import numpy as np
+    import torch
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": "reference", "unavailable": "no CUDA device visible"}))
+        return
+    import torch.distributed as dist
+    rank, local_rank, world = dist_env()
+    from baseline.harness import load_reference
+    torch.cuda.set_device(local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1"); os.environ.setdefault("MASTER_PORT", "29533")
+    os.environ.setdefault("RANK", "0"); os.environ.setdefault("LOCAL_RANK", "0"); os.environ.setdefault("WORLD_SIZE", "1")
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local_rank))
+    ga = load_reference(ref_dir)                       # the upstream Gradient_Averaging_main module
+    news_index = synthetic_news_index(np)
+    dev = torch.device("cuda", local_rank)
+    torch.manual_seed(1234)
+    with contextlib.redirect_stdout(sys.stderr):
+        model = ga.UserModel(ga.NewsDataset(news_index), news_index, dev).to(dev)
+        optimizer = ga.optim.SGD(model.parameters(), lr=0.00005)
+        trainer = ga.Trainer(model, [], optimizer, save_every=10 ** 9, snapshot_path="/nonexistent/snapshot.pt")
+    total = args.warmup + args.steps
+    cand_h, his_h = make_batches(np, total, rank)
+    label = torch.zeros(B_USERS, dtype=torch.long, device=dev)   # upstream leaves labels on the CPU
+
+    def one_step(i):
+        dl = [(torch.from_numpy(cand_h[i]), torch.from_numpy(his_h[i]), label)]
+        with contextlib.redirect_stdout(sys.stderr):
+            return ga.train_on_step(trainer.model, dl, optimizer)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        one_step(i)
+    barrier()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.warmup, total):
+        one_step(i)
+    e1.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    ms = e0.elapsed_time(e1) / args.steps
+    n_rows = B_USERS * (1 + NPRATIO + HIS_LEN)
+    h2d = n_rows * 2 * TITLE_LEN * 8 * 2 + n_rows * 400 * 4 * 2      # token rows (two passes) + vectors and grads back up
+    d2h = n_rows * 400 * 4 * 2 + 4                                   # news vectors and their grads + loss
+    finish(args, "reference", rank, world, ms, ms, h2d, d2h, 0, clocks,
+           {"note": "unmodified upstream sources (baseline/_ref) run through Gradient_Averaging_main.Trainer/"
+                    "train_on_step with DDP over NCCL; its public API takes host ids and returns a host loss, so the "
+                    "device-timed and end-to-end regions coincide; upstream has no clip/noise in this mode"})
+    dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--transport", default="nvlink", choices=["nvlink", "collective"])
+    args = ap.parse_args()
+    if args.steps is None:
+        args.steps = 20 if args.impl == "ours" else 5
+    args.warmup = max(args.warmup, 3)
+    if args.gpus > 1 and "RANK" not in os.environ:
+        # convenience: re-launch under torch.distributed.run
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    (run_ours if args.impl == "ours" else run_reference)(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,326 @@
+// Memory-bound pieces of the DistilBERT trunk and of the text head:
+//   N9  embedding gather (word + position) + LayerNorm                     (HF DistilBERT Embeddings)
+//   -   LayerNorm over rows that already hold x + residual (the GEMM epilogue added it)
+//   N8  12-head self-attention over one title (T <= 64 tokens), key-padding mask
+//   N10 additive-attention pooling of the text head: alpha = exp(e·w2 + b2) / (sum + 1e-8), sum alpha*h
+// Reference call sites: encoder.py:27 (DistilBertModel), encoder.py:28 → attention.py:14-26.
+// All activations are bf16, statistics and accumulation fp32. Row counts may come from device
+// memory (count_dev * rows_per_item) so a captured graph follows the per-step de-dup count.
+#include "common.cuh"
+
+namespace fr {
+
+constexpr int kHid = 768;            // DistilBERT width; one warp owns a row: 24 elements per lane
+constexpr int kPerLane = kHid / 32;  // 24 = 3 x 8 bf16 (16-byte vectors)
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float* v) {
+  const uint4 q = *reinterpret_cast<const uint4*>(p);
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = __bfloat1622float2(h[i]);
+    v[2 * i] = f.x;
+    v[2 * i + 1] = f.y;
+  }
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float* v) {
+  uint4 q;
+  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+  *reinterpret_cast<uint4*>(p) = q;
+}
+
+// x[24] per lane → normalised in place. Two-pass (mean, then centred variance) in registers.
+__device__ __forceinline__ void warp_layernorm(float* x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                               int lane, float eps) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kPerLane; ++i) s += x[i];
+  const float mean = warp_sum(s) * (1.f / kHid);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < kPerLane; ++i) {
+    const float d = x[i] - mean;
+    q += d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / kHid) + eps);
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const int col = c * 256 + lane * 8;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) x[c * 8 + i] = (x[c * 8 + i] - mean) * rstd * gamma[col + i] + beta[col + i];
+  }
+}
+
+// out[(n*T + t), :] = LN(word[tokens[items[n], t]] + pos[t])
+__global__ void __launch_bounds__(256) embed_ln_kernel(const int* __restrict__ tokens, const int* __restrict__ items,
+                                                       const int* __restrict__ count_dev, int n_items, int T,
+                                                       const __nv_bfloat16* __restrict__ word,
+                                                       const __nv_bfloat16* __restrict__ pos,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       __nv_bfloat16* __restrict__ out, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
+  const int rows = n_eff * T;
+  for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += gridDim.x * (blockDim.x >> 5)) {
+    const int n = row / T, t = row - n * T;
+    const int item = items ? items[n] : n;
+    const int tok = tokens[(size_t)item * T + t];
+    float x[kPerLane], p[8];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const int col = c * 256 + lane * 8;
+      load8(word + (size_t)tok * kHid + col, x + c * 8);
+      load8(pos + (size_t)t * kHid + col, p);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) x[c * 8 + i] += p[i];
+    }
+    warp_layernorm(x, gamma, beta, lane, eps);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) store8(out + (size_t)row * kHid + c * 256 + lane * 8, x + c * 8);
+  }
+}
+
+__global__ void __launch_bounds__(256) layernorm_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                        int rows_max, const int* __restrict__ count_dev, int rows_per_item,
+                                                        float eps) {
+  const int lane = threadIdx.x & 31;
+  int rows = rows_max;
+  if (count_dev) rows = min(rows_max, *count_dev * rows_per_item);
+  for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += gridDim.x * (blockDim.x >> 5)) {
+    float x[kPerLane];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) load8(in + (size_t)row * kHid + c * 256 + lane * 8, x + c * 8);
+    warp_layernorm(x, gamma, beta, lane, eps);
+#pragma unroll
+    for (int c = 0; c < 3; ++c) store8(out + (size_t)row * kHid + c * 256 + lane * 8, x + c * 8);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Self-attention over one title. qkv [rows, 3*768] = (q | k | v), heads of 64. One warp per
+// (item, head): K and V of that head staged in shared memory, each lane owns query rows
+// lane and lane+32 and runs an online soft-max over the keys. q is scaled by 1/8 (HF scales q).
+// Masked keys get -inf (HF: masked_fill(finfo.min)); an item whose mask is all zero attends
+// uniformly, exactly as soft-max over a constant row does.
+// ---------------------------------------------------------------------------------------------
+constexpr int kHeadDim = 64;
+constexpr int kMaxT = 64;
+constexpr int kAttnWarps = 2;
+
+__global__ void __launch_bounds__(kAttnWarps * 32) bert_attention_kernel(
+    const __nv_bfloat16* __restrict__ qkv, const int* __restrict__ mask_table, const int* __restrict__ items,
+    const int* __restrict__ count_dev, int n_items, int T, int heads, __nv_bfloat16* __restrict__ out) {
+  __shared__ __align__(16) __nv_bfloat16 sK[kAttnWarps][kMaxT][kHeadDim];
+  __shared__ __align__(16) __nv_bfloat16 sV[kAttnWarps][kMaxT][kHeadDim];
+  __shared__ float sBias[kAttnWarps][kMaxT];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
+  const int total = n_eff * heads;
+  const int ld = 3 * heads * kHeadDim;
+  for (int job = blockIdx.x * kAttnWarps + w; job < total; job += gridDim.x * kAttnWarps) {
+    const int n = job / heads, h = job - n * heads;
+    const int item = items ? items[n] : n;
+    const size_t row0 = (size_t)n * T;
+    // stage K, V: T rows x 64 bf16 = T x 8 uint4
+    for (int i = lane; i < T * 8; i += 32) {
+      const int r = i >> 3, c = i & 7;
+      const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * kHeadDim + c * 8;
+      *reinterpret_cast<uint4*>(&sK[w][r][c * 8]) = *reinterpret_cast<const uint4*>(base + heads * kHeadDim);
+      *reinterpret_cast<uint4*>(&sV[w][r][c * 8]) = *reinterpret_cast<const uint4*>(base + 2 * heads * kHeadDim);
+    }
+    bool any = false;
+    for (int j = lane; j < T; j += 32) {
+      const int mk = mask_table ? mask_table[(size_t)item * T + j] : 1;
+      sBias[w][j] = mk ? 0.f : -INFINITY;
+      any |= (mk != 0);
+    }
+    any = __any_sync(0xffffffffu, any);
+    __syncwarp();
+    for (int qr = lane; qr < T; qr += 32) {
+      float q[kHeadDim];
+      const __nv_bfloat16* qp = qkv + (row0 + qr) * ld + h * kHeadDim;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) load8(qp + c * 8, q + c * 8);
+#pragma unroll
+      for (int d = 0; d < kHeadDim; ++d) q[d] *= 0.125f;
+      float m = -INFINITY, l = 0.f;
+      float acc[kHeadDim];
+#pragma unroll
+      for (int d = 0; d < kHeadDim; ++d) acc[d] = 0.f;
+      for (int j = 0; j < T; ++j) {
+        const float bias = any ? sBias[w][j] : 0.f;
+        if (bias == -INFINITY) continue;            // uniform across the warp (same item)
+        float s = 0.f;
+        const __nv_bfloat162* kp = reinterpret_cast<const __nv_bfloat162*>(&sK[w][j][0]);
+#pragma unroll
+        for (int d = 0; d < kHeadDim / 2; ++d) {
+          const float2 kf = __bfloat1622float2(kp[d]);
+          s = fmaf(q[2 * d], kf.x, s);
+          s = fmaf(q[2 * d + 1], kf.y, s);
+        }
+        const float m_new = fmaxf(m, s);
+        const float corr = __expf(m - m_new);
+        const float p = __expf(s - m_new);
+        l = l * corr + p;
+        const __nv_bfloat162* vp = reinterpret_cast<const __nv_bfloat162*>(&sV[w][j][0]);
+#pragma unroll
+        for (int d = 0; d < kHeadDim / 2; ++d) {
+          const float2 vf = __bfloat1622float2(vp[d]);
+          acc[2 * d] = fmaf(p, vf.x, acc[2 * d] * corr);
+          acc[2 * d + 1] = fmaf(p, vf.y, acc[2 * d + 1] * corr);
+        }
+        m = m_new;
+      }
+      const float inv = 1.f / l;
+#pragma unroll
+      for (int d = 0; d < kHeadDim; ++d) acc[d] *= inv;
+      __nv_bfloat16* op = out + (row0 + qr) * (size_t)(heads * kHeadDim) + h * kHeadDim;
+#pragma unroll
+      for (int c = 0; c < 8; ++c) store8(op + c * 8, acc + c * 8);
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Text-head pooling (forward). e = tanh(h·W1^T + b1) comes from the GEMM (tanh epilogue), bf16 [rows, Hq].
+// One warp per item: a_t = e_t·w2 + b2; alpha = exp(a - m) / (sum exp(a - m) + 1e-8 exp(-m));
+// pooled = sum_t alpha_t h_t  (bf16 [n, 768]); alpha is kept (fp32 [n, T]) for the backward.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) text_pool_kernel(const __nv_bfloat16* __restrict__ hidden,
+                                                        const __nv_bfloat16* __restrict__ e, const float* __restrict__ w2,
+                                                        const float* __restrict__ b2, const int* __restrict__ mask_table,
+                                                        const int* __restrict__ items, const int* __restrict__ count_dev,
+                                                        int n_items, int T, int Hq, __nv_bfloat16* __restrict__ pooled,
+                                                        float* __restrict__ alpha_out) {
+  __shared__ float sA[4][kMaxT];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
+  for (int n = blockIdx.x * 4 + w; n < n_eff; n += gridDim.x * 4) {
+    const size_t row0 = (size_t)n * T;
+    const int item = items ? items[n] : n;
+    float mx = -INFINITY;
+    for (int t = 0; t < T; ++t) {
+      float s = 0.f;
+      for (int c = lane * 2; c < Hq; c += 64) {
+        const float2 ef = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(e + (row0 + t) * Hq + c));
+        s = fmaf(ef.x, w2[c], s);
+        s = fmaf(ef.y, w2[c + 1], s);
+      }
+      s = warp_sum(s) + b2[0];
+      if (lane == 0) sA[w][t] = s;
+      mx = fmaxf(mx, s);
+    }
+    __syncwarp();
+    float z = 0.f;
+    for (int t = lane; t < T; t += 32) {
+      const float mk = (mask_table && mask_table[(size_t)item * T + t] == 0) ? 0.f : 1.f;
+      const float ex = __expf(sA[w][t] - mx) * mk;
+      sA[w][t] = ex;
+      z += ex;
+    }
+    z = warp_sum(z) + 1e-8f * __expf(-mx);
+    __syncwarp();
+    const float invz = 1.f / z;
+    float acc[kPerLane];
+#pragma unroll
+    for (int i = 0; i < kPerLane; ++i) acc[i] = 0.f;
+    for (int t = 0; t < T; ++t) {
+      const float a = sA[w][t] * invz;
+      if (lane == 0 && alpha_out) alpha_out[row0 + t] = a;
+      float hv[8];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        load8(hidden + (row0 + t) * kHid + c * 256 + lane * 8, hv);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[c * 8 + i] = fmaf(a, hv[i], acc[c * 8 + i]);
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) store8(pooled + (size_t)n * kHid + c * 256 + lane * 8, acc + c * 8);
+    __syncwarp();
+  }
+}
+
+// fp32 → bf16 cast of a contiguous buffer (weight packing, activations entering a GEMM)
+__global__ void __launch_bounds__(256) cast_bf16_kernel(const float4* __restrict__ in, uint2* __restrict__ out, size_t n4) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    const float4 v = in[i];
+    uint2 q;
+    *reinterpret_cast<__nv_bfloat162*>(&q.x) = __floats2bfloat162_rn(v.x, v.y);
+    *reinterpret_cast<__nv_bfloat162*>(&q.y) = __floats2bfloat162_rn(v.z, v.w);
+    out[i] = q;
+  }
+}
+
+}  // namespace fr
+
+using namespace fr;
+
+static inline int grid_for(long long warps_needed, int warps_per_block, int cap_blocks) {
+  long long b = (warps_needed + warps_per_block - 1) / warps_per_block;
+  if (b > cap_blocks) b = cap_blocks;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+FR_API int fr_bert_embed_ln(const int* tokens, const int* items, const int* count_dev, int n_items, int T,
+                            const void* word, const void* pos, const float* gamma, const float* beta, void* out,
+                            float eps, int hidden, void* stream) {
+  FR_REQUIRE(hidden == kHid, "fr_bert_embed_ln: hidden=%d (only %d is built)", hidden, kHid);
+  if (n_items == 0) return 0;
+  embed_ln_kernel<<<grid_for((long long)n_items * T, 8, kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(
+      tokens, items, count_dev, n_items, T, (const __nv_bfloat16*)word, (const __nv_bfloat16*)pos, gamma, beta,
+      (__nv_bfloat16*)out, eps);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_layernorm_bf16(const void* in, void* out, const float* gamma, const float* beta, int rows,
+                             const int* count_dev, int rows_per_item, float eps, int hidden, void* stream) {
+  FR_REQUIRE(hidden == kHid, "fr_layernorm_bf16: hidden=%d (only %d is built)", hidden, kHid);
+  if (rows == 0) return 0;
+  layernorm_kernel<<<grid_for(rows, 8, kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)in, (__nv_bfloat16*)out, gamma, beta, rows, count_dev, rows_per_item, eps);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_bert_attention(const void* qkv, const int* mask_table, const int* items, const int* count_dev,
+                             int n_items, int T, int heads, int head_dim, void* out, void* stream) {
+  FR_REQUIRE(head_dim == kHeadDim, "fr_bert_attention: head_dim=%d (only %d is built)", head_dim, kHeadDim);
+  FR_REQUIRE(T >= 1 && T <= kMaxT, "fr_bert_attention: T=%d must be in [1,%d]", T, kMaxT);
+  if (n_items == 0) return 0;
+  bert_attention_kernel<<<grid_for((long long)n_items * heads, kAttnWarps, kNumSMs * 16), kAttnWarps * 32, 0,
+                          (cudaStream_t)stream>>>((const __nv_bfloat16*)qkv, mask_table, items, count_dev, n_items, T,
+                                                  heads, (__nv_bfloat16*)out);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_text_pool(const void* hidden, const void* e, const float* w2, const float* b2, const int* mask_table,
+                        const int* items, const int* count_dev, int n_items, int T, int Hq, int hidden_dim,
+                        void* pooled, float* alpha_out, void* stream) {
+  FR_REQUIRE(hidden_dim == kHid, "fr_text_pool: hidden=%d (only %d is built)", hidden_dim, kHid);
+  FR_REQUIRE(T >= 1 && T <= kMaxT && Hq % 2 == 0, "fr_text_pool: T=%d Hq=%d", T, Hq);
+  if (n_items == 0) return 0;
+  text_pool_kernel<<<grid_for(n_items, 4, kNumSMs * 8), 128, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)hidden, (const __nv_bfloat16*)e, w2, b2, mask_table, items, count_dev, n_items, T, Hq,
+      (__nv_bfloat16*)pooled, alpha_out);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream) {
+  FR_REQUIRE(n % 4 == 0, "fr_cast_f32_to_bf16: n=%lld must be a multiple of 4", n);
+  if (n == 0) return 0;
+  const size_t n4 = (size_t)n / 4;
+  int blocks = (int)((n4 + 255) / 256);
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  cast_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const float4*)in, (uint2*)out, n4);
+  FR_LAUNCH_CHECK();
+  return 0;
+}

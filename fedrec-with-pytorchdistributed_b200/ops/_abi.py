@@ -20,6 +20,12 @@ SIGNATURES = {
     "fr_dedup": (I, [P, I, I, P, P, P, P, P]),
     "fr_sq_norm": (I, [P, LL, P, P]),
     "fr_clip_noise": (I, [P, LL, P, F, F, c_ulonglong, c_uint, P]),
+    # bert_ops.cu
+    "fr_bert_embed_ln": (I, [P, P, P, I, I, P, P, P, P, P, F, I, P]),
+    "fr_layernorm_bf16": (I, [P, P, P, P, I, P, I, F, I, P]),
+    "fr_bert_attention": (I, [P, P, P, P, I, I, I, I, P, P]),
+    "fr_text_pool": (I, [P, P, P, P, P, P, P, I, I, I, I, P, P, P]),
+    "fr_cast_f32_to_bf16": (I, [P, P, LL, P]),
     # gemm_sm100.cu
     "fr_gemm_bf16": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, I, P]),
 }

@@ -170,3 +170,53 @@ def linear_bf16(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] =
                            stream_ptr(x.device)), "fr_gemm_bf16")
     count_launches(1)
     return out
+
+
+# ---- DistilBERT trunk / text head pieces (CUDA only; the CPU path is the nn.Module code) -------------
+def bert_embed_ln(tokens, items, count, n_items, T, word, pos, gamma, beta, out, eps=1e-12):
+    lib = require_native()
+    check(lib.fr_bert_embed_ln(tokens.data_ptr(), _p(items), _p(count), n_items, T, word.data_ptr(), pos.data_ptr(),
+                               gamma.data_ptr(), beta.data_ptr(), out.data_ptr(), eps, word.shape[1],
+                               stream_ptr(out.device)), "fr_bert_embed_ln")
+    count_launches(1)
+    return out
+
+
+def layernorm_bf16(x, gamma, beta, out=None, count=None, rows_per_item=1, eps=1e-12):
+    lib = require_native()
+    out = torch.empty_like(x) if out is None else out
+    check(lib.fr_layernorm_bf16(x.data_ptr(), out.data_ptr(), gamma.data_ptr(), beta.data_ptr(), x.shape[0], _p(count),
+                                rows_per_item, eps, x.shape[1], stream_ptr(x.device)), "fr_layernorm_bf16")
+    count_launches(1)
+    return out
+
+
+def bert_attention(qkv, mask_table, items, count, n_items, T, heads, out):
+    lib = require_native()
+    check(lib.fr_bert_attention(qkv.data_ptr(), _p(mask_table), _p(items), _p(count), n_items, T, heads,
+                                qkv.shape[1] // (3 * heads), out.data_ptr(), stream_ptr(out.device)), "fr_bert_attention")
+    count_launches(1)
+    return out
+
+
+def text_pool(hidden, e, w2, b2, mask_table, items, count, n_items, T, pooled, alpha):
+    lib = require_native()
+    check(lib.fr_text_pool(hidden.data_ptr(), e.data_ptr(), w2.data_ptr(), b2.data_ptr(), _p(mask_table), _p(items),
+                           _p(count), n_items, T, e.shape[1], hidden.shape[1], pooled.data_ptr(), _p(alpha),
+                           stream_ptr(hidden.device)), "fr_text_pool")
+    count_launches(1)
+    return pooled
+
+
+def cast_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """fp32 → bf16 copy with our kernel (weight packing)."""
+    lib = require_native()
+    x = x.contiguous()
+    out = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16) if out is None else out
+    n = x.numel()
+    if n % 4 != 0:
+        out.copy_(x)
+        return out
+    check(lib.fr_cast_f32_to_bf16(x.data_ptr(), out.data_ptr(), n, stream_ptr(x.device)), "fr_cast_f32_to_bf16")
+    count_launches(1)
+    return out

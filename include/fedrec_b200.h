@@ -47,6 +47,32 @@ int fr_sq_norm(const float* x, long long n, float* out, void* stream);
 int fr_clip_noise(float* x, long long n, const float* sq, float clip, float noise_std, unsigned long long seed,
                   unsigned stream_id, void* stream);
 
+/* ---- DistilBERT trunk / text head, memory-bound parts (csrc/bert_ops.cu) ----------------------------- */
+
+/* out[(n*T+t),:] = LayerNorm(word[tokens[items[n],t]] + pos[t]) in bf16, n < min(n_items, *count_dev).
+ * Replaces the HF Embeddings module reached from encoder.py:27. hidden must be 768. */
+int fr_bert_embed_ln(const int* tokens, const int* items, const int* count_dev, int n_items, int T, const void* word,
+                     const void* pos, const float* gamma, const float* beta, void* out, float eps, int hidden,
+                     void* stream);
+
+/* Row LayerNorm, bf16 in/out (the residual was already added by the GEMM epilogue). rows limited to
+ * *count_dev * rows_per_item when count_dev != NULL. Replaces sa_layer_norm / output_layer_norm. */
+int fr_layernorm_bf16(const void* in, void* out, const float* gamma, const float* beta, int rows, const int* count_dev,
+                      int rows_per_item, float eps, int hidden, void* stream);
+
+/* Multi-head self-attention over one title: qkv bf16 [n*T, 3*heads*64] -> out bf16 [n*T, heads*64], q scaled by
+ * 1/8, key-padding mask from mask_table[items[n], :]. Replaces HF MultiHeadSelfAttention (encoder.py:27). */
+int fr_bert_attention(const void* qkv, const int* mask_table, const int* items, const int* count_dev, int n_items,
+                      int T, int heads, int head_dim, void* out, void* stream);
+
+/* Text-head additive pooling: alpha = exp(e.w2+b2)/(sum+1e-8) over T, pooled = sum alpha*h. e comes from the GEMM
+ * with the tanh epilogue. Replaces attention.py:18-25 as called from encoder.py:28. */
+int fr_text_pool(const void* hidden, const void* e, const float* w2, const float* b2, const int* mask_table,
+                 const int* items, const int* count_dev, int n_items, int T, int Hq, int hidden_dim, void* pooled,
+                 float* alpha_out, void* stream);
+
+int fr_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
+
 /* ---- tcgen05 GEMM (csrc/gemm_sm100.cu) ------------------------------------------------------------ */
 
 /* out = epi(A[M,K]·W[N,K]^T + bias); A, W bf16 K-major; out bf16 or fp32. epi: 0 bias, 1 bias+GELU(erf),

@@ -1,0 +1,34 @@
+"""The native library builds for sm_100a on a CPU-only box and contains Blackwell tensor-core code."""
+import os
+import shutil
+import subprocess
+
+import pytest
+
+from fedrec_b200.ops import native
+from fedrec_b200.ops._abi import SIGNATURES
+
+
+def test_library_builds_and_binds():
+    path = native.build()
+    assert os.path.exists(path)
+    lib = native.lib()
+    assert lib.fr_version() >= 100
+    for name in SIGNATURES:
+        assert hasattr(lib, name), name
+
+
+def test_header_declares_every_bound_symbol():
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "fedrec_b200.h")).read()
+    for name in SIGNATURES:
+        assert name + "(" in hdr, f"{name} missing from include/fedrec_b200.h"
+
+
+@pytest.mark.skipif(shutil.which("cuobjdump") is None, reason="cuobjdump not installed")
+def test_sass_has_tcgen05_and_tma():
+    sass = subprocess.run(["cuobjdump", "-sass", native.build()], capture_output=True, text=True).stdout
+    assert "UTCHMMA" in sass            # tcgen05.mma kind::f16
+    assert "UTMALDG" in sass            # TMA tensor load
+    assert "LDTM" in sass               # tcgen05.ld
+    assert "HGMMA" not in sass and "sm_100a" in sass

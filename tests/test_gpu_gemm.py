@@ -1,0 +1,72 @@
+"""tcgen05 GEMM vs an fp32 PyTorch reference of the same op."""
+import os
+
+import pytest
+import torch
+
+from fedrec_b200 import ops
+from fedrec_b200.ops import dispatch as D, reference as ref
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _check(M, N, K, epi="bias", block_n=0, out_dtype=torch.bfloat16, m_dev=None, m_scale=1, seed=0):
+    ops.require_native()
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    x = (torch.randn(M, K, device=DEV, generator=g) * 0.5).bfloat16()
+    w = (torch.randn(N, K, device=DEV, generator=g) * (1.0 / K ** 0.5)).bfloat16()
+    b = torch.randn(N, device=DEV, generator=g) * 0.1
+    r = (torch.randn(M, N, device=DEV, generator=g)).bfloat16() if epi == "resid" else None
+    out = torch.full((M, N), 7.0, device=DEV, dtype=out_dtype)
+    cnt = torch.tensor([m_dev], device=DEV, dtype=torch.int32) if m_dev is not None else None
+    D.linear_bf16(x, w, b, epi, resid=r, out=out, block_n=block_n, m_dev=cnt, m_scale=m_scale)
+    torch.cuda.synchronize()
+    want = ref.linear(x, w, b, {"bias": 0, "gelu": 1, "resid": 2, "tanh": 3}[epi], r)
+    rows = M if m_dev is None else min(M, m_dev * m_scale)
+    got = out.float()
+    err = (got[:rows] - want[:rows]).abs()
+    tol = 2e-2 if out_dtype == torch.bfloat16 else 2e-3
+    if float(err.max()) > tol * max(1.0, float(want.abs().max())):
+        os.makedirs("gpurun_out", exist_ok=True)
+        bad = (err > tol).nonzero()
+        with open("gpurun_out/gemm_diag.txt", "a") as f:
+            f.write(f"M={M} N={N} K={K} epi={epi} bn={block_n} max_err={float(err.max())} n_bad={bad.shape[0]}\n")
+            f.write(f" first bad idx: {bad[:16].tolist()}\n got {got[:4, :8].tolist()}\n want {want[:4, :8].tolist()}\n")
+            f.write(f" bad rows hist(mod 128): {torch.bincount(bad[:, 0] % 128, minlength=128).tolist()}\n")
+            f.write(f" bad cols hist(mod 64): {torch.bincount(bad[:, 1] % 64, minlength=64).tolist()}\n")
+    torch.testing.assert_close(got[:rows], want[:rows], atol=tol, rtol=tol)
+    if rows < M:
+        assert (got[rows + 127:] == 7.0).all()                     # rows past the dynamic M are untouched
+
+
+@pytest.mark.parametrize("block_n", [64, 128, 256])
+def test_square_tiles(block_n):
+    _check(256, 256, 128, block_n=block_n)
+
+
+def test_single_k_block():
+    _check(128, 64, 64, block_n=64)
+
+
+@pytest.mark.parametrize("M,N,K,epi", [
+    (300, 768, 768, "bias"), (1000, 2304, 768, "bias"), (513, 3072, 768, "gelu"), (257, 768, 3072, "resid"),
+    (2500, 1200, 400, "bias"), (2500, 200, 400, "tanh"), (82500, 768, 768, "bias"), (4099, 384, 768, "tanh"),
+])
+def test_model_shapes(M, N, K, epi):
+    _check(M, N, K, epi)
+
+
+def test_fp32_output_small_m():
+    _check(130, 400, 768, out_dtype=torch.float32)
+    _check(2750, 400, 768, out_dtype=torch.float32)
+
+
+def test_dynamic_m_from_device():
+    _check(3000, 768, 768, m_dev=37, m_scale=30)
+    _check(3000, 768, 768, m_dev=0, m_scale=30)
+    _check(3000, 768, 768, m_dev=1000, m_scale=30)                 # larger than M: clamps
+
+
+def test_many_waves_persistent():
+    _check(148 * 128 * 3 + 5, 256, 192, block_n=256)
