@@ -245,6 +245,82 @@ __global__ void __launch_bounds__(128) text_pool_kernel(const __nv_bfloat16* __r
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Text-head pooling backward (the "injected gradient" pass of model.py:72-90, head only: the trunk is frozen).
+//   d_alpha_t = d_pooled · h_t ;  d_a_t = alpha_t (d_alpha_t - sum_s alpha_s d_alpha_s)
+//   d_b2 += sum d_a ; d_w2 += sum_t d_a_t e_t ; d_pre[t] = d_a_t * w2 * (1 - e_t^2)      (bf16, GEMM operand)
+// One warp per item, grid-stride; per-block partial sums for d_w2 so atomics stay rare. Rows of d_pre in
+// [count*T, round_up(count*T, 64)) are zeroed: the weight-gradient GEMM reduces over whole 64-row blocks.
+// ---------------------------------------------------------------------------------------------
+constexpr int kMaxHq = 512;
+__global__ void __launch_bounds__(128) text_pool_bwd_kernel(const __nv_bfloat16* __restrict__ hidden,
+                                                            const __nv_bfloat16* __restrict__ e,
+                                                            const float* __restrict__ alpha,
+                                                            const __nv_bfloat16* __restrict__ d_pooled,
+                                                            const float* __restrict__ w2, const int* __restrict__ count_dev,
+                                                            int n_items, int T, int Hq, __nv_bfloat16* __restrict__ d_pre,
+                                                            float* __restrict__ d_w2, float* __restrict__ d_b2) {
+  __shared__ float sDa[4][kMaxT];
+  __shared__ float sW2[kMaxHq];
+  __shared__ float sAcc[kMaxHq];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
+  for (int c = threadIdx.x; c < Hq; c += 128) { sW2[c] = w2[c]; sAcc[c] = 0.f; }
+  if (blockIdx.x == 0) {                       // zero the tail rows up to the next 64-row boundary
+    const int r0 = n_eff * T, r1 = min(n_items * T, (r0 + 63) / 64 * 64);
+    for (int i = threadIdx.x; i < (r1 - r0) * Hq; i += 128) d_pre[(size_t)r0 * Hq + i] = __float2bfloat16(0.f);
+  }
+  __syncthreads();
+  float db2 = 0.f;
+  float wacc[kMaxHq / 32];
+#pragma unroll
+  for (int i = 0; i < kMaxHq / 32; ++i) wacc[i] = 0.f;
+  for (int n = blockIdx.x * 4 + w; n < n_eff; n += gridDim.x * 4) {
+    const size_t row0 = (size_t)n * T;
+    float dp[kPerLane];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) load8(d_pooled + (size_t)n * kHid + c * 256 + lane * 8, dp + c * 8);
+    float dot = 0.f;
+    for (int t = 0; t < T; ++t) {
+      float hv[8], s = 0.f;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        load8(hidden + (row0 + t) * kHid + c * 256 + lane * 8, hv);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s = fmaf(dp[c * 8 + i], hv[i], s);
+      }
+      s = warp_sum(s);
+      const float al = alpha[row0 + t];
+      if (lane == 0) sDa[w][t] = s;
+      dot = fmaf(al, s, dot);
+    }
+    __syncwarp();
+    for (int t = 0; t < T; ++t) {
+      const float da = alpha[row0 + t] * (sDa[w][t] - dot);
+      if (lane == 0) db2 += da;
+#pragma unroll
+      for (int i = 0; i < kMaxHq / 32; ++i) {
+        const int c = lane + 32 * i;
+        if (c < Hq) {
+          const float ev = __bfloat162float(e[(row0 + t) * Hq + c]);
+          wacc[i] = fmaf(da, ev, wacc[i]);
+          d_pre[(row0 + t) * Hq + c] = __float2bfloat16(da * sW2[c] * (1.f - ev * ev));
+        }
+      }
+    }
+    __syncwarp();
+  }
+#pragma unroll
+  for (int i = 0; i < kMaxHq / 32; ++i) {
+    const int c = lane + 32 * i;
+    if (c < Hq) atomicAdd(&sAcc[c], wacc[i]);
+  }
+  if (lane == 0 && db2 != 0.f) atomicAdd(d_b2, db2);
+  __syncthreads();
+  for (int c = threadIdx.x; c < Hq; c += 128)
+    if (sAcc[c] != 0.f) atomicAdd(d_w2 + c, sAcc[c]);
+}
+
 // fp32 → bf16 cast of a contiguous buffer (weight packing, activations entering a GEMM)
 __global__ void __launch_bounds__(256) cast_bf16_kernel(const float4* __restrict__ in, uint2* __restrict__ out, size_t n4) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
@@ -310,6 +386,19 @@ FR_API int fr_text_pool(const void* hidden, const void* e, const float* w2, cons
   text_pool_kernel<<<grid_for(n_items, 4, kNumSMs * 8), 128, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)hidden, (const __nv_bfloat16*)e, w2, b2, mask_table, items, count_dev, n_items, T, Hq,
       (__nv_bfloat16*)pooled, alpha_out);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_text_pool_bwd(const void* hidden, const void* e, const float* alpha, const void* d_pooled, const float* w2,
+                            const int* count_dev, int n_items, int T, int Hq, int hidden_dim, void* d_pre, float* d_w2,
+                            float* d_b2, void* stream) {
+  FR_REQUIRE(hidden_dim == kHid, "fr_text_pool_bwd: hidden=%d (only %d is built)", hidden_dim, kHid);
+  FR_REQUIRE(T >= 1 && T <= kMaxT && Hq >= 1 && Hq <= kMaxHq, "fr_text_pool_bwd: T=%d Hq=%d", T, Hq);
+  if (n_items == 0) return 0;
+  text_pool_bwd_kernel<<<grid_for(n_items, 4, kNumSMs * 2), 128, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)hidden, (const __nv_bfloat16*)e, alpha, (const __nv_bfloat16*)d_pooled, w2, count_dev, n_items, T,
+      Hq, (__nv_bfloat16*)d_pre, d_w2, d_b2);
   FR_LAUNCH_CHECK();
   return 0;
 }

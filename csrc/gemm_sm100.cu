@@ -289,14 +289,20 @@ static PFN_encodeTiled get_encode() {
   return fn;
 }
 
-// [rows, cols] bf16 row-major with leading dimension ld (elements); box = box_rows x 64 cols, 128B swizzle.
+// [rows, cols] bf16 row-major with leading dimension ld (elements); box = box_rows x box_cols, 128B swizzle.
+int make_tmap_bf16_2d_box(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows,
+                          int box_cols);
 int make_tmap_bf16_2d(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows) {
+  return make_tmap_bf16_2d_box(out, base, rows, cols, ld, box_rows, BK);
+}
+int make_tmap_bf16_2d_box(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows,
+                          int box_cols) {
   PFN_encodeTiled enc = get_encode();
   FR_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
   FR_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * 2) % 16 == 0, "TMA operand must be 16-byte aligned with ld %% 8 == 0 (ld=%lld)", ld);
   cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,

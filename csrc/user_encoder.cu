@@ -1,0 +1,546 @@
+// N4 / N5 / N6 / N11: the user encoder and the loss, forward and backward, around the tcgen05 GEMMs.
+//
+// Reference math (encoder.py:49-56, attention.py:14-26,37-45,69-81, model.py:121-126):
+//   x   = dropout(his_vec, 0.2)                       his_vec = news_vecs[his ids]
+//   QKV = x Wqkv^T + b                                (GEMM, gemm_sm100.cu)
+//   A   = exp(QK^T/sqrt(dk)) * mask / (rowsum + 1e-8) ; ctx = merge_heads(A V)          → ue_mha_fwd
+//   e   = tanh(ctx W1^T + b1)                         (GEMM with tanh epilogue)
+//   a   = exp(e w2 + b2) * mask / (sum_L + 1e-8) ; u = sum_L a ctx
+//   s   = sigmoid(cand · u) ; loss = mean_B CE(s, 0)                                    → ue_pool_score
+// The backward kernels emit the operands of the weight-gradient GEMMs (gemm_grad_sm100.cu) and scatter
+// the gradients of the news vectors straight into d_news[unique row] (the reference's Python dict
+// segment-sum, main.py:20-42), optionally with the reference's LDP noise (client.py:87-89).
+//
+// Kernels here are latency-bound glue between GEMMs (≈3 GFLOP per 50-user round in total): one warp per
+// (user, head) or per user, fp32 math, bf16 tensors where a GEMM consumes them.
+#include "common.cuh"
+
+namespace fr {
+
+constexpr int kMaxL = 64;       // history length limit (reference: 50)
+constexpr int kFwdWarps = 2;    // (user, head) jobs per block, forward
+constexpr int kBwdWarps = 1;    // backward keeps q, k, v, dctx of one job in shared memory
+
+__device__ __forceinline__ void red_add_f32x4(float* addr, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// Inverted-dropout multiplier for element (row, 4*q4..4*q4+3): four keep decisions from one Philox call.
+__device__ __forceinline__ float4 dropout_mult4(const Philox& rng, uint64_t idx4, float p, float inv_keep) {
+  uint32_t r[4];
+  rng(idx4, 0xD0u, r);
+  const uint32_t thr = (uint32_t)(p * 4294967296.0);
+  return make_float4(r[0] >= thr ? inv_keep : 0.f, r[1] >= thr ? inv_keep : 0.f, r[2] >= thr ? inv_keep : 0.f,
+                     r[3] >= thr ? inv_keep : 0.f);
+}
+
+// X[b*L + l, :] = bf16( dropout( news_vecs[inv_his[b*L + l], :] ) )
+__global__ void __launch_bounds__(256) ue_gather_dropout_kernel(const float* __restrict__ news_vecs, const int* __restrict__ inv_his,
+                                                                __nv_bfloat16* __restrict__ X, int rows, int D4, float p,
+                                                                unsigned long long seed) {
+  const Philox rng(seed);
+  const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const size_t total = (size_t)rows * D4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int row = (int)(i / D4), q = (int)(i - (size_t)row * D4);
+    float4 v = reinterpret_cast<const float4*>(news_vecs)[(size_t)inv_his[row] * D4 + q];
+    if (p > 0.f) {
+      const float4 m = dropout_mult4(rng, i, p, inv_keep);
+      v.x *= m.x; v.y *= m.y; v.z *= m.z; v.w *= m.w;
+    }
+    uint2 o;
+    *reinterpret_cast<__nv_bfloat162*>(&o.x) = __floats2bfloat162_rn(v.x, v.y);
+    *reinterpret_cast<__nv_bfloat162*>(&o.y) = __floats2bfloat162_rn(v.z, v.w);
+    reinterpret_cast<uint2*>(X)[i] = o;
+  }
+}
+
+// d_news[inv_his[row], :] += dX[row, :] * dropout_mult (+ N(0, noise_std^2))
+__global__ void __launch_bounds__(256) ue_scatter_dx_kernel(const float* __restrict__ dX, const int* __restrict__ inv_his,
+                                                            float* __restrict__ d_news, int rows, int D4, float p,
+                                                            unsigned long long seed, float noise_std,
+                                                            unsigned long long noise_seed) {
+  const Philox rng(seed), nrng(noise_seed);
+  const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
+  const size_t total = (size_t)rows * D4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int row = (int)(i / D4), q = (int)(i - (size_t)row * D4);
+    float4 v = reinterpret_cast<const float4*>(dX)[i];
+    if (p > 0.f) {
+      const float4 m = dropout_mult4(rng, i, p, inv_keep);
+      v.x *= m.x; v.y *= m.y; v.z *= m.z; v.w *= m.w;
+    }
+    if (noise_std > 0.f) {
+      uint32_t r[4]; nrng(i, 0x415u, r);
+      float z0, z1, z2, z3; box_muller(r[0], r[1], z0, z1); box_muller(r[2], r[3], z2, z3);
+      v.x += noise_std * z0; v.y += noise_std * z1; v.z += noise_std * z2; v.w += noise_std * z3;
+    }
+    red_add_f32x4(d_news + ((size_t)inv_his[row] * D4 + q) * 4, v);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Multi-head self-attention over the history, one warp per (user, head).
+// qkv bf16 [B*L, 3*H*dk] (q | k | v), ctx bf16 [B*L, H*dk], stats fp32 [B*H*L, 2] = (row max, denominator).
+// Lane i owns query rows i and i+32.
+// ---------------------------------------------------------------------------------------------------
+template <int DK>
+__global__ void __launch_bounds__(kFwdWarps * 32) ue_mha_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, const int* __restrict__ his_ids,
+                                                         __nv_bfloat16* __restrict__ ctx, float* __restrict__ stats,
+                                                         int B, int L, int H, float scale, int use_mask) {
+  __shared__ float sK[kFwdWarps][kMaxL][DK + 1];
+  __shared__ float sV[kFwdWarps][kMaxL][DK + 1];
+  __shared__ float sM[kFwdWarps][kMaxL];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int job = blockIdx.x * kFwdWarps + w;
+  if (job >= B * H) return;
+  const int b = job / H, h = job - b * H;
+  const int ld = 3 * H * DK;
+  const size_t row0 = (size_t)b * L;
+  for (int i = lane; i < L * DK; i += 32) {
+    const int r = i / DK, d = i - r * DK;
+    const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * DK + d;
+    sK[w][r][d] = __bfloat162float(base[H * DK]);
+    sV[w][r][d] = __bfloat162float(base[2 * H * DK]);
+  }
+  for (int j = lane; j < L; j += 32) sM[w][j] = (use_mask && his_ids[row0 + j] == 0) ? 0.f : 1.f;
+  __syncwarp();
+  for (int i = lane; i < L; i += 32) {
+    float q[DK];
+#pragma unroll
+    for (int d = 0; d < DK; ++d) q[d] = __bfloat162float(qkv[(row0 + i) * ld + h * DK + d]) * scale;
+    float m = -INFINITY;
+    for (int j = 0; j < L; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int d = 0; d < DK; ++d) s = fmaf(q[d], sK[w][j][d], s);
+      m = fmaxf(m, s);
+    }
+    float z = 0.f, acc[DK];
+#pragma unroll
+    for (int d = 0; d < DK; ++d) acc[d] = 0.f;
+    for (int j = 0; j < L; ++j) {
+      float s = 0.f;
+#pragma unroll
+      for (int d = 0; d < DK; ++d) s = fmaf(q[d], sK[w][j][d], s);
+      const float e = __expf(s - m) * sM[w][j];
+      z += e;
+#pragma unroll
+      for (int d = 0; d < DK; ++d) acc[d] = fmaf(e, sV[w][j][d], acc[d]);
+    }
+    z += 1e-8f * __expf(-m);
+    const float inv = 1.f / z;
+    __nv_bfloat16* op = ctx + (row0 + i) * (size_t)(H * DK) + h * DK;
+#pragma unroll
+    for (int d = 0; d < DK; d += 2)
+      *reinterpret_cast<__nv_bfloat162*>(op + d) = __floats2bfloat162_rn(acc[d] * inv, acc[d + 1] * inv);
+    stats[((size_t)job * L + i) * 2] = m;
+    stats[((size_t)job * L + i) * 2 + 1] = z;
+  }
+}
+
+// Backward of the attention: dctx bf16 [B*L, H*dk] → dqkv bf16 [B*L, 3*H*dk]. Probabilities are
+// recomputed from q, k and the saved (max, denominator).
+template <int DK>
+__global__ void __launch_bounds__(kBwdWarps * 32) ue_mha_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dctx,
+                                                         const float* __restrict__ stats, const int* __restrict__ his_ids,
+                                                         __nv_bfloat16* __restrict__ dqkv, int B, int L, int H, float scale,
+                                                         int use_mask) {
+  __shared__ float sQ[kBwdWarps][kMaxL][DK + 1];     // q * scale
+  __shared__ float sK[kBwdWarps][kMaxL][DK + 1];
+  __shared__ float sV[kBwdWarps][kMaxL][DK + 1];
+  __shared__ float sG[kBwdWarps][kMaxL][DK + 1];     // dctx
+  __shared__ float sMx[kBwdWarps][kMaxL], sZ[kBwdWarps][kMaxL], sDd[kBwdWarps][kMaxL], sMask[kBwdWarps][kMaxL];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int job = blockIdx.x * kBwdWarps + w;
+  if (job >= B * H) return;
+  const int b = job / H, h = job - b * H;
+  const int ld = 3 * H * DK;
+  const size_t row0 = (size_t)b * L;
+  for (int i = lane; i < L * DK; i += 32) {
+    const int r = i / DK, d = i - r * DK;
+    const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * DK + d;
+    sQ[w][r][d] = __bfloat162float(base[0]) * scale;
+    sK[w][r][d] = __bfloat162float(base[H * DK]);
+    sV[w][r][d] = __bfloat162float(base[2 * H * DK]);
+    sG[w][r][d] = __bfloat162float(dctx[(row0 + r) * (size_t)(H * DK) + h * DK + d]);
+  }
+  for (int j = lane; j < L; j += 32) {
+    sMx[w][j] = stats[((size_t)job * L + j) * 2];
+    sZ[w][j] = stats[((size_t)job * L + j) * 2 + 1];
+    sMask[w][j] = (use_mask && his_ids[row0 + j] == 0) ? 0.f : 1.f;
+  }
+  __syncwarp();
+  // pass 1 (lane = query i): Dd_i = sum_j P_ij dP_ij, then dQ_i = scale * sum_j dS_ij K_j
+  for (int i = lane; i < L; i += 32) {
+    const float m = sMx[w][i], invz = 1.f / sZ[w][i];
+    float dd = 0.f;
+    for (int j = 0; j < L; ++j) {
+      float s = 0.f, dp = 0.f;
+#pragma unroll
+      for (int d = 0; d < DK; ++d) {
+        s = fmaf(sQ[w][i][d], sK[w][j][d], s);
+        dp = fmaf(sG[w][i][d], sV[w][j][d], dp);
+      }
+      dd = fmaf(__expf(s - m) * sMask[w][j] * invz, dp, dd);
+    }
+    sDd[w][i] = dd;
+    float dq[DK];
+#pragma unroll
+    for (int d = 0; d < DK; ++d) dq[d] = 0.f;
+    for (int j = 0; j < L; ++j) {
+      float s = 0.f, dp = 0.f;
+#pragma unroll
+      for (int d = 0; d < DK; ++d) {
+        s = fmaf(sQ[w][i][d], sK[w][j][d], s);
+        dp = fmaf(sG[w][i][d], sV[w][j][d], dp);
+      }
+      const float ds = __expf(s - m) * sMask[w][j] * invz * (dp - dd);
+#pragma unroll
+      for (int d = 0; d < DK; ++d) dq[d] = fmaf(ds, sK[w][j][d], dq[d]);
+    }
+    __nv_bfloat16* op = dqkv + (row0 + i) * ld + h * DK;
+#pragma unroll
+    for (int d = 0; d < DK; d += 2)
+      *reinterpret_cast<__nv_bfloat162*>(op + d) = __floats2bfloat162_rn(dq[d] * scale, dq[d + 1] * scale);
+  }
+  __syncwarp();
+  // pass 2 (lane = key j): dV_j = sum_i P_ij dctx_i ; dK_j = sum_i dS_ij (q_i * scale)
+  for (int j = lane; j < L; j += 32) {
+    float dk[DK], dv[DK];
+#pragma unroll
+    for (int d = 0; d < DK; ++d) { dk[d] = 0.f; dv[d] = 0.f; }
+    const float mk = sMask[w][j];
+    for (int i = 0; i < L; ++i) {
+      float s = 0.f, dp = 0.f;
+#pragma unroll
+      for (int d = 0; d < DK; ++d) {
+        s = fmaf(sQ[w][i][d], sK[w][j][d], s);
+        dp = fmaf(sG[w][i][d], sV[w][j][d], dp);
+      }
+      const float pij = __expf(s - sMx[w][i]) * mk / sZ[w][i];
+      const float ds = pij * (dp - sDd[w][i]);
+#pragma unroll
+      for (int d = 0; d < DK; ++d) {
+        dv[d] = fmaf(pij, sG[w][i][d], dv[d]);
+        dk[d] = fmaf(ds, sQ[w][i][d], dk[d]);     // sQ already carries the 1/sqrt(dk) factor
+      }
+    }
+    __nv_bfloat16* op = dqkv + (row0 + j) * ld + h * DK;
+#pragma unroll
+    for (int d = 0; d < DK; d += 2) {
+      *reinterpret_cast<__nv_bfloat162*>(op + H * DK + d) = __floats2bfloat162_rn(dk[d], dk[d + 1]);
+      *reinterpret_cast<__nv_bfloat162*>(op + 2 * H * DK + d) = __floats2bfloat162_rn(dv[d], dv[d + 1]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Additive pooling + candidate scoring + sigmoid + soft-max CE, forward and (optionally) backward.
+// One block (128 threads) per user. D <= 512, Q <= 256, L <= 64, C <= 32.
+// ---------------------------------------------------------------------------------------------------
+struct PoolScoreArgs {
+  const __nv_bfloat16* ctx;     // [B*L, D]
+  const __nv_bfloat16* e;       // [B*L, Q]  tanh(fc1)
+  const float* w2;              // [Q]
+  const float* b2;              // [1]
+  const float* news_vecs;       // [U, D]
+  const int* inv_cand;          // [B*C]
+  const int* his_ids;           // [B*L] (mask) or null
+  float* score;                 // [B, C]
+  float* loss_mean;             // [1], zeroed by the entry point
+  float* user_vec;              // [B, D] or null
+  // backward outputs (null in inference)
+  __nv_bfloat16* d_ctx_pool;    // [B*L, D]   alpha_l * d_u
+  __nv_bfloat16* d_pre;         // [B*L, Q]   d a_l * w2 * (1 - e^2)
+  float* d_w2;                  // [Q]  (+=)
+  float* d_b2;                  // [1]  (+=)
+  float* d_news;                // [U, D] (+=)  candidate gradients scattered by unique row
+  int B, L, C, D, Q, use_mask, train;
+  float noise_std;
+  unsigned long long noise_seed;
+};
+
+__global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs a) {
+  __shared__ float sA[kMaxL];          // logits → exp → alpha
+  __shared__ float sU[512];            // user vector, later d_u
+  __shared__ float sS[32];             // candidate logits / ds
+  __shared__ float sDal[kMaxL];        // d_alpha, later d_a
+  __shared__ float red[32];
+  const int b = blockIdx.x, tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int L = a.L, D = a.D, Q = a.Q, C = a.C;
+  const size_t row0 = (size_t)b * L;
+  // a_l = e_l · w2 + b2  (one warp per row, 4 rows in flight)
+  for (int l = w; l < L; l += 4) {
+    float s = 0.f;
+    for (int c = lane; c < Q; c += 32) s = fmaf(__bfloat162float(a.e[(row0 + l) * Q + c]), a.w2[c], s);
+    s = warp_sum(s);
+    if (lane == 0) sA[l] = s + a.b2[0];
+  }
+  __syncthreads();
+  float mx = -INFINITY;
+  for (int l = tid; l < L; l += 128) mx = fmaxf(mx, sA[l]);
+  mx = block_max(mx, red);
+  float z = 0.f;
+  for (int l = tid; l < L; l += 128) {
+    const float mk = (a.use_mask && a.his_ids[row0 + l] == 0) ? 0.f : 1.f;
+    const float ex = __expf(sA[l] - mx) * mk;
+    sA[l] = ex;
+    z += ex;
+  }
+  z = block_sum(z, red) + 1e-8f * __expf(-mx);
+  __syncthreads();
+  for (int l = tid; l < L; l += 128) sA[l] *= 1.f / z;
+  __syncthreads();
+  // u = sum_l alpha_l ctx_l
+  for (int d = tid; d < D; d += 128) {
+    float acc = 0.f;
+    for (int l = 0; l < L; ++l) acc = fmaf(sA[l], __bfloat162float(a.ctx[(row0 + l) * D + d]), acc);
+    sU[d] = acc;
+    if (a.user_vec) a.user_vec[(size_t)b * D + d] = acc;
+  }
+  __syncthreads();
+  // candidate logits
+  for (int c = w; c < C; c += 4) {
+    const float* cv = a.news_vecs + (size_t)a.inv_cand[b * C + c] * D;
+    float s = 0.f;
+    for (int d = lane; d < D; d += 32) s = fmaf(cv[d], sU[d], s);
+    s = warp_sum(s);
+    if (lane == 0) sS[c] = s;
+  }
+  __syncthreads();
+  if (w == 0) {
+    const bool act = lane < C;
+    const float p = act ? 1.f / (1.f + __expf(-sS[lane])) : -INFINITY;
+    const float pm = warp_max(p);
+    const float ex = act ? __expf(p - pm) : 0.f;
+    const float zz = warp_sum(ex);
+    const float p0 = __shfl_sync(0xffffffffu, p, 0);
+    if (act && a.score) a.score[b * C + lane] = p;
+    if (lane == 0 && a.loss_mean) atomicAdd(a.loss_mean, -(p0 - pm - __logf(zz)) / (float)a.B);
+    // dL/ds_c = (softmax_c - [c == 0]) / B * p (1 - p)
+    const float ds = act ? (ex / zz - (lane == 0 ? 1.f : 0.f)) / (float)a.B * p * (1.f - p) : 0.f;
+    __syncwarp();
+    sS[lane] = ds;
+  }
+  if (!a.train) return;
+  __syncthreads();
+  // d_cand_c = ds_c * u → scattered into d_news ; d_u = sum_c ds_c cand_c
+  {
+    const Philox nrng(a.noise_seed);
+    const int D4 = D / 4;
+    for (int i = tid; i < C * D4; i += 128) {
+      const int c = i / D4, q = i - c * D4;
+      const float ds = sS[c];
+      float4 v = make_float4(ds * sU[4 * q], ds * sU[4 * q + 1], ds * sU[4 * q + 2], ds * sU[4 * q + 3]);
+      if (a.noise_std > 0.f) {
+        uint32_t r[4]; nrng((uint64_t)(b * C + c) * D4 + q, 0xCA4Du, r);
+        float z0, z1, z2, z3; box_muller(r[0], r[1], z0, z1); box_muller(r[2], r[3], z2, z3);
+        v.x += a.noise_std * z0; v.y += a.noise_std * z1; v.z += a.noise_std * z2; v.w += a.noise_std * z3;
+      }
+      red_add_f32x4(a.d_news + ((size_t)a.inv_cand[b * C + c] * D4 + q) * 4, v);
+    }
+  }
+  __syncthreads();
+  for (int d = tid; d < D; d += 128) {
+    float du = 0.f;
+    for (int c = 0; c < C; ++c) du = fmaf(sS[c], a.news_vecs[(size_t)a.inv_cand[b * C + c] * D + d], du);
+    sU[d] = du;                       // from here on sU holds d_u
+  }
+  __syncthreads();
+  // d_alpha_l = d_u · ctx_l ; d_ctx_pool[l] = alpha_l * d_u
+  for (int l = w; l < L; l += 4) {
+    float s = 0.f;
+    const float al = sA[l];
+    for (int d = lane * 2; d < D; d += 64) {
+      const float2 cf = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(a.ctx + (row0 + l) * D + d));
+      s = fmaf(sU[d], cf.x, s);
+      s = fmaf(sU[d + 1], cf.y, s);
+      *reinterpret_cast<__nv_bfloat162*>(a.d_ctx_pool + (row0 + l) * D + d) = __floats2bfloat162_rn(al * sU[d], al * sU[d + 1]);
+    }
+    s = warp_sum(s);
+    if (lane == 0) sDal[l] = s;
+  }
+  __syncthreads();
+  float dot = 0.f;
+  for (int l = tid; l < L; l += 128) dot = fmaf(sA[l], sDal[l], dot);
+  dot = block_sum(dot, red);
+  __syncthreads();
+  float db2 = 0.f;
+  for (int l = tid; l < L; l += 128) {
+    const float da = sA[l] * (sDal[l] - dot);
+    sDal[l] = da;
+    db2 += da;
+  }
+  db2 = block_sum(db2, red);
+  if (tid == 0) atomicAdd(a.d_b2, db2);
+  __syncthreads();
+  // d_w2 += sum_l da_l e_l ; d_pre[l] = da_l * w2 * (1 - e^2)
+  for (int c = tid; c < Q; c += 128) {
+    float acc = 0.f;
+    const float wc = a.w2[c];
+    for (int l = 0; l < L; ++l) {
+      const float ev = __bfloat162float(a.e[(row0 + l) * Q + c]);
+      acc = fmaf(sDal[l], ev, acc);
+      a.d_pre[(row0 + l) * Q + c] = __float2bfloat16(sDal[l] * wc * (1.f - ev * ev));
+    }
+    atomicAdd(a.d_w2 + c, acc);
+  }
+}
+
+// out[n] += sum_m X[m, n]   (bias gradients). X bf16 [M, N] with ld; rows limited by *m_dev * m_scale.
+__global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ X, float* __restrict__ out, int M,
+                                                          int N, int ld, const int* __restrict__ m_dev, int m_scale) {
+  if (m_dev) M = min(M, *m_dev * m_scale);
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int rlane = threadIdx.x >> 5;            // 8 row lanes
+  __shared__ float sm[8][33];
+  float acc = 0.f;
+  if (col < N)
+    for (int r = blockIdx.y * 8 + rlane; r < M; r += gridDim.y * 8) acc += __bfloat162float(X[(size_t)r * ld + col]);
+  sm[rlane][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (rlane == 0 && col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sm[i][threadIdx.x];
+    atomicAdd(out + col, t);
+  }
+}
+__global__ void __launch_bounds__(256) colsum_f32_kernel(const float* __restrict__ X, float* __restrict__ out, int M, int N,
+                                                         int ld, const int* __restrict__ m_dev, int m_scale) {
+  if (m_dev) M = min(M, *m_dev * m_scale);
+  const int col = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int rlane = threadIdx.x >> 5;
+  __shared__ float sm[8][33];
+  float acc = 0.f;
+  if (col < N)
+    for (int r = blockIdx.y * 8 + rlane; r < M; r += gridDim.y * 8) acc += X[(size_t)r * ld + col];
+  sm[rlane][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (rlane == 0 && col < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sm[i][threadIdx.x];
+    atomicAdd(out + col, t);
+  }
+}
+
+// out[c, r] = bf16(in[r, c])  — K-major copies of weights for the data-gradient GEMMs (tiny matrices)
+__global__ void __launch_bounds__(256) transpose_cast_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ out,
+                                                             int R, int Ccols, int ld_out) {
+  __shared__ float t[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    t[i][threadIdx.x] = (r < R && c < Ccols) ? in[(size_t)r * Ccols + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (c < Ccols && r < R) out[(size_t)c * ld_out + r] = __float2bfloat16(t[threadIdx.x][i]);
+  }
+}
+
+}  // namespace fr
+
+using namespace fr;
+
+FR_API int fr_ue_gather_dropout(const float* news_vecs, const int* inv_his, void* X, int rows, int D, float p,
+                                unsigned long long seed, void* stream) {
+  FR_REQUIRE(D % 4 == 0 && p >= 0.f && p < 1.f, "fr_ue_gather_dropout: D=%d p=%f", D, p);
+  if (rows == 0) return 0;
+  const size_t total = (size_t)rows * (D / 4);
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  ue_gather_dropout_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(news_vecs, inv_his, (__nv_bfloat16*)X, rows, D / 4, p, seed);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_ue_scatter_dx(const float* dX, const int* inv_his, float* d_news, int rows, int D, float p,
+                            unsigned long long seed, float noise_std, unsigned long long noise_seed, void* stream) {
+  FR_REQUIRE(D % 4 == 0, "fr_ue_scatter_dx: D=%d", D);
+  if (rows == 0) return 0;
+  const size_t total = (size_t)rows * (D / 4);
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  ue_scatter_dx_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dX, inv_his, d_news, rows, D / 4, p, seed, noise_std, noise_seed);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_ue_mha_fwd(const void* qkv, const int* his_ids, void* ctx, float* stats, int B, int L, int H, int dk,
+                         int use_mask, void* stream) {
+  FR_REQUIRE(L >= 1 && L <= kMaxL, "fr_ue_mha_fwd: L=%d must be in [1,%d]", L, kMaxL);
+  FR_REQUIRE(dk == 20 || dk == 32 || dk == 16, "fr_ue_mha_fwd: head dim %d not built (16, 20, 32)", dk);
+  FR_REQUIRE(!use_mask || his_ids, "fr_ue_mha_fwd: mask needs his_ids");
+  if (B == 0) return 0;
+  const int blocks = (B * H + kFwdWarps - 1) / kFwdWarps;
+  const float scale = 1.f / sqrtf((float)dk);
+  cudaStream_t s = (cudaStream_t)stream;
+#define FR_GO(DK) ue_mha_fwd_kernel<DK><<<blocks, kFwdWarps * 32, 0, s>>>((const __nv_bfloat16*)qkv, his_ids, (__nv_bfloat16*)ctx, stats, B, L, H, scale, use_mask)
+  if (dk == 20) FR_GO(20); else if (dk == 32) FR_GO(32); else FR_GO(16);
+#undef FR_GO
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_ue_mha_bwd(const void* qkv, const void* dctx, const float* stats, const int* his_ids, void* dqkv, int B,
+                         int L, int H, int dk, int use_mask, void* stream) {
+  FR_REQUIRE(L >= 1 && L <= kMaxL, "fr_ue_mha_bwd: L=%d must be in [1,%d]", L, kMaxL);
+  FR_REQUIRE(dk == 20 || dk == 32 || dk == 16, "fr_ue_mha_bwd: head dim %d not built (16, 20, 32)", dk);
+  if (B == 0) return 0;
+  const int blocks = (B * H + kBwdWarps - 1) / kBwdWarps;
+  const float scale = 1.f / sqrtf((float)dk);
+  cudaStream_t s = (cudaStream_t)stream;
+#define FR_GO(DK) ue_mha_bwd_kernel<DK><<<blocks, kBwdWarps * 32, 0, s>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dctx, stats, his_ids, (__nv_bfloat16*)dqkv, B, L, H, scale, use_mask)
+  if (dk == 20) FR_GO(20); else if (dk == 32) FR_GO(32); else FR_GO(16);
+#undef FR_GO
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, const float* b2, const float* news_vecs,
+                            const int* inv_cand, const int* his_ids, float* score, float* loss_mean, float* user_vec,
+                            void* d_ctx_pool, void* d_pre, float* d_w2, float* d_b2, float* d_news, int B, int L, int C,
+                            int D, int Q, int use_mask, int train, float noise_std, unsigned long long noise_seed,
+                            void* stream) {
+  FR_REQUIRE(L >= 1 && L <= kMaxL && C >= 1 && C <= 32 && D <= 512 && D % 4 == 0 && Q <= 256, "fr_ue_pool_score: bad shape L=%d C=%d D=%d Q=%d", L, C, D, Q);
+  FR_REQUIRE(!train || (d_ctx_pool && d_pre && d_w2 && d_b2 && d_news), "fr_ue_pool_score: backward outputs missing");
+  FR_REQUIRE(!use_mask || his_ids, "fr_ue_pool_score: mask needs his_ids");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (loss_mean) FR_CHECK(cudaMemsetAsync(loss_mean, 0, sizeof(float), s));
+  if (B == 0) return 0;
+  PoolScoreArgs a;
+  a.ctx = (const __nv_bfloat16*)ctx; a.e = (const __nv_bfloat16*)e; a.w2 = w2; a.b2 = b2; a.news_vecs = news_vecs;
+  a.inv_cand = inv_cand; a.his_ids = his_ids; a.score = score; a.loss_mean = loss_mean; a.user_vec = user_vec;
+  a.d_ctx_pool = (__nv_bfloat16*)d_ctx_pool; a.d_pre = (__nv_bfloat16*)d_pre; a.d_w2 = d_w2; a.d_b2 = d_b2; a.d_news = d_news;
+  a.B = B; a.L = L; a.C = C; a.D = D; a.Q = Q; a.use_mask = use_mask; a.train = train; a.noise_std = noise_std;
+  a.noise_seed = noise_seed;
+  ue_pool_score_kernel<<<B, 128, 0, s>>>(a);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_colsum(const void* X, int is_bf16, float* out, int M, int N, int ld, const int* m_dev, int m_scale,
+                     void* stream) {
+  if (M == 0 || N == 0) return 0;
+  int rows_blocks = (M + 255) / 256;
+  if (rows_blocks > 64) rows_blocks = 64;
+  if (rows_blocks < 1) rows_blocks = 1;
+  dim3 grid((N + 31) / 32, rows_blocks);
+  if (is_bf16) colsum_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)X, out, M, N, ld, m_dev, m_scale);
+  else colsum_f32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)X, out, M, N, ld, m_dev, m_scale);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_transpose_cast(const float* in, void* out, int R, int Ccols, int ld_out, void* stream) {
+  FR_REQUIRE(ld_out >= R, "fr_transpose_cast: ld_out=%d < R=%d", ld_out, R);
+  if (R == 0 || Ccols == 0) return 0;
+  dim3 grid((Ccols + 31) / 32, (R + 31) / 32), block(32, 8);
+  transpose_cast_kernel<<<grid, block, 0, (cudaStream_t)stream>>>(in, (__nv_bfloat16*)out, R, Ccols, ld_out);
+  FR_LAUNCH_CHECK();
+  return 0;
+}

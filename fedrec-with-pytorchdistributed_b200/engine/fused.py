@@ -20,7 +20,6 @@ from __future__ import annotations
 from typing import Dict, Optional
 
 import torch
-import torch.nn.functional as F
 
 from .. import ops
 from ..ops import dispatch as D
@@ -70,6 +69,8 @@ class FusedStep:
         assert self.dev.type == "cuda"
         self.trunk = PackedTrunk(model.text_encoder.DistillBert)
         self._bufs: Dict[int, Dict[str, torch.Tensor]] = {}
+        self._ubufs: Dict[tuple, Dict[str, torch.Tensor]] = {}
+        self._step_no = 0
         self._dedup_ws: Optional[torch.Tensor] = None
         self._gen = torch.Generator(device=self.dev)
         self._gen.manual_seed(cfg.seed + 17)
@@ -89,7 +90,10 @@ class FusedStep:
         hq = self.model.text_encoder.additive_attention.att_fc1.out_features
         b = {"x": z(R, dim), "y": z(R, dim), "ctx": z(R, dim), "qkv": z(R, 3 * dim), "ffn": z(R, ffn),
              "e": z(R, hq), "pooled": z(K, dim), "alpha": z(R, dt=torch.float32),
-             "news_vecs": z(K, self.cfg.news_dim, dt=torch.float32)}
+             "news_vecs": z(K, self.cfg.news_dim, dt=torch.float32),
+             # backward
+             "d_news": z(K, self.cfg.news_dim, dt=torch.float32), "d_news_bf": z(K, self.cfg.news_dim),
+             "d_pooled": z(K, dim), "d_pre": z(R, hq), "wfcT": z(dim, self.cfg.news_dim)}
         self._bufs[K] = b
         return b
 
@@ -132,55 +136,129 @@ class FusedStep:
             uniq, count, inv = ids, None, torch.arange(K, device=self.dev, dtype=torch.int32)
         return ids, uniq, count, inv, K
 
-    # ---- full step -----------------------------------------------------------------------------------------
-    def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
+    # ---- user encoder + loss, forward (and backward when training) -----------------------------------------
+    def _user_buffers(self, B: int, L: int, C: int) -> Dict[str, torch.Tensor]:
+        key = (B, L, C)
+        if key in self._ubufs:
+            return self._ubufs[key]
+        m = self.model
+        mha = m.user_encoder.multihead_attention
+        D, H, dk = mha.d_model, mha.n_heads, mha.d_k
+        Q = m.user_encoder.additive_attention.att_fc1.out_features
+        bf, dev = torch.bfloat16, self.dev
+        z = lambda *s, dt=bf: torch.zeros(*s, device=dev, dtype=dt)  # noqa: E731
+        R = B * L
+        u = {"X": z(R, D), "qkv": z(R, 3 * H * dk), "ctx": z(R, H * dk), "stats": z(B * H * L, 2, dt=torch.float32),
+             "E": z(R, Q), "score": z(B, C, dt=torch.float32), "loss": z((), dt=torch.float32),
+             "user": z(B, H * dk, dt=torch.float32), "d_ctx_pool": z(R, H * dk), "d_pre": z(R, Q), "d_ctx": z(R, H * dk),
+             "dqkv": z(R, 3 * H * dk), "dX": z(R, D, dt=torch.float32),
+             "wqkv": z(3 * H * dk, D), "bqkv": z(3 * H * dk, dt=torch.float32), "wqkvT": z(D, 3 * H * dk),
+             "w1": z(Q, H * dk), "w1T": z(H * dk, Q)}
+        self._ubufs[key] = u
+        return u
+
+    def _user_forward(self, b, inv, his, B, L, C, train: bool, seed: int):
         m, cfg = self.model, self.cfg
-        B, C = cand.shape
-        L = his.shape[1]
-        ids, uniq, count, inv, K = self._ids(cand, his)
-        b = self.encode(uniq, count, K)
-        m.train(train)
-        # --- user encoder + loss (autograd over fp32 news vectors) ---
-        nv = b["news_vecs"].detach().requires_grad_(train)
-        inv_l = inv.long()
-        his_vec = nv[inv_l[: B * L]].view(B, L, -1)
-        cand_vec = nv[inv_l[B * L:]].view(B, C, -1)
-        if train and cfg.news_grad_noise > 0:
-            std = cfg.news_grad_noise
+        ue = m.user_encoder
+        mha, aa = ue.multihead_attention, ue.additive_attention
+        H, dk = mha.n_heads, mha.d_k
+        u = self._user_buffers(B, L, C)
+        nv = b["news_vecs"]
+        inv_his, inv_cand = inv[: B * L], inv[B * L:]
+        p = float(ue.dropout_rate) if train else 0.0
+        use_mask = bool(cfg.mask_padding)
+        his_flat = his.reshape(-1).to(torch.int32) if use_mask else None
+        HD = H * dk
+        for i, lin in enumerate((mha.W_Q, mha.W_K, mha.W_V)):
+            D.cast_bf16(lin.weight.data, out=u["wqkv"][i * HD:(i + 1) * HD])
+            u["bqkv"][i * HD:(i + 1) * HD].copy_(lin.bias.data)
+        D.cast_bf16(aa.att_fc1.weight.data, out=u["w1"])
+        D.ue_gather_dropout(nv, inv_his, u["X"], p, seed)
+        D.linear_bf16(u["X"], u["wqkv"], u["bqkv"], "bias", out=u["qkv"])
+        D.ue_mha_fwd(u["qkv"], his_flat, u["ctx"], u["stats"], B, L, H, dk, use_mask)
+        D.linear_bf16(u["ctx"], u["w1"], aa.att_fc1.bias.data, "tanh", out=u["E"])
+        fl = m.flat
+        if train:
+            D.ue_pool_score(u["ctx"], u["E"], aa.att_fc2.weight.data.view(-1), aa.att_fc2.bias.data, nv, inv_cand,
+                            his_flat, u["score"], u["loss"], u["user"], u["d_ctx_pool"], u["d_pre"],
+                            fl.view("user_encoder.additive_attention.att_fc2.weight", grad=True).view(-1),
+                            fl.view("user_encoder.additive_attention.att_fc2.bias", grad=True), b["d_news"], B, L, C,
+                            use_mask, True, cfg.news_grad_noise, seed + 1)
+        else:
+            D.ue_pool_score(u["ctx"], u["E"], aa.att_fc2.weight.data.view(-1), aa.att_fc2.bias.data, nv, inv_cand,
+                            his_flat, u["score"], u["loss"], u["user"], None, None, None, None, None, B, L, C,
+                            use_mask, False)
+        return u, p, his_flat, use_mask
 
-            def _noise(g):
-                return g + torch.randn(g.shape, device=g.device, dtype=g.dtype, generator=self._gen) * std
-            his_vec.register_hook(_noise)
-            cand_vec.register_hook(_noise)
-        his_mask = (his != 0) if cfg.mask_padding else None
-        user = m.user_encoder(his_vec, his_mask)
-        loss, _ = ops.score_ce(cand_vec, user)
-        if not train:
-            return loss.detach()
-        m.flat.zero_grad()
-        loss.backward()
-        # --- text head backward with the per-news gradient injected (head-only; trunk is frozen) ---
-        T = m.news_tokens.shape[1]
-        hidden = b["x"].view(K, T, -1).float()
+    def _user_backward(self, u, b, inv, his_flat, use_mask, B, L, C, p, seed):
+        m, cfg = self.model, self.cfg
+        ue = m.user_encoder
+        mha, aa = ue.multihead_attention, ue.additive_attention
+        H, dk = mha.n_heads, mha.d_k
+        HD = H * dk
+        fl = m.flat
+        g = lambda name: fl.view(name, grad=True)  # noqa: E731
+        inv_his = inv[: B * L]
+        # additive attention fc1: data gradient (+ pooling path as the residual), weight and bias gradients
+        D.transpose_cast(aa.att_fc1.weight.data, out=u["w1T"])
+        D.linear_bf16(u["d_pre"], u["w1T"], None, "resid", resid=u["d_ctx_pool"], out=u["d_ctx"])
+        D.gemm_grad(u["d_pre"], u["ctx"], g("user_encoder.additive_attention.att_fc1.weight"))
+        D.colsum(u["d_pre"], g("user_encoder.additive_attention.att_fc1.bias"))
+        # attention
+        D.ue_mha_bwd(u["qkv"], u["d_ctx"], u["stats"], his_flat, u["dqkv"], B, L, H, dk, use_mask)
+        # Q/K/V projections
+        for i, nm in enumerate(("W_Q", "W_K", "W_V")):
+            sl = u["dqkv"][:, i * HD:(i + 1) * HD]
+            D.gemm_grad(sl, u["X"], g(f"user_encoder.multihead_attention.{nm}.weight"))
+            D.colsum(sl, g(f"user_encoder.multihead_attention.{nm}.bias"))
+            D.transpose_cast(getattr(mha, nm).weight.data, out=u["wqkvT"][:, i * HD:(i + 1) * HD])
+        D.linear_bf16(u["dqkv"], u["wqkvT"], None, "bias", out=u["dX"])
+        D.ue_scatter_dx(u["dX"], inv_his, b["d_news"], p, seed, cfg.news_grad_noise, seed + 2)
+
+    def _text_head_backward(self, b, count, K):
+        """d_news [K, D] → gradients of text_encoder.fc and text_encoder.additive_attention (trunk frozen)."""
+        m = self.model
         te = m.text_encoder
-        msk = m.news_mask[uniq.long()] if te.mask_padding else None
-        with torch.enable_grad():
-            vec = te.head(hidden, msk)
-            vec.backward(nv.grad)
-        return loss.detach()
+        aa = te.additive_attention
+        T = m.news_tokens.shape[1]
+        fl = m.flat
+        g = lambda name: fl.view(name, grad=True)  # noqa: E731
+        D.cast_bf16(b["d_news"], out=b["d_news_bf"])
+        D.transpose_cast(te.fc.weight.data, out=b["wfcT"])
+        D.linear_bf16(b["d_news_bf"], b["wfcT"], None, "bias", out=b["d_pooled"], m_dev=count, m_scale=1)
+        D.gemm_grad(b["d_news_bf"], b["pooled"], g("text_encoder.fc.weight"), k_dev=count, k_scale=1)
+        D.colsum(b["d_news"], g("text_encoder.fc.bias"), m_dev=count, m_scale=1)
+        D.text_pool_bwd(b["x"], b["e"], b["alpha"], b["d_pooled"], aa.att_fc2.weight.data.view(-1), count, K, T,
+                        b["d_pre"], g("text_encoder.additive_attention.att_fc2.weight").view(-1),
+                        g("text_encoder.additive_attention.att_fc2.bias"))
+        D.gemm_grad(b["d_pre"], b["x"], g("text_encoder.additive_attention.att_fc1.weight"), k_dev=count, k_scale=T)
+        D.colsum(b["d_pre"], g("text_encoder.additive_attention.att_fc1.bias"), m_dev=count, m_scale=T)
 
+    # ---- full step -----------------------------------------------------------------------------------------
     @torch.no_grad()
-    def scores(self, cand: torch.Tensor, his: torch.Tensor) -> torch.Tensor:
+    def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
         m = self.model
         B, C = cand.shape
         L = his.shape[1]
+        self._step_no += 1
+        seed = self.cfg.seed * 1000003 + 3 * self._step_no
         ids, uniq, count, inv, K = self._ids(cand, his)
         b = self.encode(uniq, count, K)
-        nv = b["news_vecs"]
-        inv_l = inv.long()
-        was = m.training
-        m.eval()
-        his_mask = (his != 0) if self.cfg.mask_padding else None
-        user = m.user_encoder(nv[inv_l[: B * L]].view(B, L, -1), his_mask)
-        m.train(was)
-        return torch.sigmoid(torch.bmm(nv[inv_l[B * L:]].view(B, C, -1), user.unsqueeze(-1)).squeeze(-1))
+        if train:
+            m.flat.zero_grad()
+            b["d_news"].zero_()
+        u, p, his_flat, use_mask = self._user_forward(b, inv, his, B, L, C, train, seed)
+        if train:
+            self._user_backward(u, b, inv, his_flat, use_mask, B, L, C, p, seed)
+            self._text_head_backward(b, count if count is not None else None, K)
+        self.last_scores = u["score"]
+        return u["loss"].clone()
+
+    @torch.no_grad()
+    def scores(self, cand: torch.Tensor, his: torch.Tensor) -> torch.Tensor:
+        B, C = cand.shape
+        L = his.shape[1]
+        ids, uniq, count, inv, K = self._ids(cand, his)
+        b = self.encode(uniq, count, K)
+        u, _, _, _ = self._user_forward(b, inv, his, B, L, C, False, 0)
+        return u["score"].clone()

@@ -26,6 +26,26 @@ SIGNATURES = {
     "fr_bert_attention": (I, [P, P, P, P, I, I, I, I, P, P]),
     "fr_text_pool": (I, [P, P, P, P, P, P, P, I, I, I, I, P, P, P]),
     "fr_cast_f32_to_bf16": (I, [P, P, LL, P]),
+    "fr_text_pool_bwd": (I, [P, P, P, P, P, P, I, I, I, I, P, P, P, P]),
+    # user_encoder.cu
+    "fr_ue_gather_dropout": (I, [P, P, P, I, I, F, c_ulonglong, P]),
+    "fr_ue_scatter_dx": (I, [P, P, P, I, I, F, c_ulonglong, F, c_ulonglong, P]),
+    "fr_ue_mha_fwd": (I, [P, P, P, P, I, I, I, I, I, P]),
+    "fr_ue_mha_bwd": (I, [P, P, P, P, P, I, I, I, I, I, P]),
+    "fr_ue_pool_score": (I, [P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, F, c_ulonglong, P]),
+    "fr_colsum": (I, [P, I, P, I, I, I, P, I, P]),
+    "fr_transpose_cast": (I, [P, P, I, I, I, P]),
+    # gemm_grad_sm100.cu
+    "fr_gemm_grad_bf16": (I, [P, P, P, I, I, I, I, I, I, P, I, I, P]),
+    # aggregate.cu
+    "fr_grad_allreduce": (I, [P, P, P, I, I, I, LL, c_uint, F, F, F, c_ulonglong, I, P]),
+    "fr_param_average": (I, [P, P, P, P, I, I, I, LL, c_uint, I, P]),
+    "fr_signal_pad_bytes": (I, []),
+    "fr_symm_alloc": (I, [P, LL]),
+    "fr_symm_free": (I, [P]),
+    "fr_symm_export": (I, [P, P]),
+    "fr_symm_import": (I, [P, P]),
+    "fr_symm_close": (I, [P]),
     # gemm_sm100.cu
     "fr_gemm_bf16": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, I, P]),
 }

@@ -220,3 +220,90 @@ def cast_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tens
     check(lib.fr_cast_f32_to_bf16(x.data_ptr(), out.data_ptr(), n, stream_ptr(x.device)), "fr_cast_f32_to_bf16")
     count_launches(1)
     return out
+
+
+# ---- user encoder / loss / gradient GEMMs (CUDA only) -------------------------------------------------------
+def ue_gather_dropout(news_vecs, inv_his, X, p, seed):
+    lib = require_native()
+    check(lib.fr_ue_gather_dropout(news_vecs.data_ptr(), inv_his.data_ptr(), X.data_ptr(), X.shape[0], X.shape[1],
+                                   float(p), int(seed) & (2 ** 64 - 1), stream_ptr(X.device)), "fr_ue_gather_dropout")
+    count_launches(1)
+    return X
+
+
+def ue_scatter_dx(dX, inv_his, d_news, p, seed, noise_std=0.0, noise_seed=0):
+    lib = require_native()
+    check(lib.fr_ue_scatter_dx(dX.data_ptr(), inv_his.data_ptr(), d_news.data_ptr(), dX.shape[0], dX.shape[1], float(p),
+                               int(seed) & (2 ** 64 - 1), float(noise_std), int(noise_seed) & (2 ** 64 - 1),
+                               stream_ptr(dX.device)), "fr_ue_scatter_dx")
+    count_launches(1)
+    return d_news
+
+
+def ue_mha_fwd(qkv, his_ids, ctx, stats, B, L, H, dk, use_mask=False):
+    lib = require_native()
+    check(lib.fr_ue_mha_fwd(qkv.data_ptr(), _p(his_ids), ctx.data_ptr(), stats.data_ptr(), B, L, H, dk, int(use_mask),
+                            stream_ptr(qkv.device)), "fr_ue_mha_fwd")
+    count_launches(1)
+    return ctx
+
+
+def ue_mha_bwd(qkv, dctx, stats, his_ids, dqkv, B, L, H, dk, use_mask=False):
+    lib = require_native()
+    check(lib.fr_ue_mha_bwd(qkv.data_ptr(), dctx.data_ptr(), stats.data_ptr(), _p(his_ids), dqkv.data_ptr(), B, L, H, dk,
+                            int(use_mask), stream_ptr(qkv.device)), "fr_ue_mha_bwd")
+    count_launches(1)
+    return dqkv
+
+
+def ue_pool_score(ctx, e, w2, b2, news_vecs, inv_cand, his_ids, score, loss, user_vec, d_ctx_pool, d_pre, d_w2, d_b2,
+                  d_news, B, L, C, use_mask=False, train=True, noise_std=0.0, noise_seed=0):
+    lib = require_native()
+    check(lib.fr_ue_pool_score(ctx.data_ptr(), e.data_ptr(), w2.data_ptr(), b2.data_ptr(), news_vecs.data_ptr(),
+                               inv_cand.data_ptr(), _p(his_ids), _p(score), _p(loss), _p(user_vec), _p(d_ctx_pool),
+                               _p(d_pre), _p(d_w2), _p(d_b2), _p(d_news), B, L, C, ctx.shape[1], e.shape[1],
+                               int(use_mask), int(train), float(noise_std), int(noise_seed) & (2 ** 64 - 1),
+                               stream_ptr(ctx.device)), "fr_ue_pool_score")
+    count_launches(1)
+
+
+def colsum(X, out, m_dev=None, m_scale=1):
+    """``out[n] += sum_m X[m, n]`` (X bf16 or fp32, unit inner stride)."""
+    lib = require_native()
+    assert X.stride(1) == 1 and out.dtype == torch.float32
+    check(lib.fr_colsum(X.data_ptr(), 1 if X.dtype == torch.bfloat16 else 0, out.data_ptr(), X.shape[0], X.shape[1],
+                        X.stride(0), _p(m_dev), m_scale, stream_ptr(X.device)), "fr_colsum")
+    count_launches(1)
+    return out
+
+
+def transpose_cast(w: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out[c, r] = bf16(w[r, c])`` for a contiguous fp32 matrix."""
+    lib = require_native()
+    R, Cc = w.shape
+    assert w.is_contiguous() and w.dtype == torch.float32
+    out = torch.empty(Cc, R, device=w.device, dtype=torch.bfloat16) if out is None else out
+    check(lib.fr_transpose_cast(w.data_ptr(), out.data_ptr(), R, Cc, out.stride(0), stream_ptr(w.device)), "fr_transpose_cast")
+    count_launches(1)
+    return out
+
+
+def gemm_grad(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, k_dev=None, k_scale=1, splits=0) -> torch.Tensor:
+    """``out[M1, N1] += A[K, M1]^T @ B[K, N1]`` on tcgen05 (MN-major operands, split-K, fp32 accumulate into ``out``)."""
+    lib = require_native()
+    assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and out.dtype == torch.float32
+    assert A.stride(1) == 1 and B.stride(1) == 1 and out.stride(1) == 1 and A.shape[0] == B.shape[0]
+    check(lib.fr_gemm_grad_bf16(A.data_ptr(), B.data_ptr(), out.data_ptr(), A.shape[1], B.shape[1], A.shape[0],
+                                A.stride(0), B.stride(0), out.stride(0), _p(k_dev), k_scale, splits,
+                                stream_ptr(A.device)), "fr_gemm_grad_bf16")
+    count_launches(1)
+    return out
+
+
+def text_pool_bwd(hidden, e, alpha, d_pooled, w2, count, n_items, T, d_pre, d_w2, d_b2):
+    lib = require_native()
+    check(lib.fr_text_pool_bwd(hidden.data_ptr(), e.data_ptr(), alpha.data_ptr(), d_pooled.data_ptr(), w2.data_ptr(),
+                               _p(count), n_items, T, e.shape[1], hidden.shape[1], d_pre.data_ptr(), d_w2.data_ptr(),
+                               d_b2.data_ptr(), stream_ptr(hidden.device)), "fr_text_pool_bwd")
+    count_launches(1)
+    return d_pre

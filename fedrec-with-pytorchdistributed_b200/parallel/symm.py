@@ -1,0 +1,163 @@
+"""Symmetric (peer-mapped) memory runtime for the aggregation kernels.
+
+Each rank allocates one heap — a signal pad followed by a data region — with identical
+layout on every GPU, exports it through CUDA IPC, and maps every peer's heap into its own
+address space. The 64-byte IPC handles travel once over the regular process group
+(``all_gather_object``); after that the process group is not used by the aggregation paths.
+Tensors handed out by ``alloc_f32`` are ordinary torch tensors viewing the heap, so the flat
+parameter/gradient buffers of the model live directly in memory the peers can load from.
+
+``SymmetricHeap.local(world)`` builds ``world`` heaps on the *current* GPU: the kernels then
+run all logical ranks inside one cooperative launch (``ranks_here = world``), which is how the
+single-GPU tests exercise the exact multi-rank code path without spinning kernels that wait on
+each other across launches.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from ..ops.native import check, require_native
+from ..ops.dispatch import count_launches, stream_ptr
+
+_ALIGN = 256
+
+
+class _RawCuda:
+    """Expose a raw device allocation to torch through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 3}
+
+
+def _as_tensor(ptr: int, nbytes: int, device: torch.device) -> torch.Tensor:
+    return torch.as_tensor(_RawCuda(ptr, nbytes), device=device)
+
+
+class SymmetricHeap:
+    def __init__(self, device: torch.device, rank: int, world: int, heap_bytes: int):
+        self.lib = require_native()
+        self.device, self.rank, self.W = device, rank, world
+        self.pad_bytes = int(self.lib.fr_signal_pad_bytes())
+        self.heap_bytes = int(heap_bytes)
+        self.local_ptr: int = 0
+        self.peer_ptrs: List[int] = []
+        self._imported: List[int] = []
+        self._cursor = (self.pad_bytes + _ALIGN - 1) // _ALIGN * _ALIGN
+        self._epoch = 0
+        self._local_heaps: Optional[List[int]] = None     # single-GPU emulation: all ranks' heaps are ours
+        self._bytes_tensor: Optional[torch.Tensor] = None
+        self.mc_ptr: int = 0
+
+    # ---- construction -----------------------------------------------------------------------------------
+    @classmethod
+    def create(cls, info, heap_bytes: int = 64 << 20) -> "SymmetricHeap":
+        h = cls(info.device, info.rank, info.world_size, heap_bytes)
+        p = ctypes.c_void_p()
+        with torch.cuda.device(info.device):
+            check(h.lib.fr_symm_alloc(ctypes.byref(p), h.heap_bytes), "fr_symm_alloc")
+        h.local_ptr = p.value
+        h._bytes_tensor = _as_tensor(h.local_ptr, h.heap_bytes, h.device)
+        return h
+
+    def finalize(self) -> None:
+        """Exchange IPC handles and map every peer's heap (collective over the default process group)."""
+        if self.peer_ptrs:
+            return
+        handle = ctypes.create_string_buffer(64)
+        check(self.lib.fr_symm_export(self.local_ptr, handle), "fr_symm_export")
+        gathered: List[Optional[bytes]] = [None] * self.W
+        dist.all_gather_object(gathered, handle.raw)
+        ptrs = []
+        with torch.cuda.device(self.device):
+            for r, raw in enumerate(gathered):
+                if r == self.rank:
+                    ptrs.append(self.local_ptr)
+                    continue
+                q = ctypes.c_void_p()
+                check(self.lib.fr_symm_import(ctypes.create_string_buffer(raw, 64), ctypes.byref(q)), "fr_symm_import")
+                ptrs.append(q.value)
+                self._imported.append(q.value)
+        self.peer_ptrs = ptrs
+        torch.cuda.synchronize(self.device)
+        dist.barrier()
+
+    @classmethod
+    def local(cls, world: int, heap_bytes: int = 16 << 20, device: Optional[torch.device] = None) -> List["SymmetricHeap"]:
+        """``world`` heaps on one GPU, each seeing all of them as peers (single-GPU emulation)."""
+        device = device or torch.device("cuda", torch.cuda.current_device())
+        heaps = []
+        for r in range(world):
+            h = cls(device, r, world, heap_bytes)
+            p = ctypes.c_void_p()
+            check(h.lib.fr_symm_alloc(ctypes.byref(p), heap_bytes), "fr_symm_alloc")
+            h.local_ptr = p.value
+            h._bytes_tensor = _as_tensor(h.local_ptr, heap_bytes, device)
+            heaps.append(h)
+        ptrs = [h.local_ptr for h in heaps]
+        for h in heaps:
+            h.peer_ptrs = list(ptrs)
+            h._local_heaps = ptrs
+        return heaps
+
+    # ---- allocation ----------------------------------------------------------------------------------------
+    def alloc_f32(self, numel: int) -> torch.Tensor:
+        nbytes = (numel * 4 + _ALIGN - 1) // _ALIGN * _ALIGN
+        if self._cursor + nbytes > self.heap_bytes:
+            raise MemoryError(f"symmetric heap exhausted: need {nbytes} B at offset {self._cursor} of {self.heap_bytes}")
+        off = self._cursor
+        self._cursor += nbytes
+        t = self._bytes_tensor[off: off + numel * 4].view(torch.float32)
+        t.zero_()
+        return t
+
+    def offset_of(self, t: torch.Tensor) -> int:
+        off = t.data_ptr() - self.local_ptr
+        if not (0 <= off and off + t.numel() * t.element_size() <= self.heap_bytes):
+            raise ValueError("tensor does not live in this symmetric heap")
+        return off
+
+    # ---- kernels ---------------------------------------------------------------------------------------------
+    def _ptr_arrays(self, off: int):
+        bufs = (ctypes.c_void_p * self.W)(*[p + off for p in self.peer_ptrs])
+        pads = (ctypes.c_void_p * self.W)(*self.peer_ptrs)
+        return bufs, pads
+
+    def _next_epoch(self) -> int:
+        self._epoch += 1
+        return self._epoch
+
+    def grad_allreduce_(self, g: torch.Tensor, clip: float, noise_std: float, seed: int, scale: float,
+                        ranks_here: int = 1, blocks: int = 0) -> torch.Tensor:
+        assert self.peer_ptrs, "call finalize() first"
+        bufs, pads = self._ptr_arrays(self.offset_of(g))
+        n = (g.numel() + 3) // 4 * 4
+        check(self.lib.fr_grad_allreduce(bufs, pads, self.mc_ptr or None, self.W, self.rank if ranks_here == 1 else 0,
+                                         ranks_here, n, self._next_epoch(), float(clip), float(noise_std), float(scale),
+                                         int(seed) & (2 ** 64 - 1), blocks, stream_ptr(self.device)), "fr_grad_allreduce")
+        count_launches(1)
+        return g
+
+    def param_average_(self, buf: torch.Tensor, weights: Sequence[float], ranks_here: int = 1, blocks: int = 0) -> torch.Tensor:
+        assert self.peer_ptrs, "call finalize() first"
+        bufs, pads = self._ptr_arrays(self.offset_of(buf))
+        w = (ctypes.c_float * self.W)(*[float(x) for x in weights])
+        n = (buf.numel() + 3) // 4 * 4
+        check(self.lib.fr_param_average(bufs, pads, self.mc_ptr or None, w, self.W, self.rank if ranks_here == 1 else 0,
+                                        ranks_here, n, self._next_epoch(), blocks, stream_ptr(self.device)), "fr_param_average")
+        count_launches(1)
+        return buf
+
+    def close(self) -> None:
+        if self.local_ptr == 0:
+            return
+        torch.cuda.synchronize(self.device)
+        for p in self._imported:
+            self.lib.fr_symm_close(p)
+        self._imported = []
+        self._bytes_tensor = None
+        # the heap itself stays allocated until process exit: torch tensors may still view it
+        self.local_ptr = 0

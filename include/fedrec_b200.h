@@ -73,6 +73,72 @@ int fr_text_pool(const void* hidden, const void* e, const float* w2, const float
 
 int fr_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
 
+/* Backward of fr_text_pool given d_pooled (bf16 [n,768]): writes d_pre = d(tanh input) bf16 [n*T,Hq] (tail rows
+ * zeroed to a 64-row boundary), accumulates d_w2 [Hq], d_b2 [1]. The trunk is frozen, so no d_hidden.
+ * Replaces the autograd of attention.py:16-25 inside news_vecs.backward(news_grad), model.py:86-87. */
+int fr_text_pool_bwd(const void* hidden, const void* e, const float* alpha, const void* d_pooled, const float* w2,
+                     const int* count_dev, int n_items, int T, int Hq, int hidden_dim, void* d_pre, float* d_w2,
+                     float* d_b2, void* stream);
+
+/* ---- user encoder + loss, forward and backward (csrc/user_encoder.cu) ---------------------------------- */
+
+/* X[r,:] = bf16(dropout(news_vecs[inv_his[r],:], p)) with a Philox mask (seed); encoder.py:50 + the gather that
+ * model.py:112-117 does through numpy. fr_ue_scatter_dx is its backward fused with the news-gradient
+ * segment-sum (main.py:20-42) and the optional LDP noise on news-vector gradients (client.py:87-89):
+ * d_news[inv_his[r],:] += dX[r,:]*mask + N(0, noise_std^2). */
+int fr_ue_gather_dropout(const float* news_vecs, const int* inv_his, void* X, int rows, int D, float p,
+                         unsigned long long seed, void* stream);
+int fr_ue_scatter_dx(const float* dX, const int* inv_his, float* d_news, int rows, int D, float p,
+                     unsigned long long seed, float noise_std, unsigned long long noise_seed, void* stream);
+
+/* Per-(user, head) attention exp(QK^T/sqrt(dk))*mask/(rowsum+1e-8) · V; qkv bf16 [B*L, 3*H*dk] -> ctx bf16
+ * [B*L, H*dk], stats fp32 [B*H*L, 2]. attention.py:37-45,69-81. The backward recomputes the probabilities. */
+int fr_ue_mha_fwd(const void* qkv, const int* his_ids, void* ctx, float* stats, int B, int L, int H, int dk,
+                  int use_mask, void* stream);
+int fr_ue_mha_bwd(const void* qkv, const void* dctx, const float* stats, const int* his_ids, void* dqkv, int B, int L,
+                  int H, int dk, int use_mask, void* stream);
+
+/* Additive pooling over the history + candidate scoring + sigmoid + soft-max CE (label 0), and with train != 0 the
+ * whole backward down to the GEMM operands: d_ctx_pool, d_pre (bf16), d_w2/d_b2 (+=), candidate gradients
+ * scattered into d_news (+=). attention.py:14-26, model.py:121-126. */
+int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, const float* b2, const float* news_vecs,
+                     const int* inv_cand, const int* his_ids, float* score, float* loss_mean, float* user_vec,
+                     void* d_ctx_pool, void* d_pre, float* d_w2, float* d_b2, float* d_news, int B, int L, int C, int D,
+                     int Q, int use_mask, int train, float noise_std, unsigned long long noise_seed, void* stream);
+
+/* out[n] += sum_m X[m,n] (bias gradients); X bf16 or fp32 with leading dimension ld. */
+int fr_colsum(const void* X, int is_bf16, float* out, int M, int N, int ld, const int* m_dev, int m_scale, void* stream);
+/* out[c,r] = bf16(in[r,c]): K-major weight copies for the data-gradient GEMMs. */
+int fr_transpose_cast(const float* in, void* out, int R, int Ccols, int ld_out, void* stream);
+
+/* ---- federated aggregation over NVLink (csrc/aggregate.cu) -------------------------------------------- */
+
+/* Every rank owns one fp32 buffer of n floats and one signal pad (fr_signal_pad_bytes(), zero-initialised) in
+ * peer-mapped memory; bufs_host[i]/pads_host[i] are THIS process's mappings of rank i's. mc_buf: NVLS multicast
+ * mapping of the buffers or NULL (plain peer loads/stores). epoch: > 0 and increasing by one per call on a pad
+ * set (shared by both functions). ranks_here = 1 normally (rank = rank_base); ranks_here > 1 runs that many
+ * logical ranks inside one cooperative launch on the local GPU (single-GPU testing). blocks <= 0 = default.
+ *
+ * fr_grad_allreduce: buf_r <- scale * sum_i [ buf_i * min(1, clip/||buf_i||) + N(0, noise_std^2) ] on every rank.
+ *   Replaces DDP's gradient all-reduce and Gradient_Averaging_main.py:146; noise: client.py:87-89.
+ * fr_param_average: buf_r <- sum_i weights_host[i] * buf_i on every rank (weighted FedAvg + redistribution).
+ *   Replaces Parameter_Averaging_main.py:144-148, server.py:37-55,76-77 and client.py:261-264. */
+int fr_grad_allreduce(void* const* bufs_host, void* const* pads_host, void* mc_buf, int W, int rank_base,
+                      int ranks_here, long long n, unsigned epoch, float clip, float noise_std, float scale,
+                      unsigned long long seed, int blocks, void* stream);
+int fr_param_average(void* const* bufs_host, void* const* pads_host, void* mc_buf, const float* weights_host, int W,
+                     int rank_base, int ranks_here, long long n, unsigned epoch, int blocks, void* stream);
+int fr_signal_pad_bytes(void);
+
+/* Peer-mappable allocations through CUDA IPC: alloc (zeroed), export a 64-byte handle, import a peer's handle
+ * (enables peer access lazily), close an imported mapping, free. Replaces init_process_group's role as the
+ * only transport (main.py:144 etc.): here the process group is used for the handle exchange only. */
+int fr_symm_alloc(void** ptr_out_host, long long bytes);
+int fr_symm_free(void* ptr);
+int fr_symm_export(void* ptr, void* handle64_host);
+int fr_symm_import(const void* handle64_host, void** ptr_out_host);
+int fr_symm_close(void* ptr);
+
 /* ---- tcgen05 GEMM (csrc/gemm_sm100.cu) ------------------------------------------------------------ */
 
 /* out = epi(A[M,K]·W[N,K]^T + bias); A, W bf16 K-major; out bf16 or fp32. epi: 0 bias, 1 bias+GELU(erf),
@@ -81,6 +147,12 @@ int fr_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
 int fr_gemm_bf16(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32, int M,
                  int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n, const int* m_dev, int m_scale,
                  void* stream);
+
+/* out[M1,N1] (fp32) += A[K,M1]^T · B[K,N1]: weight gradients dW = dY^T X on tcgen05 with MN-major operands and
+ * split-K (csrc/gemm_grad_sm100.cu). K_eff = min(K, *k_dev * k_scale); rows of A in [K_eff, round_up(K_eff,64))
+ * must be zero. Replaces the autograd weight-gradient GEMMs of every trainable nn.Linear. */
+int fr_gemm_grad_bf16(const void* A, const void* B, float* out, int M1, int N1, int K, int lda, int ldb, int ldo,
+                      const int* k_dev, int k_scale, int splits, void* stream);
 
 #ifdef __cplusplus
 }
