@@ -173,6 +173,8 @@ def test_text_head_backward_matches_autograd():
     pooled_ref.backward(d_pooled[:m].float())
     assert (d_pre[m * T: (m * T + 63) // 64 * 64] == 0).all() and (d_pre[(m * T + 63) // 64 * 64:] == 9.0).all()
     rel = lambda a, b_: float((a - b_).norm() / b_.norm())  # noqa: E731
-    assert rel(d_w2, w2r.grad) < 3e-2 and rel(d_b2, b2r.grad) < 3e-2
+    assert rel(d_w2, w2r.grad) < 3e-2
+    # d_b2 = sum_t d_a_t = dot * (1 - sum alpha) is ~0 by construction: compare on the scale of the other gradients
+    assert abs(float(d_b2) - float(b2r.grad)) < 1e-3 * float(w2r.grad.abs().max())
     assert rel(dW1, w1r.grad) < 3e-2, rel(dW1, w1r.grad)
     assert rel(db1, b1r.grad) < 3e-2
