@@ -353,3 +353,63 @@ FR_API int fr_clip_noise(float* x, long long n, const float* sq, float clip, flo
   FR_LAUNCH_CHECK();
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// fr_dedup_static: the same de-duplication as fr_dedup for callers that have no memory to hand over.
+//
+// fr_dedup needs fr_dedup_workspace_ints(N) ints of scratch from its caller. Some callers cannot supply it:
+// a C or C++ host that drives this library directly and owns no device allocator, a serving process in which
+// another framework's pool has already claimed the whole device-memory budget (a fresh cudaMalloc there can
+// fail or fragment the pool), and request loops that forbid cudaMalloc/cudaFree outright because both
+// serialise against every stream on the device. For them the scratch lives here, in a file-scope device array
+// that every GPU loading this library carries until the process exits:
+//   kStaticDedupMaxRows = 1,048,576 table rows  ->  (1,048,576 + 1024 + 1) ints = 4,198,404 bytes per GPU.
+// Inputs and outputs are still the caller's. The function allocates nothing and frees nothing.
+//
+// Set-up: the array's name is only a host-side handle, so the device address is looked up with
+// cudaGetSymbolAddress once per device, on the first call made while that device is current; the result is
+// cached. Make that first call before starting any stream capture on the device.
+// Sharing: every call on a device uses the same array and finds the previous call's contents in it; the flag
+// region is cleared at the start of each call and the rest is fully rewritten before it is read. Two calls that
+// may overlap on the GPU (different streams, no dependency) race on the array and must be ordered by the caller.
+// ---------------------------------------------------------------------------------------------------------
+namespace fr {
+constexpr int kStaticDedupMaxRows = 1 << 20;
+constexpr int kStaticDedupInts = kStaticDedupMaxRows + (kStaticDedupMaxRows + kDedupBlock - 1) / kDedupBlock + 1;
+static __device__ __align__(256) int g_static_dedup_scratch[kStaticDedupInts];
+constexpr int kMaxDevices = 64;
+static int* g_static_dedup_ptr[kMaxDevices] = {nullptr};
+}  // namespace fr
+
+FR_API int fr_dedup_static_max_rows() { return kStaticDedupMaxRows; }
+
+FR_API int fr_dedup_static(const int* ids, int K, int N, int* uniq, int* count, int* inv, void* stream) {
+  FR_REQUIRE(K >= 1 && N >= 1, "fr_dedup_static: bad sizes K=%d N=%d", K, N);
+  FR_REQUIRE(N <= kStaticDedupMaxRows,
+             "fr_dedup_static: N=%d table rows exceed the built-in scratch (%d rows); use fr_dedup with caller scratch",
+             N, kStaticDedupMaxRows);
+  int dev = 0;
+  FR_CHECK(cudaGetDevice(&dev));
+  FR_REQUIRE(dev >= 0 && dev < kMaxDevices, "fr_dedup_static: device ordinal %d out of range", dev);
+  int* ws = __atomic_load_n(&g_static_dedup_ptr[dev], __ATOMIC_ACQUIRE);
+  if (ws == nullptr) {
+    // first call on this device: resolve the device address of the file-scope array (its host-side name is not one)
+    void* p = nullptr;
+    FR_CHECK(cudaGetSymbolAddress(&p, g_static_dedup_scratch));
+    FR_REQUIRE(p != nullptr, "fr_dedup_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+    ws = static_cast<int*>(p);
+    __atomic_store_n(&g_static_dedup_ptr[dev], ws, __ATOMIC_RELEASE);
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  const int nb = (N + kDedupBlock - 1) / kDedupBlock;
+  int* flag = ws;
+  int* block_counts = ws + N;
+  FR_CHECK(cudaMemsetAsync(flag, 0, (size_t)N * sizeof(int), s));     // must start at zero; the array keeps old contents
+  dedup_mark_kernel<<<(K + 255) / 256, 256, 0, s>>>(ids, K, N, flag);
+  dedup_count_kernel<<<nb, kDedupBlock, 0, s>>>(flag, N, block_counts);
+  dedup_scan_kernel<<<1, 1024, 0, s>>>(block_counts, nb, count);
+  dedup_compact_kernel<<<nb, kDedupBlock, 0, s>>>(flag, N, block_counts, uniq);
+  dedup_inverse_kernel<<<(K + 255) / 256, 256, 0, s>>>(ids, K, N, flag, inv, count, uniq);
+  FR_LAUNCH_CHECK();
+  return 0;
+}

@@ -18,6 +18,8 @@ SIGNATURES = {
     "fr_adam_flat": (I, [P, P, P, P, LL, F, F, F, F, F, F, P, F, P]),
     "fr_dedup_workspace_ints": (LL, [I]),
     "fr_dedup": (I, [P, I, I, P, P, P, P, P]),
+    "fr_dedup_static_max_rows": (I, []),
+    "fr_dedup_static": (I, [P, I, I, P, P, P, P]),
     "fr_sq_norm": (I, [P, LL, P, P]),
     "fr_clip_noise": (I, [P, LL, P, F, F, c_ulonglong, c_uint, P]),
     # bert_ops.cu

@@ -41,6 +41,16 @@ int fr_adam_flat(float* p, const float* g, float* m, float* v, long long n, floa
 long long fr_dedup_workspace_ints(int N);
 int fr_dedup(const int* ids, int K, int N, int* workspace, int* uniq, int* count, int* inv, void* stream);
 
+/* fr_dedup with the scratch built into the library: for hosts that cannot hand over device memory (a plain C/C++
+ * caller with no allocator of its own, a process whose memory budget another pool already holds, a request loop
+ * where cudaMalloc/cudaFree are banned because they stall every stream). No counterpart in the reference. Same
+ * outputs as fr_dedup. Limit: N <= fr_dedup_static_max_rows() (1,048,576 rows; 4,198,404 bytes of device memory
+ * per GPU, held for the life of the process); larger N is refused with an error. Allocates and frees nothing.
+ * The first call on each device resolves the scratch address and must come before any stream capture on that
+ * device. All calls on a device share the scratch: calls that can overlap on the GPU race; order them. */
+int fr_dedup_static_max_rows(void);
+int fr_dedup_static(const int* ids, int K, int N, int* uniq, int* count, int* inv, void* stream);
+
 /* *out = sum(x^2);  x = x*min(1, clip/sqrt(*sq)) + N(0, noise_std^2) with a Philox stream (seed, stream_id).
  * Single-GPU halves of the fused gradient aggregation; client.py:87-89 is the upstream noise. */
 int fr_sq_norm(const float* x, long long n, float* out, void* stream);
