@@ -263,7 +263,7 @@ FR_API int fr_grad_allreduce(void* const* bufs_host, void* const* pads_host, voi
   for (int i = 0; i < W; ++i) { p.bufs[i] = (float*)bufs_host[i]; p.pads[i] = (uint32_t*)pads_host[i]; }
   p.mc_buf = (float*)mc_buf; p.W = W; p.rank_base = rank_base; p.ranks_here = ranks_here; p.n = n; p.epoch = epoch;
   p.clip = clip; p.noise_std = noise_std; p.scale = scale; p.seed = seed;
-  if (blocks <= 0) blocks = 32;
+  if (blocks <= 0) blocks = 128;
   return launch_agg(0, mc_buf != nullptr, p, blocks, (cudaStream_t)stream);
 }
 
@@ -279,7 +279,7 @@ FR_API int fr_param_average(void* const* bufs_host, void* const* pads_host, void
   }
   p.mc_buf = (float*)mc_buf; p.W = W; p.rank_base = rank_base; p.ranks_here = ranks_here; p.n = n; p.epoch = epoch;
   p.scale = 1.f;
-  if (blocks <= 0) blocks = n >= (1 << 22) ? 96 : 32;
+  if (blocks <= 0) blocks = 128;
   return launch_agg(1, mc_buf != nullptr, p, blocks, (cudaStream_t)stream);
 }
 

@@ -1,0 +1,41 @@
+"""Tiny single-GPU drivers for `ncu --set full` captures (one kernel family per invocation).
+
+usage: python scripts/profile_target.py gemm_ffn1|gemm_out|gemm_qkv|gemm_ffn2|attention|gemm_grad|step
+"""
+import os
+import sys
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from fedrec_b200.ops import dispatch as D  # noqa: E402
+
+DEV = "cuda:0"
+what = sys.argv[1] if len(sys.argv) > 1 else "gemm_ffn1"
+M = int(os.environ.get("FEDREC_PROFILE_M", "27000"))
+torch.manual_seed(0)
+
+if what.startswith("gemm_") and what != "gemm_grad":
+    N, K, epi = {"gemm_ffn1": (3072, 768, "gelu"), "gemm_out": (768, 768, "resid"), "gemm_qkv": (2304, 768, "bias"),
+                 "gemm_ffn2": (768, 3072, "resid")}[what]
+    x = (torch.randn(M, K, device=DEV) * 0.5).bfloat16()
+    w = (torch.randn(N, K, device=DEV) / K ** 0.5).bfloat16()
+    b = torch.randn(N, device=DEV)
+    r = torch.randn(M, N, device=DEV).bfloat16() if epi == "resid" else None
+    out = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    for _ in range(6):
+        D.linear_bf16(x, w, b, epi, resid=r, out=out)
+elif what == "attention":
+    n, T, H = M // 30, 30, 12
+    qkv = (torch.randn(n * T, 2304, device=DEV) * 0.7).bfloat16()
+    out = torch.zeros(n * T, 768, device=DEV, dtype=torch.bfloat16)
+    for _ in range(6):
+        D.bert_attention(qkv, None, None, None, n, T, H, out)
+elif what == "gemm_grad":
+    A = (torch.randn(M, 384, device=DEV) * 0.3).bfloat16()
+    B = (torch.randn(M, 768, device=DEV) * 0.3).bfloat16()
+    out = torch.zeros(384, 768, device=DEV)
+    for _ in range(6):
+        D.gemm_grad(A, B, out)
+torch.cuda.synchronize()
+print("done", what)
