@@ -1,0 +1,265 @@
+// N8 on the tensor cores: DistilBERT self-attention for short titles (T <= 64 tokens, 12 heads x 64).
+//
+// A title is far smaller than a tcgen05 tile, so TP = floor(128 / T) consecutive titles share one 128-row
+// tile and the attention is block-diagonal inside it:
+//   S[128 x 128] = Q_h K_h^T        tcgen05.mma, both operands K-major, straight from the QKV GEMM output via TMA
+//   P = exp(S/8 - rowmax) masked to the row's own title and to valid keys (HF: masked_fill(finfo.min) + softmax)
+//   O[128 x 64]  = P V_h            tcgen05.mma, A = P written to shared memory in the K-major 128B-swizzled
+//                                   layout by the soft-max threads, B = V_h as loaded (tokens x 64 = MN-major)
+//   out = O / rowsum                (deferred normalisation), bf16
+// The block-diagonal waste (x TP in MMA work) is irrelevant: the tile is latency-bound, not throughput-bound.
+// One CTA = 4 warps; thread r owns row r of the tile for the soft-max and the epilogue; lane 0 of warp 0 issues
+// the TMA loads and both MMAs. 80 KB of shared memory and 256 TMEM columns per CTA, so two CTAs share an SM and
+// hide each other's latencies. Reference: HF MultiHeadSelfAttention reached from encoder.py:27.
+#include "sm100.cuh"
+#include <cuda.h>
+
+namespace fr {
+using namespace sm100;
+
+int make_tmap_bf16_2d_box(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows,
+                          int box_cols);
+
+constexpr int kAttTile = 128;
+constexpr int kAttHd = 64;
+
+__device__ __forceinline__ uint64_t att_desc_k_sw128(uint32_t addr) { return make_smem_desc_sw128(addr); }
+__device__ __forceinline__ uint64_t att_desc_mn_sw128(uint32_t addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)(1024 >> 4) << 16;      // LBO: single 64-wide atom along N, value unused
+  d |= (uint64_t)(1024 >> 4) << 32;      // SBO: 8-token groups are 1024 bytes apart
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+__host__ __device__ constexpr uint32_t att_idesc(int M, int N, int b_mn_major) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn_major << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+struct AttParams {
+  const int* mask_table;     // [table rows, T] or null
+  const int* items;          // [n_items] table row of every title, or null (identity)
+  const int* count_dev;      // optional device count of valid titles
+  __nv_bfloat16* out;        // [n_items*T, heads*64]
+  int n_items, T, heads, TP;
+};
+
+__global__ void __launch_bounds__(128, 2)
+bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sQ = smem;                     // 128 x 64 bf16, K-major SW128
+  uint8_t* sK = smem + 16384;
+  uint8_t* sV = smem + 32768;             // tokens x 64: MN-major SW128 for the second MMA
+  uint8_t* sP = smem + 49152;             // 128 x 128 bf16 as two K-major SW128 blocks of 64 columns
+  uint64_t* bar_load = reinterpret_cast<uint64_t*>(smem + 81920);
+  uint64_t* bar_mma = bar_load + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mma + 1);
+  float* sKeyBias = reinterpret_cast<float*>(tmem_slot + 2);     // [128] 0 or -inf per key column of the tile
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int T = p.T, TP = p.TP, heads = p.heads;
+  const int n_eff = p.count_dev ? min(p.n_items, *p.count_dev) : p.n_items;
+  const int num_tiles = (n_eff + TP - 1) / TP;
+  const int hd_all = heads * kAttHd;
+
+  if (tid == 0) {
+    prefetch_tmap(&tmap_qkv);
+    mbar_init(bar_load, 1);
+    mbar_init(bar_mma, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(tmem_slot, 256);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tO = tmem + 128;
+  uint32_t ph_load = 0, ph_mma = 0;
+
+  const int my_title = tid / T;                       // title slot of my row inside the tile
+  const bool row_in_tile = my_title < TP;
+  const int win_lo = my_title * T, win_hi = win_lo + T;   // my row may attend key columns [win_lo, win_hi)
+  // columns any row of this warp may need (warp-uniform chunk skipping)
+  const int w_lo = ((warp * 32) / T) * T;
+  const int w_hi = min(TP, (warp * 32 + 31) / T + 1) * T;
+
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int title0 = tile * TP;
+    const int row0 = title0 * T;
+    // key bias for the 128 key columns of this tile (key column tid and row tid belong to the same title slot)
+    bool my_uniform = false;
+    {
+      const int kt = tid / T;                         // title slot of key column `tid`
+      float bias = -INFINITY;
+      if (kt < TP && title0 + kt < n_eff) {
+        const int item = p.items ? p.items[title0 + kt] : (title0 + kt);
+        const int* mrow = p.mask_table ? p.mask_table + (size_t)item * T : nullptr;
+        bool any = false;
+        if (mrow) for (int j = 0; j < T; ++j) any |= (mrow[j] != 0);
+        const int mk = mrow ? mrow[tid - kt * T] : 1;
+        my_uniform = mrow && !any;                    // fully masked title: HF's soft-max of a constant row = uniform
+        bias = (mk != 0 || my_uniform) ? 0.f : -INFINITY;
+      }
+      sKeyBias[tid] = bias;
+    }
+    __syncthreads();
+    const bool row_ok = row_in_tile && (title0 + my_title) < n_eff;
+
+    for (int h = 0; h < heads; ++h) {
+      if (tid == 0) {
+        mbar_arrive_expect_tx(bar_load, 3 * 16384);
+        tma_load_2d(sQ, &tmap_qkv, bar_load, h * kAttHd, row0);
+        tma_load_2d(sK, &tmap_qkv, bar_load, hd_all + h * kAttHd, row0);
+        tma_load_2d(sV, &tmap_qkv, bar_load, 2 * hd_all + h * kAttHd, row0);
+      }
+      mbar_wait(bar_load, ph_load);
+      ph_load ^= 1;
+      if (tid == 0) {
+        tc_fence_after();
+        constexpr uint32_t id1 = att_idesc(128, 128, 0);
+        const uint32_t q = smem_u32(sQ), k = smem_u32(sK);
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+          umma_bf16_ss(tS, att_desc_k_sw128(q + ks * 32), att_desc_k_sw128(k + ks * 32), id1, ks > 0);
+        umma_commit(bar_mma);
+      }
+      mbar_wait(bar_mma, ph_mma);
+      ph_mma ^= 1;
+      tc_fence_after();
+
+      // ---- soft-max over my row (thread = row) ----
+      const uint32_t lane_base = ((uint32_t)(warp * 32) << 16);
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        if (c * 32 + 32 <= w_lo || c * 32 >= w_hi) continue;        // warp-uniform
+        uint32_t r[32];
+        tmem_ld_32x32(tS + lane_base + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int col = c * 32 + j;
+          const float s = (col >= win_lo && col < win_hi)
+                              ? (my_uniform ? 0.f : __uint_as_float(r[j]) * 0.125f + sKeyBias[col]) : -INFINITY;
+          mx = fmaxf(mx, s);
+        }
+      }
+      float l = 0.f;
+      const uint32_t prow = smem_u32(sP) + (uint32_t)tid * 128;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t packed[16];
+        if (c * 32 + 32 <= w_lo || c * 32 >= w_hi) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) packed[j] = 0u;
+        } else {
+          uint32_t r[32];
+          tmem_ld_32x32(tS + lane_base + c * 32, r);
+          tmem_ld_wait();
+          float e[32];
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int col = c * 32 + j;
+            const bool in = (col >= win_lo && col < win_hi) && row_in_tile;
+            const float s = my_uniform ? 0.f : __uint_as_float(r[j]) * 0.125f + sKeyBias[in ? col : 0];
+            e[j] = in ? __expf(s - mx) : 0.f;
+            l += e[j];
+          }
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const __nv_bfloat162 b2 = __floats2bfloat162_rn(e[2 * j], e[2 * j + 1]);
+            packed[j] = *reinterpret_cast<const uint32_t*>(&b2);
+          }
+        }
+        // 32 columns = 4 chunks of 16 bytes inside block (c / 2); chunk index XOR (row % 8) = 128B swizzle
+        const uint32_t blk = prow + (uint32_t)(c >> 1) * 16384;
+#pragma unroll
+        for (int q4 = 0; q4 < 4; ++q4) {
+          const uint32_t chunk = (uint32_t)((c & 1) * 4 + q4) ^ (uint32_t)(tid & 7);
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(blk + chunk * 16), "r"(packed[4 * q4]),
+                       "r"(packed[4 * q4 + 1]), "r"(packed[4 * q4 + 2]), "r"(packed[4 * q4 + 3])
+                       : "memory");
+        }
+      }
+      fence_proxy_async();                 // generic-proxy writes of P → visible to the tensor core (async proxy)
+      tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        tc_fence_after();
+        constexpr uint32_t id2 = att_idesc(128, 64, 1);
+        const uint32_t pa = smem_u32(sP), v = smem_u32(sV);
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks)
+          umma_bf16_ss(tO, att_desc_k_sw128(pa + (ks >> 2) * 16384 + (ks & 3) * 32), att_desc_mn_sw128(v + ks * 2048), id2, ks > 0);
+        umma_commit(bar_mma);
+      }
+      mbar_wait(bar_mma, ph_mma);
+      ph_mma ^= 1;
+      tc_fence_after();
+      // ---- epilogue: O / l → bf16 → global ----
+      {
+        const float inv = 1.f / l;
+        __nv_bfloat16* op = p.out + (size_t)(row0 + tid) * hd_all + h * kAttHd;
+#pragma unroll 1
+        for (int c = 0; c < 2; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tO + lane_base + c * 32, r);
+          tmem_ld_wait();
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 8) {
+              uint4 qv;
+              __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&qv);
+#pragma unroll
+              for (int t = 0; t < 4; ++t)
+                hh[t] = __floats2bfloat162_rn(__uint_as_float(r[j + 2 * t]) * inv, __uint_as_float(r[j + 2 * t + 1]) * inv);
+              *reinterpret_cast<uint4*>(op + c * 32 + j) = qv;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncthreads();                     // TMEM and shared tiles are free for the next head
+    }
+  }
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 256);
+  }
+}
+
+}  // namespace fr
+
+using namespace fr;
+
+// Tensor-core version of fr_bert_attention (same contract). T <= 64, head_dim 64.
+FR_API int fr_bert_attention_tc(const void* qkv, const int* mask_table, const int* items, const int* count_dev,
+                                int n_items, int T, int heads, int head_dim, void* out, void* stream) {
+  FR_REQUIRE(head_dim == kAttHd, "fr_bert_attention_tc: head_dim=%d (only 64 is built)", head_dim);
+  FR_REQUIRE(T >= 1 && T <= 64, "fr_bert_attention_tc: T=%d must be in [1,64]", T);
+  if (n_items == 0) return 0;
+  const int TP = kAttTile / T;
+  CUtensorMap tm;
+  if (int e = make_tmap_bf16_2d_box(&tm, qkv, (long long)n_items * T, 3LL * heads * kAttHd, 3LL * heads * kAttHd, kAttTile, 64)) return e;
+  AttParams p;
+  p.mask_table = mask_table; p.items = items; p.count_dev = count_dev; p.out = (__nv_bfloat16*)out;
+  p.n_items = n_items; p.T = T; p.heads = heads; p.TP = TP;
+  constexpr int smem = 81920 + 64 + 512 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    FR_CHECK(cudaFuncSetAttribute(bert_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  int tiles = (n_items + TP - 1) / TP;
+  int grid = tiles < 2 * kNumSMs ? tiles : 2 * kNumSMs;
+  bert_attention_tc_kernel<<<grid, 128, smem, (cudaStream_t)stream>>>(tm, p);
+  FR_LAUNCH_CHECK();
+  return 0;
+}

@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(kAttnWarps * 32) bert_attention_kernel(
           s = fmaf(q[2 * d], kf.x, s);
           s = fmaf(q[2 * d + 1], kf.y, s);
         }
+        if (!any) s = 0.f;                          // fully masked title: every score is the same constant in HF
         const float m_new = fmaxf(m, s);
         const float corr = __expf(m - m_new);
         const float p = __expf(s - m_new);

@@ -10,7 +10,7 @@
 // Structure: persistent, warp-specialised, one CTA per SM.
 //   warp 0      TMA producer   (one elected lane)  global → smem ring, kStages deep
 //   warp 1      MMA issuer     (one elected lane)  tcgen05.mma 128 x BN x 16, fp32 accumulators in TMEM
-//   warps 2..9  epilogue       tcgen05.ld → bias / GELU / tanh / residual → bf16|fp32 → global
+//   warps 2..17 epilogue       tcgen05.ld → bias / GELU / tanh / residual → bf16|fp32 → global
 // TMEM holds two accumulator stages (2 x BN columns) so the epilogue of tile i overlaps the MMAs of
 // tile i+1. M may be supplied from device memory (m_dev) so a CUDA-graph-captured step can run on the
 // de-duplicated row count of the current batch without a host round trip.
@@ -25,7 +25,7 @@ using namespace sm100;
 constexpr int BM = 128;
 constexpr int BK = 64;        // 64 bf16 = 128 bytes = one swizzle row
 constexpr int UMMA_K = 16;
-constexpr int kEpiWarps = 8;
+constexpr int kEpiWarps = 16;     // four per TMEM lane quarter: the epilogue is latency-bound, so more warps = more overlap
 constexpr int kThreads = 32 * (2 + kEpiWarps);
 
 enum Epilogue { EPI_BIAS = 0, EPI_BIAS_GELU = 1, EPI_BIAS_RESID = 2, EPI_BIAS_TANH = 3 };
@@ -47,7 +47,10 @@ struct Cfg {
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;   // BN in {64,128,256} → 128/256/512
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kColsPerWarp = BN / 4 < 32 ? 32 : BN / 4;       // columns one epilogue warp owns
+  static constexpr int kColGroups = BN / kColsPerWarp;                 // 4 (BN >= 128) or 2 (BN = 64)
+  static constexpr int kBiasBytes = kEpiWarps * kColsPerWarp * 4;      // per-warp bias staging
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kBiasBytes;
 };
 
 // erf via Abramowitz–Stegun 7.1.26 (|err| < 1.5e-7): two MUFU ops + a short polynomial, so the GELU
@@ -83,6 +86,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   uint64_t* tmem_full = empty_bar + C::kStages;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;           // [2]
   uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+  float* bias_stage = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -172,82 +176,98 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     }
   } else {
     // ------------------------------- epilogue -----------------------------------
-    const int ew = warp - 2;                 // 0..7
+    const int ew = warp - 2;                 // 0..15
     const int quarter = warp & 3;            // TMEM lane quarter this warp may touch
-    const int half = ew >> 2;                // which half of the BN columns
-    constexpr int kColsPerWarp = BN / 2;
+    const int cgroup = ew >> 2;              // which slice of the BN columns
+    constexpr int kCols = C::kColsPerWarp;
+    const bool active = cgroup < C::kColGroups;
+    float* my_bias = bias_stage + ew * kCols;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile / n_blocks) * BM;
       const int n0 = (tile % n_blocks) * BN;
-      mbar_wait(&tmem_full[acc], acc_phase);
-      tc_fence_after();
       const int row = m0 + quarter * 32 + lane;
       const bool row_ok = row < M;
+      const int wcol0 = n0 + cgroup * kCols;                 // first column of this warp
+      // While the MMAs of this tile are still running: stage the bias slice in shared memory and start the
+      // first residual load, so nothing on the critical path after the accumulator is ready waits on memory.
+      if (active) {
+        __syncwarp();
+#pragma unroll
+        for (int j = lane; j < kCols; j += 32) my_bias[j] = (p.bias && wcol0 + j < p.N) ? __ldg(p.bias + wcol0 + j) : 0.f;
+        __syncwarp();
+      }
+      uint4 rnext[4];
+      if (EPI == EPI_BIAS_RESID && active && row_ok && wcol0 < p.N) {
+        const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)row * p.ldr + wcol0);
+        const int nc = min(32, p.N - wcol0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) rnext[q] = (q * 8 < nc) ? __ldg(rp + q) : make_uint4(0, 0, 0, 0);
+      }
+      mbar_wait(&tmem_full[acc], acc_phase);
+      tc_fence_after();
+      if (active) {
 #pragma unroll 1
-      for (int cc = 0; cc < kColsPerWarp; cc += 32) {
-        const int col0 = n0 + half * kColsPerWarp + cc;
-        if (col0 >= p.N) break;              // warp-uniform
-        uint32_t r[32];
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + half * kColsPerWarp + cc);
-        tmem_ld_32x32(taddr, r);
-        tmem_ld_wait();
-        float v[32];
+        for (int cc = 0; cc < kCols; cc += 32) {
+          const int col0 = wcol0 + cc;
+          if (col0 >= p.N) break;              // warp-uniform
+          uint32_t r[32];
+          const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + cgroup * kCols + cc);
+          tmem_ld_32x32(taddr, r);
+          uint4 rcur[4];
+          if (EPI == EPI_BIAS_RESID) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-        const int ncols = min(32, p.N - col0);       // multiple of 8 (N % 8 == 0)
-        if (p.bias) {
+            for (int q = 0; q < 4; ++q) rcur[q] = rnext[q];
+            if (cc + 32 < kCols && col0 + 32 < p.N && row_ok) {       // prefetch the next chunk's residual
+              const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)row * p.ldr + col0 + 32);
+              const int nc = min(32, p.N - col0 - 32);
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            if (j < ncols) {
-              const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + j));
-              v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+              for (int q = 0; q < 4; ++q) rnext[q] = (q * 8 < nc) ? __ldg(rp + q) : make_uint4(0, 0, 0, 0);
             }
           }
-        }
-        if (EPI == EPI_BIAS_RESID) {
-          if (row_ok) {
-            const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)row * p.ldr + col0);
+          tmem_ld_wait();
+          float v[32];
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              if (j < ncols) {
-                const uint4 q = __ldg(rp + j / 8);
-                const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + my_bias[cc + j];
+          const int ncols = min(32, p.N - col0);       // multiple of 8 (N % 8 == 0)
+          if (EPI == EPI_BIAS_RESID) {
 #pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                  const float2 f = __bfloat1622float2(h[t]);
-                  v[j + 2 * t] += f.x;
-                  v[j + 2 * t + 1] += f.y;
-                }
+            for (int q = 0; q < 4; ++q) {
+              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rcur[q]);
+#pragma unroll
+              for (int t = 0; t < 4; ++t) {
+                const float2 f = __bfloat1622float2(h[t]);
+                v[q * 8 + 2 * t] += f.x;
+                v[q * 8 + 2 * t + 1] += f.y;
               }
             }
           }
-        }
-        if (EPI == EPI_BIAS_GELU) {
+          if (EPI == EPI_BIAS_GELU) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-        }
-        if (EPI == EPI_BIAS_TANH) {
+            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+          }
+          if (EPI == EPI_BIAS_TANH) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = tanh_fast(v[j]);
-        }
-        if (row_ok) {
-          if (OUT_F32) {
-            float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0);
+            for (int j = 0; j < 32; ++j) v[j] = tanh_fast(v[j]);
+          }
+          if (row_ok) {
+            if (OUT_F32) {
+              float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0);
 #pragma unroll
-            for (int j = 0; j < 32; j += 4)
-              if (j < ncols) op[j / 4] = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-          } else {
-            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + col0);
+              for (int j = 0; j < 32; j += 4)
+                if (j < ncols) op[j / 4] = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + col0);
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              if (j < ncols) {
-                uint4 q;
-                __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
+              for (int j = 0; j < 32; j += 8) {
+                if (j < ncols) {
+                  uint4 q;
+                  __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&q);
 #pragma unroll
-                for (int t = 0; t < 4; ++t) h[t] = __floats2bfloat162_rn(v[j + 2 * t], v[j + 2 * t + 1]);
-                op[j / 8] = q;
+                  for (int t = 0; t < 4; ++t) h[t] = __floats2bfloat162_rn(v[j + 2 * t], v[j + 2 * t + 1]);
+                  op[j / 8] = q;
+                }
               }
             }
           }

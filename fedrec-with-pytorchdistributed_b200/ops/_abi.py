@@ -26,6 +26,7 @@ SIGNATURES = {
     "fr_bert_embed_ln": (I, [P, P, P, I, I, P, P, P, P, P, F, I, P]),
     "fr_layernorm_bf16": (I, [P, P, P, P, I, P, I, F, I, P]),
     "fr_bert_attention": (I, [P, P, P, P, I, I, I, I, P, P]),
+    "fr_bert_attention_tc": (I, [P, P, P, P, I, I, I, I, P, P]),
     "fr_text_pool": (I, [P, P, P, P, P, P, P, I, I, I, I, P, P, P]),
     "fr_cast_f32_to_bf16": (I, [P, P, LL, P]),
     "fr_text_pool_bwd": (I, [P, P, P, P, P, P, I, I, I, I, P, P, P, P]),

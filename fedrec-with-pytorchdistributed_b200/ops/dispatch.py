@@ -1,6 +1,7 @@
 """Device dispatch: CUDA tensors → sm_100a kernels (mandatory), CPU tensors → ``ops.reference``."""
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -191,9 +192,12 @@ def layernorm_bf16(x, gamma, beta, out=None, count=None, rows_per_item=1, eps=1e
     return out
 
 
-def bert_attention(qkv, mask_table, items, count, n_items, T, heads, out):
+def bert_attention(qkv, mask_table, items, count, n_items, T, heads, out, impl: Optional[str] = None):
+    """Title self-attention. ``impl``: "tc" (tcgen05, default) or "simt" (CUDA-core kernel); FEDREC_ATTN overrides."""
     lib = require_native()
-    check(lib.fr_bert_attention(qkv.data_ptr(), _p(mask_table), _p(items), _p(count), n_items, T, heads,
+    impl = impl or os.environ.get("FEDREC_ATTN", "tc")
+    fn = lib.fr_bert_attention_tc if impl == "tc" else lib.fr_bert_attention
+    check(fn(qkv.data_ptr(), _p(mask_table), _p(items), _p(count), n_items, T, heads,
                                 qkv.shape[1] // (3 * heads), out.data_ptr(), stream_ptr(out.device)), "fr_bert_attention")
     count_launches(1)
     return out

@@ -75,6 +75,12 @@ int fr_layernorm_bf16(const void* in, void* out, const float* gamma, const float
 int fr_bert_attention(const void* qkv, const int* mask_table, const int* items, const int* count_dev, int n_items,
                       int T, int heads, int head_dim, void* out, void* stream);
 
+/* The same attention on the tensor cores (csrc/bert_attention_sm100.cu): floor(128/T) titles share one 128-row
+ * tile, S = QK^T and O = PV are tcgen05.mma with TMEM accumulators, P goes through shared memory in the swizzled
+ * K-major layout. Same arguments and results as fr_bert_attention; this is the default path. */
+int fr_bert_attention_tc(const void* qkv, const int* mask_table, const int* items, const int* count_dev, int n_items,
+                         int T, int heads, int head_dim, void* out, void* stream);
+
 /* Text-head additive pooling: alpha = exp(e.w2+b2)/(sum+1e-8) over T, pooled = sum alpha*h. e comes from the GEMM
  * with the tanh epilogue. Replaces attention.py:18-25 as called from encoder.py:28. */
 int fr_text_pool(const void* hidden, const void* e, const float* w2, const float* b2, const int* mask_table,

@@ -51,19 +51,45 @@ def test_embed_ln(model):
     torch.testing.assert_close(out.float(), want, atol=4e-2, rtol=3e-2)
 
 
-def test_attention(model):
+@pytest.mark.parametrize("impl", ["tc", "simt"])
+@pytest.mark.parametrize("n,first", [(9, 1), (301, 0), (4, 0)])
+def test_attention(model, impl, n, first):
     torch.manual_seed(3)
-    n, T, H = 9, 30, 12
+    T, H = 30, 12
     qkv = (torch.randn(n * T, 2304, device=DEV) * 0.7).bfloat16()
-    items = torch.arange(1, n + 1, device=DEV, dtype=torch.int32)
+    items = torch.arange(first, first + n, device=DEV, dtype=torch.int32)      # first=0 includes the all-masked <unk> row
     out = torch.zeros(n * T, 768, device=DEV, dtype=torch.bfloat16)
-    D.bert_attention(qkv, model.news_mask, items, None, n, T, H, out)
+    D.bert_attention(qkv, model.news_mask, items, None, n, T, H, out, impl=impl)
     q, k, v = [t.float().view(n, T, H, 64).transpose(1, 2) for t in qkv.split(768, dim=1)]
     mask = model.news_mask[items.long()]
     s = (q / 8.0) @ k.transpose(-1, -2)
     s = s.masked_fill((mask == 0)[:, None, None, :], torch.finfo(torch.float32).min)
     want = (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(n * T, 768)
     torch.testing.assert_close(out.float(), want, atol=2e-2, rtol=2e-2)
+    if n > 100:                                                                # device-side count: rows past it stay untouched
+        cnt = torch.tensor([77], device=DEV, dtype=torch.int32)
+        out2 = torch.zeros_like(out)
+        D.bert_attention(qkv, model.news_mask, items, cnt, n, T, H, out2, impl=impl)
+        assert torch.equal(out2[: 77 * T], out[: 77 * T]) and (out2[77 * T:] == 0).all()
+
+
+def test_attention_other_title_lengths():
+    torch.manual_seed(4)
+    for T in (50, 64, 17):
+        n, H = 21, 12
+        qkv = (torch.randn(n * T, 2304, device=DEV) * 0.7).bfloat16()
+        mask = (torch.rand(n, T, device=DEV) > 0.3).int()
+        mask[:, 0] = 1
+        outs = []
+        for impl in ("tc", "simt"):
+            out = torch.zeros(n * T, 768, device=DEV, dtype=torch.bfloat16)
+            D.bert_attention(qkv, mask, None, None, n, T, H, out, impl=impl)
+            outs.append(out.float())
+        q, k, v = [t.float().view(n, T, H, 64).transpose(1, 2) for t in qkv.split(768, dim=1)]
+        s = ((q / 8.0) @ k.transpose(-1, -2)).masked_fill((mask == 0)[:, None, None, :], torch.finfo(torch.float32).min)
+        want = (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(n * T, 768)
+        for o in outs:
+            torch.testing.assert_close(o, want, atol=2e-2, rtol=2e-2)
 
 
 def test_trunk_and_head_match_module(model):
