@@ -198,34 +198,24 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         for (int j = lane; j < kCols; j += 32) my_bias[j] = (p.bias && wcol0 + j < p.N) ? __ldg(p.bias + wcol0 + j) : 0.f;
         __syncwarp();
       }
-      uint4 rnext[4];
-      if (EPI == EPI_BIAS_RESID && active && row_ok && wcol0 < p.N) {
+      // the whole residual slice of this thread's row (kCols bf16) is fetched now, while the tensor core still works
+      uint4 rres[kCols / 8];
+      if (EPI == EPI_BIAS_RESID && active) {
         const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)row * p.ldr + wcol0);
-        const int nc = min(32, p.N - wcol0);
 #pragma unroll
-        for (int q = 0; q < 4; ++q) rnext[q] = (q * 8 < nc) ? __ldg(rp + q) : make_uint4(0, 0, 0, 0);
+        for (int q = 0; q < kCols / 8; ++q)
+          rres[q] = (row_ok && wcol0 + q * 8 < p.N) ? __ldg(rp + q) : make_uint4(0, 0, 0, 0);
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
       if (active) {
-#pragma unroll 1
+#pragma unroll
         for (int cc = 0; cc < kCols; cc += 32) {
           const int col0 = wcol0 + cc;
           if (col0 >= p.N) break;              // warp-uniform
           uint32_t r[32];
           const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + cgroup * kCols + cc);
           tmem_ld_32x32(taddr, r);
-          uint4 rcur[4];
-          if (EPI == EPI_BIAS_RESID) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) rcur[q] = rnext[q];
-            if (cc + 32 < kCols && col0 + 32 < p.N && row_ok) {       // prefetch the next chunk's residual
-              const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)row * p.ldr + col0 + 32);
-              const int nc = min(32, p.N - col0 - 32);
-#pragma unroll
-              for (int q = 0; q < 4; ++q) rnext[q] = (q * 8 < nc) ? __ldg(rp + q) : make_uint4(0, 0, 0, 0);
-            }
-          }
           tmem_ld_wait();
           float v[32];
 #pragma unroll
@@ -234,7 +224,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           if (EPI == EPI_BIAS_RESID) {
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rcur[q]);
+              const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&rres[cc / 8 + q]);
 #pragma unroll
               for (int t = 0; t < 4; ++t) {
                 const float2 f = __bfloat1622float2(h[t]);
