@@ -54,8 +54,9 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   uint8_t* sK = smem + 16384;
   uint8_t* sV = smem + 32768;             // tokens x 64: MN-major SW128 for the second MMA
   uint8_t* sP = smem + 49152;             // 128 x 128 bf16 as two K-major SW128 blocks of 64 columns
-  uint64_t* bar_load = reinterpret_cast<uint64_t*>(smem + 81920);
-  uint64_t* bar_mma = bar_load + 1;
+  uint64_t* bar_qk = reinterpret_cast<uint64_t*>(smem + 81920);    // Q and K of the next (tile, head) have landed
+  uint64_t* bar_v = bar_qk + 1;                                     // V of the next (tile, head) has landed
+  uint64_t* bar_mma = bar_v + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mma + 1);
   float* sKeyBias = reinterpret_cast<float*>(tmem_slot + 2);     // [128] 0 or -inf per key column of the tile
 
@@ -67,7 +68,8 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
 
   if (tid == 0) {
     prefetch_tmap(&tmap_qkv);
-    mbar_init(bar_load, 1);
+    mbar_init(bar_qk, 1);
+    mbar_init(bar_v, 1);
     mbar_init(bar_mma, 1);
     fence_barrier_init();
   }
@@ -80,7 +82,24 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem, tO = tmem + 128;
-  uint32_t ph_load = 0, ph_mma = 0;
+  uint32_t ph_qk = 0, ph_v = 0, ph_mma = 0;
+  // Loads run one (tile, head) ahead of the math: Q/K of the next job are requested as soon as S = QK^T has been
+  // produced (their buffers are free), V as soon as O = PV has been produced.
+  auto load_qk = [&](int tile_, int h_) {
+    const int r0 = tile_ * TP * T;
+    mbar_arrive_expect_tx(bar_qk, 2 * 16384);
+    tma_load_2d(sQ, &tmap_qkv, bar_qk, h_ * kAttHd, r0);
+    tma_load_2d(sK, &tmap_qkv, bar_qk, hd_all + h_ * kAttHd, r0);
+  };
+  auto load_v = [&](int tile_, int h_) {
+    const int r0 = tile_ * TP * T;
+    mbar_arrive_expect_tx(bar_v, 16384);
+    tma_load_2d(sV, &tmap_qkv, bar_v, 2 * hd_all + h_ * kAttHd, r0);
+  };
+  if (tid == 0 && (int)blockIdx.x < num_tiles) {
+    load_qk(blockIdx.x, 0);
+    load_v(blockIdx.x, 0);
+  }
 
   const int my_title = tid / T;                       // title slot of my row inside the tile
   const bool row_in_tile = my_title < TP;
@@ -112,14 +131,12 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
     const bool row_ok = row_in_tile && (title0 + my_title) < n_eff;
 
     for (int h = 0; h < heads; ++h) {
-      if (tid == 0) {
-        mbar_arrive_expect_tx(bar_load, 3 * 16384);
-        tma_load_2d(sQ, &tmap_qkv, bar_load, h * kAttHd, row0);
-        tma_load_2d(sK, &tmap_qkv, bar_load, hd_all + h * kAttHd, row0);
-        tma_load_2d(sV, &tmap_qkv, bar_load, 2 * hd_all + h * kAttHd, row0);
-      }
-      mbar_wait(bar_load, ph_load);
-      ph_load ^= 1;
+      // the job after this one (next head, or head 0 of this CTA's next tile)
+      const int nh = (h + 1 < heads) ? h + 1 : 0;
+      const int ntile = (h + 1 < heads) ? tile : tile + (int)gridDim.x;
+      const bool has_next = ntile < num_tiles;
+      mbar_wait(bar_qk, ph_qk);
+      ph_qk ^= 1;
       if (tid == 0) {
         tc_fence_after();
         constexpr uint32_t id1 = att_idesc(128, 128, 0);
@@ -132,6 +149,7 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
       mbar_wait(bar_mma, ph_mma);
       ph_mma ^= 1;
       tc_fence_after();
+      if (tid == 0 && has_next) load_qk(ntile, nh);          // sQ / sK are free again
 
       // ---- soft-max over my row (thread = row) ----
       const uint32_t lane_base = ((uint32_t)(warp * 32) << 16);
@@ -191,6 +209,7 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
       tc_fence_before();
       __syncthreads();
       if (tid == 0) {
+        mbar_wait(bar_v, ph_v);
         tc_fence_after();
         constexpr uint32_t id2 = att_idesc(128, 64, 1);
         const uint32_t pa = smem_u32(sP), v = smem_u32(sV);
@@ -199,9 +218,11 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
           umma_bf16_ss(tO, att_desc_k_sw128(pa + (ks >> 2) * 16384 + (ks & 3) * 32), att_desc_mn_sw128(v + ks * 2048), id2, ks > 0);
         umma_commit(bar_mma);
       }
+      ph_v ^= 1;
       mbar_wait(bar_mma, ph_mma);
       ph_mma ^= 1;
       tc_fence_after();
+      if (tid == 0 && has_next) load_v(ntile, nh);           // sV is free again
       // ---- epilogue: O / l → bf16 → global ----
       {
         const float inv = 1.f / l;

@@ -10,14 +10,18 @@
 // Structure: persistent, warp-specialised, one CTA per SM.
 //   warp 0      TMA producer   (one elected lane)  global → smem ring, kStages deep
 //   warp 1      MMA issuer     (one elected lane)  tcgen05.mma 128 x BN x 16, fp32 accumulators in TMEM
-//   warps 2..17 epilogue       tcgen05.ld → bias / GELU / tanh / residual → bf16|fp32 → global
+//   warps 2..17 epilogue       tcgen05.ld → bias / GELU / tanh / residual → bf16|fp32 → global.
+//                              bf16 outputs with BN >= 128 go through a per-warp swizzled staging box in shared
+//                              memory and leave with a TMA store (and the residual arrives by a TMA load into the
+//                              same box), so the epilogue issues no per-row global loads or stores at all.
 // TMEM holds two accumulator stages (2 x BN columns) so the epilogue of tile i overlaps the MMAs of
 // tile i+1. M may be supplied from device memory (m_dev) so a CUDA-graph-captured step can run on the
 // de-duplicated row count of the current batch without a host round trip.
 #include "sm100.cuh"
 #include <cuda.h>
 #include <mutex>
-#include <unordered_map>
+#include <stdlib.h>
+#include <string.h>
 
 namespace fr {
 using namespace sm100;
@@ -40,9 +44,9 @@ struct GemmParams {
   int ldo, ldr;
 };
 
-template <int BN>
+template <int BN, bool TMA_EPI>
 struct Cfg {
-  static constexpr int kStages = BN >= 256 ? 4 : (BN >= 128 ? 6 : 8);
+  static constexpr int kStages = TMA_EPI ? (BN >= 256 ? 3 : 4) : (BN >= 256 ? 4 : (BN >= 128 ? 6 : 8));
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = BN * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
@@ -50,7 +54,9 @@ struct Cfg {
   static constexpr int kColsPerWarp = BN / 4 < 32 ? 32 : BN / 4;       // columns one epilogue warp owns
   static constexpr int kColGroups = BN / kColsPerWarp;                 // 4 (BN >= 128) or 2 (BN = 64)
   static constexpr int kBiasBytes = kEpiWarps * kColsPerWarp * 4;      // per-warp bias staging
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/ + kBiasBytes;
+  static constexpr int kBoxBytes = 4096;                               // per-warp output box: 32 rows x (64|32) bf16
+  static constexpr int kStagingBytes = TMA_EPI ? kEpiWarps * kBoxBytes : 0;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/ + kBiasBytes;
 };
 
 // erf via Abramowitz–Stegun 7.1.26 (|err| < 1.5e-7): two MUFU ops + a short polynomial, so the GELU
@@ -73,20 +79,31 @@ __device__ __forceinline__ float tanh_fast(float x) {
   return y;
 }
 
-template <int BN, int EPI, bool OUT_F32>
+// byte offset of 16-byte unit j of row r inside a swizzled staging box (rows of kCols bf16)
+template <int kCols>
+__device__ __forceinline__ uint32_t box_off(int r, int j) {
+  if (kCols == 64) return (uint32_t)(r * 128 + ((j ^ (r & 7)) << 4));          // SWIZZLE_128B
+  return (uint32_t)(r * 64 + ((j ^ ((r >> 1) & 3)) << 4));                       // SWIZZLE_64B
+}
+
+template <int BN, int EPI, bool OUT_F32, bool TMA_EPI>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                    const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_r,
                     const GemmParams p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, TMA_EPI>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::kStages * C::kStageBytes);
+  uint8_t* staging = smem + C::kStages * C::kStageBytes;                     // 1024-aligned (stage sizes are)
+  uint8_t* ctrl = staging + C::kStagingBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(ctrl);
   uint64_t* empty_bar = full_bar + C::kStages;
   uint64_t* tmem_full = empty_bar + C::kStages;   // [2]
   uint64_t* tmem_empty = tmem_full + 2;           // [2]
-  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(tmem_empty + 2);
-  float* bias_stage = reinterpret_cast<float*>(smem + C::kStages * C::kStageBytes + 256);
+  uint64_t* resid_bar = tmem_empty + 2;           // [kEpiWarps]
+  uint32_t* tmem_base_slot = reinterpret_cast<uint32_t*>(resid_bar + kEpiWarps);
+  float* bias_stage = reinterpret_cast<float*>(ctrl + 512);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -104,6 +121,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
     prefetch_tmap(&tmap_b);
+    if (TMA_EPI) {
+      prefetch_tmap(&tmap_o);
+      if (EPI == EPI_BIAS_RESID) prefetch_tmap(&tmap_r);
+    }
   }
   if (warp == 1) {
     if (lane == 0) {
@@ -115,6 +136,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         mbar_init(&tmem_full[i], 1);
         mbar_init(&tmem_empty[i], kEpiWarps);
       }
+      for (int i = 0; i < kEpiWarps; ++i) mbar_init(&resid_bar[i], 1);
       fence_barrier_init();
     }
     __syncwarp();
@@ -182,25 +204,37 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     constexpr int kCols = C::kColsPerWarp;
     const bool active = cgroup < C::kColGroups;
     float* my_bias = bias_stage + ew * kCols;
+    uint8_t* my_box = staging + (TMA_EPI ? ew * C::kBoxBytes : 0);
+    const uint32_t box_u32 = smem_u32(my_box);
+    uint32_t rphase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int m0 = (tile / n_blocks) * BM;
       const int n0 = (tile % n_blocks) * BN;
-      const int row = m0 + quarter * 32 + lane;
+      const int brow0 = m0 + quarter * 32;                   // first row of this warp's 32-row box
+      const int row = brow0 + lane;
       const bool row_ok = row < M;
       const int wcol0 = n0 + cgroup * kCols;                 // first column of this warp
-      // While the MMAs of this tile are still running: stage the bias slice in shared memory and start the
-      // first residual load, so nothing on the critical path after the accumulator is ready waits on memory.
-      if (active) {
+      const bool work = active && wcol0 < p.N;               // warp-uniform
+      const bool box_full = brow0 + 32 <= M;                 // TMA store may cover the whole box
+      // While the MMAs of this tile are still running: stage the bias slice, make sure the previous TMA store has
+      // drained this warp's box, and start the residual load — nothing after "accumulator ready" waits on memory.
+      if (work) {
         __syncwarp();
 #pragma unroll
         for (int j = lane; j < kCols; j += 32) my_bias[j] = (p.bias && wcol0 + j < p.N) ? __ldg(p.bias + wcol0 + j) : 0.f;
+        if (TMA_EPI && lane == 0) {
+          tma_store_wait_read<0>();
+          if (EPI == EPI_BIAS_RESID) {
+            mbar_arrive_expect_tx(&resid_bar[ew], 32 * kCols * 2);
+            tma_load_2d(my_box, &tmap_r, &resid_bar[ew], wcol0, brow0);
+          }
+        }
         __syncwarp();
       }
-      // the whole residual slice of this thread's row (kCols bf16) is fetched now, while the tensor core still works
       uint4 rres[kCols / 8];
-      if (EPI == EPI_BIAS_RESID && active) {
+      if (!TMA_EPI && EPI == EPI_BIAS_RESID && work) {
         const uint4* rp = reinterpret_cast<const uint4*>(p.resid + (size_t)row * p.ldr + wcol0);
 #pragma unroll
         for (int q = 0; q < kCols / 8; ++q)
@@ -208,7 +242,14 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
-      if (active) {
+      if (work) {
+        if (TMA_EPI && EPI == EPI_BIAS_RESID) {
+          mbar_wait(&resid_bar[ew], rphase);
+          rphase ^= 1;
+        }
+        uint32_t packed[kCols / 2];                          // bf16x2 results of the whole slice (TMA path)
+#pragma unroll
+        for (int j = 0; j < kCols / 2; ++j) packed[j] = 0u;
 #pragma unroll
         for (int cc = 0; cc < kCols; cc += 32) {
           const int col0 = wcol0 + cc;
@@ -216,6 +257,15 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           uint32_t r[32];
           const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN + cgroup * kCols + cc);
           tmem_ld_32x32(taddr, r);
+          if (TMA_EPI && EPI == EPI_BIAS_RESID) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+              uint4 t4;
+              asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(t4.x), "=r"(t4.y), "=r"(t4.z), "=r"(t4.w)
+                           : "r"(box_u32 + box_off<kCols>(lane, cc / 8 + q)));
+              rres[cc / 8 + q] = t4;
+            }
+          }
           tmem_ld_wait();
           float v[32];
 #pragma unroll
@@ -241,7 +291,13 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
             for (int j = 0; j < 32; ++j) v[j] = tanh_fast(v[j]);
           }
-          if (row_ok) {
+          if (TMA_EPI) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const __nv_bfloat162 b2 = __floats2bfloat162_rn(v[2 * j], v[2 * j + 1]);
+              packed[cc / 2 + j] = *reinterpret_cast<const uint32_t*>(&b2);
+            }
+          } else if (row_ok) {
             if (OUT_F32) {
               float4* op = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldo + col0);
 #pragma unroll
@@ -262,12 +318,41 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
             }
           }
         }
+        // the accumulator has been read out: hand the TMEM stage back to the MMA warp before storing
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (TMA_EPI) {
+          if (box_full) {
+#pragma unroll
+            for (int q = 0; q < kCols / 8; ++q) {
+              {
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(box_u32 + box_off<kCols>(lane, q)),
+                             "r"(packed[4 * q]), "r"(packed[4 * q + 1]), "r"(packed[4 * q + 2]), "r"(packed[4 * q + 3])
+                             : "memory");
+              }
+            }
+            fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tmap_o, my_box, wcol0, brow0);     // columns past N are clipped by the tensor map
+              tma_store_commit();
+            }
+          } else if (row_ok) {                                   // last, partial row block under a device-side M
+            uint4* op = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldo + wcol0);
+#pragma unroll
+            for (int q = 0; q < kCols / 8; ++q)
+              if (wcol0 + q * 8 < p.N) op[q] = make_uint4(packed[4 * q], packed[4 * q + 1], packed[4 * q + 2], packed[4 * q + 3]);
+          }
+        }
+      } else {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&tmem_empty[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (TMA_EPI && lane == 0) tma_store_wait<0>();
   }
 
   tc_fence_before();
@@ -322,33 +407,50 @@ int make_tmap_bf16_2d_box(CUtensorMap* out, const void* base, long long rows, lo
   return 0;
 }
 
-template <int BN, int EPI, bool OUT_F32>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int max_ctas, cudaStream_t s) {
-  auto kern = gemm_bf16_tn_kernel<BN, EPI, OUT_F32>;
+struct Maps { CUtensorMap a, b, o, r; };
+
+template <int BN, int EPI, bool OUT_F32, bool TMA_EPI>
+static int launch(const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t s) {
+  auto kern = gemm_bf16_tn_kernel<BN, EPI, OUT_F32, TMA_EPI>;
+  using C = Cfg<BN, TMA_EPI>;
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
-    FR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::kSmemBytes));
+    FR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_set = true;
   }
   const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
   int grid = tiles < max_ctas ? tiles : max_ctas;
   if (grid < 1) grid = 1;
-  kern<<<grid, kThreads, Cfg<BN>::kSmemBytes, s>>>(ta, tb, p);
+  kern<<<grid, kThreads, C::kSmemBytes, s>>>(m.a, m.b, m.o, m.r, p);
   FR_LAUNCH_CHECK();
   return 0;
 }
 
-template <int BN, bool OUT_F32>
-static int dispatch_epi(int epi, const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int max_ctas,
-                        cudaStream_t s) {
+template <int BN, bool OUT_F32, bool TMA_EPI>
+static int dispatch_epi(int epi, const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t s) {
   switch (epi) {
-    case EPI_BIAS: return launch<BN, EPI_BIAS, OUT_F32>(ta, tb, p, max_ctas, s);
-    case EPI_BIAS_GELU: return launch<BN, EPI_BIAS_GELU, OUT_F32>(ta, tb, p, max_ctas, s);
-    case EPI_BIAS_RESID: return launch<BN, EPI_BIAS_RESID, OUT_F32>(ta, tb, p, max_ctas, s);
-    case EPI_BIAS_TANH: return launch<BN, EPI_BIAS_TANH, OUT_F32>(ta, tb, p, max_ctas, s);
+    case EPI_BIAS: return launch<BN, EPI_BIAS, OUT_F32, TMA_EPI>(m, p, max_ctas, s);
+    case EPI_BIAS_GELU: return launch<BN, EPI_BIAS_GELU, OUT_F32, TMA_EPI>(m, p, max_ctas, s);
+    case EPI_BIAS_RESID: return launch<BN, EPI_BIAS_RESID, OUT_F32, TMA_EPI>(m, p, max_ctas, s);
+    case EPI_BIAS_TANH: return launch<BN, EPI_BIAS_TANH, OUT_F32, TMA_EPI>(m, p, max_ctas, s);
   }
   fr::set_error("fr_gemm_bf16: unknown epilogue %d", epi);
   return -1;
+}
+
+// generic 2D bf16 map with an explicit swizzle mode (epilogue boxes)
+static int make_tmap_box_swz(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows,
+                             int box_cols, CUtensorMapSwizzle swz) {
+  PFN_encodeTiled enc = get_encode();
+  FR_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  FR_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (epilogue box) failed with CUresult %d", (int)r);
+  return 0;
 }
 
 static int sm_count() {
@@ -387,9 +489,20 @@ FR_API int fr_gemm_bf16(const void* A, const void* W, const float* bias, const v
     block_n = best;
   }
   FR_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "fr_gemm_bf16: block_n=%d", block_n);
-  CUtensorMap ta, tb;
-  if (int e = make_tmap_bf16_2d(&ta, A, M, K, lda, BM)) return e;
-  if (int e = make_tmap_bf16_2d(&tb, W, N, K, ldw, block_n)) return e;
+  Maps maps;
+  if (int e = make_tmap_bf16_2d(&maps.a, A, M, K, lda, BM)) return e;
+  if (int e = make_tmap_bf16_2d(&maps.b, W, N, K, ldw, block_n)) return e;
+  // bf16 outputs of the wide tiles leave through shared memory + TMA (FEDREC_GEMM_EPI=direct disables it)
+  static const bool allow_tma_epi = [] { const char* e = getenv("FEDREC_GEMM_EPI"); return !(e && strcmp(e, "direct") == 0); }();
+  const bool tma_epi = allow_tma_epi && !out_fp32 && block_n >= 128;
+  maps.o = maps.a; maps.r = maps.a;
+  if (tma_epi) {
+    const int kc = block_n / 4;
+    const CUtensorMapSwizzle swz = kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
+    if (int e = make_tmap_box_swz(&maps.o, out, M, N, ldo, 32, kc, swz)) return e;
+    if (epi == EPI_BIAS_RESID)
+      if (int e = make_tmap_box_swz(&maps.r, resid, M, N, ldr, 32, kc, swz)) return e;
+  }
   GemmParams p;
   p.bias = bias; p.resid = (const __nv_bfloat16*)resid; p.out = out; p.m_dev = m_dev; p.m_scale = m_scale;
   p.M = M; p.N = N; p.K = K; p.ldo = ldo; p.ldr = ldr;
@@ -397,14 +510,18 @@ FR_API int fr_gemm_bf16(const void* A, const void* W, const float* bias, const v
   const int ctas = sm_count();
   if (out_fp32) {
     switch (block_n) {
-      case 64: return dispatch_epi<64, true>(epi, ta, tb, p, ctas, s);
-      case 128: return dispatch_epi<128, true>(epi, ta, tb, p, ctas, s);
-      default: return dispatch_epi<256, true>(epi, ta, tb, p, ctas, s);
+      case 64: return dispatch_epi<64, true, false>(epi, maps, p, ctas, s);
+      case 128: return dispatch_epi<128, true, false>(epi, maps, p, ctas, s);
+      default: return dispatch_epi<256, true, false>(epi, maps, p, ctas, s);
     }
   }
+  if (tma_epi) {
+    if (block_n == 128) return dispatch_epi<128, false, true>(epi, maps, p, ctas, s);
+    return dispatch_epi<256, false, true>(epi, maps, p, ctas, s);
+  }
   switch (block_n) {
-    case 64: return dispatch_epi<64, false>(epi, ta, tb, p, ctas, s);
-    case 128: return dispatch_epi<128, false>(epi, ta, tb, p, ctas, s);
-    default: return dispatch_epi<256, false>(epi, ta, tb, p, ctas, s);
+    case 64: return dispatch_epi<64, false, false>(epi, maps, p, ctas, s);
+    case 128: return dispatch_epi<128, false, false>(epi, maps, p, ctas, s);
+    default: return dispatch_epi<256, false, false>(epi, maps, p, ctas, s);
   }
 }

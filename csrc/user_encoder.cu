@@ -37,7 +37,9 @@ __device__ __forceinline__ float4 dropout_mult4(const Philox& rng, uint64_t idx4
 // X[b*L + l, :] = bf16( dropout( news_vecs[inv_his[b*L + l], :] ) )
 __global__ void __launch_bounds__(256) ue_gather_dropout_kernel(const float* __restrict__ news_vecs, const int* __restrict__ inv_his,
                                                                 __nv_bfloat16* __restrict__ X, int rows, int D4, float p,
-                                                                unsigned long long seed) {
+                                                                unsigned long long seed,
+                                                                const unsigned long long* __restrict__ seed_dev) {
+  if (seed_dev) seed += *seed_dev;            // per-replay salt when the step lives in a CUDA graph
   const Philox rng(seed);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   const size_t total = (size_t)rows * D4;
@@ -59,7 +61,9 @@ __global__ void __launch_bounds__(256) ue_gather_dropout_kernel(const float* __r
 __global__ void __launch_bounds__(256) ue_scatter_dx_kernel(const float* __restrict__ dX, const int* __restrict__ inv_his,
                                                             float* __restrict__ d_news, int rows, int D4, float p,
                                                             unsigned long long seed, float noise_std,
-                                                            unsigned long long noise_seed) {
+                                                            unsigned long long noise_seed,
+                                                            const unsigned long long* __restrict__ seed_dev) {
+  if (seed_dev) { seed += *seed_dev; noise_seed += *seed_dev; }
   const Philox rng(seed), nrng(noise_seed);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
   const size_t total = (size_t)rows * D4;
@@ -259,6 +263,7 @@ struct PoolScoreArgs {
   int B, L, C, D, Q, use_mask, train;
   float noise_std;
   unsigned long long noise_seed;
+  const unsigned long long* seed_dev;
 };
 
 __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs a) {
@@ -327,7 +332,7 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   __syncthreads();
   // d_cand_c = ds_c * u → scattered into d_news ; d_u = sum_c ds_c cand_c
   {
-    const Philox nrng(a.noise_seed);
+    const Philox nrng(a.noise_seed + (a.seed_dev ? *a.seed_dev : 0ull));
     const int D4 = D / 4;
     for (int i = tid; i < C * D4; i += 128) {
       const int c = i / D4, q = i - c * D4;
@@ -446,26 +451,36 @@ __global__ void __launch_bounds__(256) transpose_cast_kernel(const float* __rest
 
 using namespace fr;
 
+__global__ void counter_advance_kernel(unsigned long long* ctr, unsigned long long inc) { *ctr += inc; }
+
+// *ctr += inc on the stream: the per-step salt of the RNG streams when a step is replayed from a CUDA graph.
+FR_API int fr_counter_advance(unsigned long long* ctr, unsigned long long inc, void* stream) {
+  counter_advance_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ctr, inc);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
 FR_API int fr_ue_gather_dropout(const float* news_vecs, const int* inv_his, void* X, int rows, int D, float p,
-                                unsigned long long seed, void* stream) {
+                                unsigned long long seed, const unsigned long long* seed_dev, void* stream) {
   FR_REQUIRE(D % 4 == 0 && p >= 0.f && p < 1.f, "fr_ue_gather_dropout: D=%d p=%f", D, p);
   if (rows == 0) return 0;
   const size_t total = (size_t)rows * (D / 4);
   int blocks = (int)((total + 255) / 256);
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-  ue_gather_dropout_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(news_vecs, inv_his, (__nv_bfloat16*)X, rows, D / 4, p, seed);
+  ue_gather_dropout_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(news_vecs, inv_his, (__nv_bfloat16*)X, rows, D / 4, p, seed, seed_dev);
   FR_LAUNCH_CHECK();
   return 0;
 }
 
 FR_API int fr_ue_scatter_dx(const float* dX, const int* inv_his, float* d_news, int rows, int D, float p,
-                            unsigned long long seed, float noise_std, unsigned long long noise_seed, void* stream) {
+                            unsigned long long seed, float noise_std, unsigned long long noise_seed,
+                            const unsigned long long* seed_dev, void* stream) {
   FR_REQUIRE(D % 4 == 0, "fr_ue_scatter_dx: D=%d", D);
   if (rows == 0) return 0;
   const size_t total = (size_t)rows * (D / 4);
   int blocks = (int)((total + 255) / 256);
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-  ue_scatter_dx_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dX, inv_his, d_news, rows, D / 4, p, seed, noise_std, noise_seed);
+  ue_scatter_dx_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dX, inv_his, d_news, rows, D / 4, p, seed, noise_std, noise_seed, seed_dev);
   FR_LAUNCH_CHECK();
   return 0;
 }
@@ -505,7 +520,7 @@ FR_API int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, con
                             const int* inv_cand, const int* his_ids, float* score, float* loss_mean, float* user_vec,
                             void* d_ctx_pool, void* d_pre, float* d_w2, float* d_b2, float* d_news, int B, int L, int C,
                             int D, int Q, int use_mask, int train, float noise_std, unsigned long long noise_seed,
-                            void* stream) {
+                            const unsigned long long* seed_dev, void* stream) {
   FR_REQUIRE(L >= 1 && L <= kMaxL && C >= 1 && C <= 32 && D <= 512 && D % 4 == 0 && Q <= 256, "fr_ue_pool_score: bad shape L=%d C=%d D=%d Q=%d", L, C, D, Q);
   FR_REQUIRE(!train || (d_ctx_pool && d_pre && d_w2 && d_b2 && d_news), "fr_ue_pool_score: backward outputs missing");
   FR_REQUIRE(!use_mask || his_ids, "fr_ue_pool_score: mask needs his_ids");
@@ -517,7 +532,7 @@ FR_API int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, con
   a.inv_cand = inv_cand; a.his_ids = his_ids; a.score = score; a.loss_mean = loss_mean; a.user_vec = user_vec;
   a.d_ctx_pool = (__nv_bfloat16*)d_ctx_pool; a.d_pre = (__nv_bfloat16*)d_pre; a.d_w2 = d_w2; a.d_b2 = d_b2; a.d_news = d_news;
   a.B = B; a.L = L; a.C = C; a.D = D; a.Q = Q; a.use_mask = use_mask; a.train = train; a.noise_std = noise_std;
-  a.noise_seed = noise_seed;
+  a.noise_seed = noise_seed; a.seed_dev = seed_dev;
   ue_pool_score_kernel<<<B, 128, 0, s>>>(a);
   FR_LAUNCH_CHECK();
   return 0;

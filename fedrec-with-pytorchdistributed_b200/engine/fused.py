@@ -71,6 +71,8 @@ class FusedStep:
         self._bufs: Dict[int, Dict[str, torch.Tensor]] = {}
         self._ubufs: Dict[tuple, Dict[str, torch.Tensor]] = {}
         self._step_no = 0
+        self._seed_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)   # RNG salt, bumped on the stream every step
+        self._graphs: Dict[tuple, dict] = {}
         self._dedup_ws: Optional[torch.Tensor] = None
         self._gen = torch.Generator(device=self.dev)
         self._gen.manual_seed(cfg.seed + 17)
@@ -173,7 +175,7 @@ class FusedStep:
             D.cast_bf16(lin.weight.data, out=u["wqkv"][i * HD:(i + 1) * HD])
             u["bqkv"][i * HD:(i + 1) * HD].copy_(lin.bias.data)
         D.cast_bf16(aa.att_fc1.weight.data, out=u["w1"])
-        D.ue_gather_dropout(nv, inv_his, u["X"], p, seed)
+        D.ue_gather_dropout(nv, inv_his, u["X"], p, seed, self._seed_dev)
         D.linear_bf16(u["X"], u["wqkv"], u["bqkv"], "bias", out=u["qkv"])
         D.ue_mha_fwd(u["qkv"], his_flat, u["ctx"], u["stats"], B, L, H, dk, use_mask)
         D.linear_bf16(u["ctx"], u["w1"], aa.att_fc1.bias.data, "tanh", out=u["E"])
@@ -183,7 +185,7 @@ class FusedStep:
                             his_flat, u["score"], u["loss"], u["user"], u["d_ctx_pool"], u["d_pre"],
                             fl.view("user_encoder.additive_attention.att_fc2.weight", grad=True).view(-1),
                             fl.view("user_encoder.additive_attention.att_fc2.bias", grad=True), b["d_news"], B, L, C,
-                            use_mask, True, cfg.news_grad_noise, seed + 1)
+                            use_mask, True, cfg.news_grad_noise, seed + 1, self._seed_dev)
         else:
             D.ue_pool_score(u["ctx"], u["E"], aa.att_fc2.weight.data.view(-1), aa.att_fc2.bias.data, nv, inv_cand,
                             his_flat, u["score"], u["loss"], u["user"], None, None, None, None, None, B, L, C,
@@ -213,7 +215,7 @@ class FusedStep:
             D.colsum(sl, g(f"user_encoder.multihead_attention.{nm}.bias"))
             D.transpose_cast(getattr(mha, nm).weight.data, out=u["wqkvT"][:, i * HD:(i + 1) * HD])
         D.linear_bf16(u["dqkv"], u["wqkvT"], None, "bias", out=u["dX"])
-        D.ue_scatter_dx(u["dX"], inv_his, b["d_news"], p, seed, cfg.news_grad_noise, seed + 2)
+        D.ue_scatter_dx(u["dX"], inv_his, b["d_news"], p, seed, cfg.news_grad_noise, seed + 2, self._seed_dev)
 
     def _text_head_backward(self, b, count, K):
         """d_news [K, D] → gradients of text_encoder.fc and text_encoder.additive_attention (trunk frozen)."""
@@ -235,13 +237,50 @@ class FusedStep:
         D.colsum(b["d_pre"], g("text_encoder.additive_attention.att_fc1.bias"), m_dev=count, m_scale=T)
 
     # ---- full step -----------------------------------------------------------------------------------------
-    @torch.no_grad()
     def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
+        """One step. With ``cfg.cuda_graph`` the whole kernel sequence (≈90 launches) is captured once per batch
+        shape and replayed; ids are copied into the graph's static input buffers and a device-side counter salts
+        the dropout / noise streams so every replay draws fresh randomness."""
+        if not (train and self.cfg.cuda_graph):
+            return self._run_eager(cand, his, train)
+        key = (tuple(cand.shape), tuple(his.shape))
+        g = self._graphs.get(key)
+        if g is None:
+            g = self._capture(cand, his, key)
+        g["cand"].copy_(cand, non_blocking=True)
+        g["his"].copy_(his, non_blocking=True)
+        g["graph"].replay()
+        D.count_launches(g["launches"])
+        return g["loss"]
+
+    def _capture(self, cand, his, key):
+        static_c = torch.zeros(cand.shape, dtype=torch.int32, device=self.dev)
+        static_h = torch.zeros(his.shape, dtype=torch.int32, device=self.dev)
+        static_c.copy_(cand)
+        static_h.copy_(his)
+        side = torch.cuda.Stream(device=self.dev)
+        side.wait_stream(torch.cuda.current_stream(self.dev))
+        with torch.cuda.stream(side):                       # warm-up: buffers, attributes, tensor maps
+            for _ in range(2):
+                self._run_eager(static_c, static_h, True)
+        torch.cuda.current_stream(self.dev).wait_stream(side)
+        torch.cuda.synchronize(self.dev)
+        graph = torch.cuda.CUDAGraph()
+        n0 = D.launch_count()
+        with torch.cuda.graph(graph):
+            loss = self._run_eager(static_c, static_h, True)
+        g = {"graph": graph, "cand": static_c, "his": static_h, "loss": loss, "launches": D.launch_count() - n0}
+        self._graphs[key] = g
+        return g
+
+    @torch.no_grad()
+    def _run_eager(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
         m = self.model
         B, C = cand.shape
         L = his.shape[1]
         self._step_no += 1
         seed = self.cfg.seed * 1000003 + 3 * self._step_no
+        D.counter_advance(self._seed_dev, 0x9E3779B97F4A7C15 & (2 ** 63 - 1))
         ids, uniq, count, inv, K = self._ids(cand, his)
         b = self.encode(uniq, count, K)
         if train:

@@ -31,11 +31,12 @@ SIGNATURES = {
     "fr_cast_f32_to_bf16": (I, [P, P, LL, P]),
     "fr_text_pool_bwd": (I, [P, P, P, P, P, P, I, I, I, I, P, P, P, P]),
     # user_encoder.cu
-    "fr_ue_gather_dropout": (I, [P, P, P, I, I, F, c_ulonglong, P]),
-    "fr_ue_scatter_dx": (I, [P, P, P, I, I, F, c_ulonglong, F, c_ulonglong, P]),
+    "fr_ue_gather_dropout": (I, [P, P, P, I, I, F, c_ulonglong, P, P]),
+    "fr_counter_advance": (I, [P, c_ulonglong, P]),
+    "fr_ue_scatter_dx": (I, [P, P, P, I, I, F, c_ulonglong, F, c_ulonglong, P, P]),
     "fr_ue_mha_fwd": (I, [P, P, P, P, I, I, I, I, I, P]),
     "fr_ue_mha_bwd": (I, [P, P, P, P, P, I, I, I, I, I, P]),
-    "fr_ue_pool_score": (I, [P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, F, c_ulonglong, P]),
+    "fr_ue_pool_score": (I, [P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, F, c_ulonglong, P, P]),
     "fr_colsum": (I, [P, I, P, I, I, I, P, I, P]),
     "fr_transpose_cast": (I, [P, P, I, I, I, P]),
     # gemm_grad_sm100.cu

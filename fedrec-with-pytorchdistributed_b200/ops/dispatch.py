@@ -227,19 +227,26 @@ def cast_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tens
 
 
 # ---- user encoder / loss / gradient GEMMs (CUDA only) -------------------------------------------------------
-def ue_gather_dropout(news_vecs, inv_his, X, p, seed):
+def counter_advance(ctr: torch.Tensor, inc: int = 1) -> None:
+    lib = require_native()
+    check(lib.fr_counter_advance(ctr.data_ptr(), int(inc), stream_ptr(ctr.device)), "fr_counter_advance")
+    count_launches(1)
+
+
+def ue_gather_dropout(news_vecs, inv_his, X, p, seed, seed_dev=None):
     lib = require_native()
     check(lib.fr_ue_gather_dropout(news_vecs.data_ptr(), inv_his.data_ptr(), X.data_ptr(), X.shape[0], X.shape[1],
-                                   float(p), int(seed) & (2 ** 64 - 1), stream_ptr(X.device)), "fr_ue_gather_dropout")
+                                   float(p), int(seed) & (2 ** 64 - 1), _p(seed_dev), stream_ptr(X.device)),
+          "fr_ue_gather_dropout")
     count_launches(1)
     return X
 
 
-def ue_scatter_dx(dX, inv_his, d_news, p, seed, noise_std=0.0, noise_seed=0):
+def ue_scatter_dx(dX, inv_his, d_news, p, seed, noise_std=0.0, noise_seed=0, seed_dev=None):
     lib = require_native()
     check(lib.fr_ue_scatter_dx(dX.data_ptr(), inv_his.data_ptr(), d_news.data_ptr(), dX.shape[0], dX.shape[1], float(p),
                                int(seed) & (2 ** 64 - 1), float(noise_std), int(noise_seed) & (2 ** 64 - 1),
-                               stream_ptr(dX.device)), "fr_ue_scatter_dx")
+                               _p(seed_dev), stream_ptr(dX.device)), "fr_ue_scatter_dx")
     count_launches(1)
     return d_news
 
@@ -261,13 +268,13 @@ def ue_mha_bwd(qkv, dctx, stats, his_ids, dqkv, B, L, H, dk, use_mask=False):
 
 
 def ue_pool_score(ctx, e, w2, b2, news_vecs, inv_cand, his_ids, score, loss, user_vec, d_ctx_pool, d_pre, d_w2, d_b2,
-                  d_news, B, L, C, use_mask=False, train=True, noise_std=0.0, noise_seed=0):
+                  d_news, B, L, C, use_mask=False, train=True, noise_std=0.0, noise_seed=0, seed_dev=None):
     lib = require_native()
     check(lib.fr_ue_pool_score(ctx.data_ptr(), e.data_ptr(), w2.data_ptr(), b2.data_ptr(), news_vecs.data_ptr(),
                                inv_cand.data_ptr(), _p(his_ids), _p(score), _p(loss), _p(user_vec), _p(d_ctx_pool),
                                _p(d_pre), _p(d_w2), _p(d_b2), _p(d_news), B, L, C, ctx.shape[1], e.shape[1],
                                int(use_mask), int(train), float(noise_std), int(noise_seed) & (2 ** 64 - 1),
-                               stream_ptr(ctx.device)), "fr_ue_pool_score")
+                               _p(seed_dev), stream_ptr(ctx.device)), "fr_ue_pool_score")
     count_launches(1)
 
 

@@ -103,9 +103,13 @@ int fr_text_pool_bwd(const void* hidden, const void* e, const float* alpha, cons
  * segment-sum (main.py:20-42) and the optional LDP noise on news-vector gradients (client.py:87-89):
  * d_news[inv_his[r],:] += dX[r,:]*mask + N(0, noise_std^2). */
 int fr_ue_gather_dropout(const float* news_vecs, const int* inv_his, void* X, int rows, int D, float p,
-                         unsigned long long seed, void* stream);
+                         unsigned long long seed, const unsigned long long* seed_dev, void* stream);
 int fr_ue_scatter_dx(const float* dX, const int* inv_his, float* d_news, int rows, int D, float p,
-                     unsigned long long seed, float noise_std, unsigned long long noise_seed, void* stream);
+                     unsigned long long seed, float noise_std, unsigned long long noise_seed,
+                     const unsigned long long* seed_dev, void* stream);
+/* seed_dev (optional, device): added to the seeds at run time, so a step replayed from a CUDA graph still draws a
+ * fresh dropout mask / noise every replay; fr_counter_advance bumps it on the stream. */
+int fr_counter_advance(unsigned long long* ctr, unsigned long long inc, void* stream);
 
 /* Per-(user, head) attention exp(QK^T/sqrt(dk))*mask/(rowsum+1e-8) · V; qkv bf16 [B*L, 3*H*dk] -> ctx bf16
  * [B*L, H*dk], stats fp32 [B*H*L, 2]. attention.py:37-45,69-81. The backward recomputes the probabilities. */
@@ -120,7 +124,8 @@ int fr_ue_mha_bwd(const void* qkv, const void* dctx, const float* stats, const i
 int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, const float* b2, const float* news_vecs,
                      const int* inv_cand, const int* his_ids, float* score, float* loss_mean, float* user_vec,
                      void* d_ctx_pool, void* d_pre, float* d_w2, float* d_b2, float* d_news, int B, int L, int C, int D,
-                     int Q, int use_mask, int train, float noise_std, unsigned long long noise_seed, void* stream);
+                     int Q, int use_mask, int train, float noise_std, unsigned long long noise_seed,
+                     const unsigned long long* seed_dev, void* stream);
 
 /* out[n] += sum_m X[m,n] (bias gradients); X bf16 or fp32 with leading dimension ld. */
 int fr_colsum(const void* X, int is_bf16, float* out, int M, int N, int ld, const int* m_dev, int m_scale, void* stream);
