@@ -44,11 +44,14 @@ struct GemmParams {
   int ldo, ldr;
 };
 
-template <int BN, bool TMA_EPI>
+// CG = 1: one CTA per 128 x BN tile. CG = 2: a CTA pair (cta_group::2) per 256 x BN tile; each CTA stages its own
+// 128 rows of A and half of the B tile, so the L2 → shared-memory traffic per FLOP drops by a third.
+template <int BN, bool TMA_EPI, int CG>
 struct Cfg {
-  static constexpr int kStages = TMA_EPI ? (BN >= 256 ? 3 : 4) : (BN >= 256 ? 4 : (BN >= 128 ? 6 : 8));
+  static constexpr int kStages = CG == 2 ? (TMA_EPI ? 4 : 6)
+                                         : (TMA_EPI ? (BN >= 256 ? 3 : 4) : (BN >= 256 ? 4 : (BN >= 128 ? 6 : 8)));
   static constexpr int kABytes = BM * BK * 2;
-  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kBBytes = (BN / CG) * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;   // BN in {64,128,256} → 128/256/512
   static constexpr int kColsPerWarp = BN / 4 < 32 ? 32 : BN / 4;       // columns one epilogue warp owns
@@ -59,20 +62,23 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/ + kBiasBytes;
 };
 
-// erf via Abramowitz–Stegun 7.1.26 (|err| < 1.5e-7): two MUFU ops + a short polynomial, so the GELU
-// epilogue keeps up with the tensor pipe (libdevice erff is ~3x the instructions).
-__device__ __forceinline__ float fast_erf(float x) {
-  const float ax = fabsf(x);
-  const float t = __frcp_rn(fmaf(0.3275911f, ax, 1.0f));
+// Exact-form GELU 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz–Stegun 7.1.26 (|err| < 1.5e-7, far below
+// bf16 resolution). Written so the per-element cost is two MUFU ops (rcp.approx, ex2.approx) plus ~11 FP32 ops:
+// the GELU epilogue has to keep pace with the tensor pipe (libdevice erff / IEEE division are 2-3x the work).
+__device__ __forceinline__ float gelu_erf(float x) {
+  float t, e;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.23164189f /* 0.3275911 / sqrt 2 */, fabsf(x), 1.0f)));
+  const float w = x * x;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(w * -0.72134752f /* -log2(e) / 2 */));
   float poly = fmaf(1.061405429f, t, -1.453152027f);
   poly = fmaf(poly, t, 1.421413741f);
   poly = fmaf(poly, t, -0.284496736f);
   poly = fmaf(poly, t, 0.254829592f);
   poly *= t;
-  const float r = 1.0f - poly * __expf(-ax * ax);
-  return copysignf(r, x);
+  const float erf_abs = fmaf(-poly, e, 1.0f);
+  const float hx = 0.5f * x;
+  return fmaf(hx, copysignf(erf_abs, x), hx);
 }
-__device__ __forceinline__ float gelu_erf(float x) { return 0.5f * x * (1.0f + fast_erf(x * 0.70710678118654752f)); }
 __device__ __forceinline__ float tanh_fast(float x) {
   float y;
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -86,12 +92,12 @@ __device__ __forceinline__ uint32_t box_off(int r, int j) {
   return (uint32_t)(r * 64 + ((j ^ ((r >> 1) & 3)) << 4));                       // SWIZZLE_64B
 }
 
-template <int BN, int EPI, bool OUT_F32, bool TMA_EPI>
+template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_r,
                     const GemmParams p) {
-  using C = Cfg<BN, TMA_EPI>;
+  using C = Cfg<BN, TMA_EPI, CG>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -113,10 +119,12 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     const long long md = (long long)(*p.m_dev) * p.m_scale;
     if (md < M) M = (int)md;
   }
-  const int m_blocks = (M + BM - 1) / BM;
+  const uint32_t cta_rank = CG == 2 ? cluster_ctarank() : 0u;     // 0 = leader of the pair
+  const int m_blocks = (M + BM * CG - 1) / (BM * CG);
   const int n_blocks = (p.N + BN - 1) / BN;
   const int k_blocks = (p.K + BK - 1) / BK;
   const int num_tiles = m_blocks * n_blocks;
+  const int tile_first = (int)blockIdx.x / CG, tile_step = (int)gridDim.x / CG;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -134,16 +142,18 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       }
       for (int i = 0; i < 2; ++i) {
         mbar_init(&tmem_full[i], 1);
-        mbar_init(&tmem_empty[i], kEpiWarps);
+        mbar_init(&tmem_empty[i], kEpiWarps * CG);
       }
       for (int i = 0; i < kEpiWarps; ++i) mbar_init(&resid_bar[i], 1);
       fence_barrier_init();
     }
     __syncwarp();
-    tmem_alloc(tmem_base_slot, C::kTmemCols);
+    if (CG == 2) tmem_alloc_pair(tmem_base_slot, C::kTmemCols);
+    else tmem_alloc(tmem_base_slot, C::kTmemCols);
   }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();       // the peer's barriers must exist before anything signals them
+  else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
 
@@ -152,29 +162,37 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / n_blocks) * BM;
-        const int n0 = (tile % n_blocks) * BN;
+      for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+        const int m0 = (tile / n_blocks) * (BM * CG) + (int)cta_rank * BM;
+        const int n0 = (tile % n_blocks) * BN + (int)cta_rank * (BN / CG) * (CG - 1);
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
           uint8_t* sb = sa + C::kABytes;
-          mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
-          tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BK, m0);
-          tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BK, n0);
+          if (CG == 2) {
+            // both CTAs' bytes are credited to the leader's barrier; only the leader arrives on it
+            const uint32_t leader_bar = mapa_u32(smem_u32(&full_bar[stage]), 0);
+            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
+            tma_load_2d_pair(sa, &tmap_a, leader_bar, kb * BK, m0);
+            tma_load_2d_pair(sb, &tmap_b, leader_bar, kb * BK, n0);
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+            tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BK, m0);
+            tma_load_2d(sb, &tmap_b, &full_bar[stage], kb * BK, n0);
+          }
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ------------------------------- MMA issuer ---------------------------------
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN);
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
@@ -187,12 +205,15 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             // advance 32 bytes (16 bf16) along K inside the swizzle row: +2 in 16-byte units
-            umma_bf16_ss(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+            if (CG == 2) umma_bf16_ss_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+            else umma_bf16_ss(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
           }
-          umma_commit(&empty_bar[stage]);          // smem slot free once these MMAs retire
+          if (CG == 2) umma_commit_pair(&empty_bar[stage], 3);   // frees the slot in both CTAs
+          else umma_commit(&empty_bar[stage]);                    // smem slot free once these MMAs retire
           if (++stage == C::kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&tmem_full[acc]);              // accumulator complete → epilogue
+        if (CG == 2) umma_commit_pair(&tmem_full[acc], 3);       // accumulator complete → both epilogues
+        else umma_commit(&tmem_full[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -209,8 +230,15 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     uint32_t rphase = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile / n_blocks) * BM;
+    // the accumulator stage is handed back to the leader's MMA warp: locally, or across the pair
+    const uint32_t empty_remote[2] = {CG == 2 ? mapa_u32(smem_u32(&tmem_empty[0]), 0) : 0u,
+                                      CG == 2 ? mapa_u32(smem_u32(&tmem_empty[1]), 0) : 0u};
+    auto release_acc = [&](int a) {
+      if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(empty_remote[a]);
+      else mbar_arrive(&tmem_empty[a]);
+    };
+    for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+      const int m0 = (tile / n_blocks) * (BM * CG) + (int)cta_rank * BM;
       const int n0 = (tile % n_blocks) * BN;
       const int brow0 = m0 + quarter * 32;                   // first row of this warp's 32-row box
       const int row = brow0 + lane;
@@ -321,7 +349,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         // the accumulator has been read out: hand the TMEM stage back to the MMA warp before storing
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (lane == 0) release_acc(acc);
         if (TMA_EPI) {
           if (box_full) {
 #pragma unroll
@@ -348,7 +376,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       } else {
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(&tmem_empty[acc]);
+        if (lane == 0) release_acc(acc);
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
@@ -356,10 +384,12 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();       // neither CTA may leave while the pair still uses its memory
+  else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, C::kTmemCols);
+    if (CG == 2) tmem_dealloc_pair(tmem_base, C::kTmemCols);
+    else tmem_dealloc(tmem_base, C::kTmemCols);
   }
 }
 
@@ -409,30 +439,41 @@ int make_tmap_bf16_2d_box(CUtensorMap* out, const void* base, long long rows, lo
 
 struct Maps { CUtensorMap a, b, o, r; };
 
-template <int BN, int EPI, bool OUT_F32, bool TMA_EPI>
+template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG>
 static int launch(const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t s) {
-  auto kern = gemm_bf16_tn_kernel<BN, EPI, OUT_F32, TMA_EPI>;
-  using C = Cfg<BN, TMA_EPI>;
+  auto kern = gemm_bf16_tn_kernel<BN, EPI, OUT_F32, TMA_EPI, CG>;
+  using C = Cfg<BN, TMA_EPI, CG>;
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     FR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
     attr_set = true;
   }
-  const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
-  int grid = tiles < max_ctas ? tiles : max_ctas;
-  if (grid < 1) grid = 1;
-  kern<<<grid, kThreads, C::kSmemBytes, s>>>(m.a, m.b, m.o, m.r, p);
-  FR_LAUNCH_CHECK();
+  const int tiles = ((p.M + BM * CG - 1) / (BM * CG)) * ((p.N + BN - 1) / BN);
+  int grid = tiles * CG < max_ctas ? tiles * CG : max_ctas / CG * CG;
+  if (grid < CG) grid = CG;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = C::kSmemBytes;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = CG == 2 ? 1 : 0;
+  FR_CHECK(cudaLaunchKernelEx(&cfg, kern, m.a, m.b, m.o, m.r, p));
   return 0;
 }
 
-template <int BN, bool OUT_F32, bool TMA_EPI>
+template <int BN, bool OUT_F32, bool TMA_EPI, int CG = 1>
 static int dispatch_epi(int epi, const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t s) {
   switch (epi) {
-    case EPI_BIAS: return launch<BN, EPI_BIAS, OUT_F32, TMA_EPI>(m, p, max_ctas, s);
-    case EPI_BIAS_GELU: return launch<BN, EPI_BIAS_GELU, OUT_F32, TMA_EPI>(m, p, max_ctas, s);
-    case EPI_BIAS_RESID: return launch<BN, EPI_BIAS_RESID, OUT_F32, TMA_EPI>(m, p, max_ctas, s);
-    case EPI_BIAS_TANH: return launch<BN, EPI_BIAS_TANH, OUT_F32, TMA_EPI>(m, p, max_ctas, s);
+    case EPI_BIAS: return launch<BN, EPI_BIAS, OUT_F32, TMA_EPI, CG>(m, p, max_ctas, s);
+    case EPI_BIAS_GELU: return launch<BN, EPI_BIAS_GELU, OUT_F32, TMA_EPI, CG>(m, p, max_ctas, s);
+    case EPI_BIAS_RESID: return launch<BN, EPI_BIAS_RESID, OUT_F32, TMA_EPI, CG>(m, p, max_ctas, s);
+    case EPI_BIAS_TANH: return launch<BN, EPI_BIAS_TANH, OUT_F32, TMA_EPI, CG>(m, p, max_ctas, s);
   }
   fr::set_error("fr_gemm_bf16: unknown epilogue %d", epi);
   return -1;
@@ -470,9 +511,9 @@ using namespace fr;
 
 // out = epi(A · W^T + bias).  A [M,K] ld=lda, W [N,K] ld=ldw (both bf16, K-major), out bf16 or fp32 ld=ldo.
 // block_n: 0 = choose, else 64/128/256.  m_dev (optional, device int): effective M = min(M, *m_dev*m_scale).
-FR_API int fr_gemm_bf16(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32,
-                        int M, int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n,
-                        const int* m_dev, int m_scale, void* stream) {
+static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32,
+                          int M, int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n,
+                          const int* m_dev, int m_scale, int cta_group, int tma_epilogue, void* stream) {
   FR_REQUIRE(M >= 1 && N >= 8 && K >= 8, "fr_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
   FR_REQUIRE(N % 8 == 0 && K % 8 == 0, "fr_gemm_bf16: N=%d and K=%d must be multiples of 8", N, K);
   FR_REQUIRE(ldo % 8 == 0 && ((uintptr_t)out & 15) == 0, "fr_gemm_bf16: out must be 16-byte aligned, ldo %% 8 == 0");
@@ -489,12 +530,23 @@ FR_API int fr_gemm_bf16(const void* A, const void* W, const float* bias, const v
     block_n = best;
   }
   FR_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "fr_gemm_bf16: block_n=%d", block_n);
+  // cta_group: 0 = choose. Pairs need the wide tile, a bf16 output and enough rows to fill the GPU with pairs.
+  static const int env_cg = [] { const char* e = getenv("FEDREC_GEMM_CTA_GROUP"); return e ? atoi(e) : 0; }();
+  if (cta_group == 0) cta_group = env_cg;
+  const bool pair_ok = !out_fp32 && block_n == 256;
+  if (cta_group == 0) cta_group = (pair_ok && M >= 4096) ? 2 : 1;
+  if (cta_group == 2 && !pair_ok) cta_group = 1;
+  FR_REQUIRE(cta_group == 1 || cta_group == 2, "fr_gemm_bf16: cta_group=%d", cta_group);
   Maps maps;
   if (int e = make_tmap_bf16_2d(&maps.a, A, M, K, lda, BM)) return e;
-  if (int e = make_tmap_bf16_2d(&maps.b, W, N, K, ldw, block_n)) return e;
-  // bf16 outputs of the wide tiles leave through shared memory + TMA (FEDREC_GEMM_EPI=direct disables it)
-  static const bool allow_tma_epi = [] { const char* e = getenv("FEDREC_GEMM_EPI"); return !(e && strcmp(e, "direct") == 0); }();
-  const bool tma_epi = allow_tma_epi && !out_fp32 && block_n >= 128;
+  if (int e = make_tmap_bf16_2d(&maps.b, W, N, K, ldw, block_n / cta_group)) return e;
+  // bf16 outputs of the wide tiles leave through shared memory + TMA (FEDREC_GEMM_EPI=direct disables it).
+  // For single CTAs the staging boxes cost a pipeline stage, which only pays off when the epilogue dominates (short K).
+  static const int env_epi = [] { const char* e = getenv("FEDREC_GEMM_EPI"); return !e ? 0 : (strcmp(e, "direct") == 0 ? -1 : 1); }();
+  if (tma_epilogue == 0) tma_epilogue = env_epi;
+  bool tma_epi = !out_fp32 && block_n == 256 && (cta_group == 2 || K <= 1536);
+  if (tma_epilogue < 0) tma_epi = false;
+  if (tma_epilogue > 0) tma_epi = !out_fp32 && block_n == 256;
   maps.o = maps.a; maps.r = maps.a;
   if (tma_epi) {
     const int kc = block_n / 4;
@@ -515,13 +567,30 @@ FR_API int fr_gemm_bf16(const void* A, const void* W, const float* bias, const v
       default: return dispatch_epi<256, true, false>(epi, maps, p, ctas, s);
     }
   }
-  if (tma_epi) {
-    if (block_n == 128) return dispatch_epi<128, false, true>(epi, maps, p, ctas, s);
-    return dispatch_epi<256, false, true>(epi, maps, p, ctas, s);
+  if (cta_group == 2) {
+    if (tma_epi) return dispatch_epi<256, false, true, 2>(epi, maps, p, ctas, s);
+    return dispatch_epi<256, false, false, 2>(epi, maps, p, ctas, s);
   }
+  if (tma_epi) return dispatch_epi<256, false, true>(epi, maps, p, ctas, s);
   switch (block_n) {
     case 64: return dispatch_epi<64, false, false>(epi, maps, p, ctas, s);
     case 128: return dispatch_epi<128, false, false>(epi, maps, p, ctas, s);
     default: return dispatch_epi<256, false, false>(epi, maps, p, ctas, s);
   }
+}
+
+FR_API int fr_gemm_bf16(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32,
+                        int M, int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n,
+                        const int* m_dev, int m_scale, void* stream) {
+  return gemm_bf16_impl(A, W, bias, resid, out, out_fp32, M, N, K, lda, ldw, ldo, ldr, epi, block_n, m_dev, m_scale, 0, 0,
+                        stream);
+}
+
+// Same with the two scheduling choices made explicit: cta_group 0 = choose, 1 = single CTAs, 2 = CTA pairs
+// (cta_group::2, 256-row MMAs); tma_epilogue 0 = choose, -1 = per-row global stores, 1 = staged TMA stores.
+FR_API int fr_gemm_bf16_ex(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32,
+                           int M, int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n,
+                           const int* m_dev, int m_scale, int cta_group, int tma_epilogue, void* stream) {
+  return gemm_bf16_impl(A, W, bias, resid, out, out_fp32, M, N, K, lda, ldw, ldo, ldr, epi, block_n, m_dev, m_scale,
+                        cta_group, tma_epilogue, stream);
 }

@@ -52,4 +52,5 @@ SIGNATURES = {
     "fr_symm_close": (I, [P]),
     # gemm_sm100.cu
     "fr_gemm_bf16": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, I, P]),
+    "fr_gemm_bf16_ex": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, I, I, I, P]),
 }

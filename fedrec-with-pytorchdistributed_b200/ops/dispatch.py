@@ -151,8 +151,11 @@ _EPI = {"none": 0, "bias": 0, "gelu": 1, "resid": 2, "tanh": 3}
 def linear_bf16(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None, epi: str = "bias",
                 resid: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None,
                 out_dtype: torch.dtype = torch.bfloat16, block_n: int = 0,
-                m_dev: Optional[torch.Tensor] = None, m_scale: int = 1) -> torch.Tensor:
-    """``epi(x @ w.T + bias)`` on the tcgen05 GEMM. ``x [M,K]`` and ``w [N,K]`` bf16 with unit inner stride."""
+                m_dev: Optional[torch.Tensor] = None, m_scale: int = 1, cta_group: int = 0,
+                tma_epilogue: int = 0) -> torch.Tensor:
+    """``epi(x @ w.T + bias)`` on the tcgen05 GEMM. ``x [M,K]`` and ``w [N,K]`` bf16 with unit inner stride.
+
+    ``cta_group`` (0 auto / 1 / 2) and ``tma_epilogue`` (0 auto / -1 direct / 1 staged TMA) pin the kernel variant."""
     assert x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
     assert x.dim() == 2 and w.dim() == 2 and x.stride(1) == 1 and w.stride(1) == 1
     lib = require_native()
@@ -165,10 +168,10 @@ def linear_bf16(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] =
         assert bias.dtype == torch.float32 and bias.is_contiguous()
     if resid is not None:
         assert resid.dtype == torch.bfloat16 and resid.stride(1) == 1
-    check(lib.fr_gemm_bf16(x.data_ptr(), w.data_ptr(), _p(bias), _p(resid), out.data_ptr(),
-                           1 if out.dtype == torch.float32 else 0, M, N, K, x.stride(0), w.stride(0), out.stride(0),
-                           resid.stride(0) if resid is not None else 0, _EPI[epi], block_n, _p(m_dev), m_scale,
-                           stream_ptr(x.device)), "fr_gemm_bf16")
+    check(lib.fr_gemm_bf16_ex(x.data_ptr(), w.data_ptr(), _p(bias), _p(resid), out.data_ptr(),
+                              1 if out.dtype == torch.float32 else 0, M, N, K, x.stride(0), w.stride(0), out.stride(0),
+                              resid.stride(0) if resid is not None else 0, _EPI[epi], block_n, _p(m_dev), m_scale,
+                              cta_group, tma_epilogue, stream_ptr(x.device)), "fr_gemm_bf16")
     count_launches(1)
     return out
 

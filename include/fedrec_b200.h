@@ -169,6 +169,13 @@ int fr_gemm_bf16(const void* A, const void* W, const float* bias, const void* re
                  int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n, const int* m_dev, int m_scale,
                  void* stream);
 
+/* fr_gemm_bf16 with its two scheduling choices explicit. cta_group: 0 choose, 1 one CTA per 128 x block_n tile,
+ * 2 a CTA pair per 256 x 256 tile (tcgen05 cta_group::2, each CTA stages half of the B tile; bf16 out, block_n 256).
+ * tma_epilogue: 0 choose, -1 per-row global stores, 1 swizzled shared-memory boxes + TMA store / TMA residual load. */
+int fr_gemm_bf16_ex(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32, int M,
+                    int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n, const int* m_dev,
+                    int m_scale, int cta_group, int tma_epilogue, void* stream);
+
 /* out[M1,N1] (fp32) += A[K,M1]^T · B[K,N1]: weight gradients dW = dY^T X on tcgen05 with MN-major operands and
  * split-K (csrc/gemm_grad_sm100.cu). K_eff = min(K, *k_dev * k_scale); rows of A in [K_eff, round_up(K_eff,64))
  * must be zero. Replaces the autograd weight-gradient GEMMs of every trainable nn.Linear. */

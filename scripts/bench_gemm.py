@@ -47,12 +47,18 @@ def main():
         r = torch.randn(M, N, device=DEV).bfloat16() if epi == "resid" else None
         out = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
         ours_med, ours_min = timeit(lambda: D.linear_bf16(x, w, b, epi, resid=r, out=out), flush)
+        variants = {}
+        if N >= 256 and M >= 4096:
+            for cg in (1, 2):
+                for te in (-1, 1):
+                    t, _ = timeit(lambda: D.linear_bf16(x, w, b, epi, resid=r, out=out, block_n=256, cta_group=cg, tma_epilogue=te), flush, iters=6)
+                    variants[f"cg{cg}_{'tma' if te > 0 else 'direct'}_tflops"] = round(2.0 * M * N * K / t / 1e9, 1)
         wt = w.t()
         lib_med, lib_min = timeit(lambda: torch.matmul(x, wt, out=out), flush)
         fl = 2.0 * M * N * K
         rows.append({"name": name, "M": M, "N": N, "K": K, "epi": epi, "ours_ms": ours_med, "ours_min_ms": ours_min,
                      "ours_tflops": fl / ours_med / 1e9, "cublas_plain_ms": lib_med, "cublas_tflops": fl / lib_med / 1e9,
-                     "frac_of_measured_bf16_peak": fl / ours_med / 1e9 / peaks.get("bf16_tflops", 1665.4)})
+                     "frac_of_measured_bf16_peak": fl / ours_med / 1e9 / peaks.get("bf16_tflops", 1665.4), **variants})
         print(rows[-1], flush=True)
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump(rows, open("gpurun_out/gemm_bench.json", "w"), indent=1)

@@ -11,7 +11,8 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _check(M, N, K, epi="bias", block_n=0, out_dtype=torch.bfloat16, m_dev=None, m_scale=1, seed=0):
+def _check(M, N, K, epi="bias", block_n=0, out_dtype=torch.bfloat16, m_dev=None, m_scale=1, seed=0, cta_group=0,
+           tma_epilogue=0):
     ops.require_native()
     g = torch.Generator(device=DEV).manual_seed(seed)
     x = (torch.randn(M, K, device=DEV, generator=g) * 0.5).bfloat16()
@@ -20,7 +21,8 @@ def _check(M, N, K, epi="bias", block_n=0, out_dtype=torch.bfloat16, m_dev=None,
     r = (torch.randn(M, N, device=DEV, generator=g)).bfloat16() if epi == "resid" else None
     out = torch.full((M, N), 7.0, device=DEV, dtype=out_dtype)
     cnt = torch.tensor([m_dev], device=DEV, dtype=torch.int32) if m_dev is not None else None
-    D.linear_bf16(x, w, b, epi, resid=r, out=out, block_n=block_n, m_dev=cnt, m_scale=m_scale)
+    D.linear_bf16(x, w, b, epi, resid=r, out=out, block_n=block_n, m_dev=cnt, m_scale=m_scale, cta_group=cta_group,
+                  tma_epilogue=tma_epilogue)
     torch.cuda.synchronize()
     want = ref.linear(x, w, b, {"bias": 0, "gelu": 1, "resid": 2, "tanh": 3}[epi], r)
     rows = M if m_dev is None else min(M, m_dev * m_scale)
@@ -58,6 +60,21 @@ def test_single_k_block():
 ])
 def test_model_shapes(M, N, K, epi):
     _check(M, N, K, epi)
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
+@pytest.mark.parametrize("tma_epilogue", [-1, 1])
+@pytest.mark.parametrize("M,N,K,epi", [(4500, 768, 768, "resid"), (8200, 3072, 768, "gelu"), (5000, 768, 3072, "resid"),
+                                       (300, 2304, 768, "bias"), (256, 256, 64, "bias"), (6000, 400, 192, "tanh")])
+def test_kernel_variants(cta_group, tma_epilogue, M, N, K, epi):
+    """Every (CTA pair | single CTA) x (staged TMA | direct) epilogue variant on the wide tile."""
+    _check(M, N, K, epi, block_n=256, cta_group=cta_group, tma_epilogue=tma_epilogue)
+
+
+@pytest.mark.parametrize("cta_group", [1, 2])
+def test_variants_with_device_side_m(cta_group):
+    _check(6000, 768, 768, "resid", block_n=256, m_dev=133, m_scale=30, cta_group=cta_group, tma_epilogue=1)
+    _check(6000, 768, 768, "gelu", block_n=256, m_dev=7, m_scale=30, cta_group=cta_group, tma_epilogue=1)
 
 
 def test_fp32_output_small_m():
