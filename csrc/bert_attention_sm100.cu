@@ -1,16 +1,20 @@
 // N8 on the tensor cores: DistilBERT self-attention for short titles (T <= 64 tokens, 12 heads x 64).
 //
-// A title is far smaller than a tcgen05 tile, so TP = floor(128 / T) consecutive titles share one 128-row
-// tile and the attention is block-diagonal inside it:
+// A title is far smaller than a tcgen05 tile, so several titles share one 128-row tile: every title gets a slot of
+// SLOT = 32 (T <= 32) or 64 rows, TP = 128 / SLOT titles per tile, and the attention is block-diagonal inside it:
 //   S[128 x 128] = Q_h K_h^T        tcgen05.mma, both operands K-major, straight from the QKV GEMM output via TMA
-//   P = exp(S/8 - rowmax) masked to the row's own title and to valid keys (HF: masked_fill(finfo.min) + softmax)
-//   O[128 x 64]  = P V_h            tcgen05.mma, A = P written to shared memory in the K-major 128B-swizzled
-//                                   layout by the soft-max threads, B = V_h as loaded (tokens x 64 = MN-major)
+//                                   (one {64 x SLOT} box per title and operand, so title t sits at rows SLOT*t)
+//   P = exp(S/8 - rowmax), masked to valid keys (HF: masked_fill(finfo.min) + softmax); a row only ever needs the
+//       SLOT columns of its own title = exactly the TMEM chunk(s) its warp owns, kept in registers
+//   O[128 x 64]  = P V_h            tcgen05.mma, A = P written to shared memory in the K-major 128B-swizzled layout
+//                                   (only the diagonal blocks are rewritten; the rest was zeroed once),
+//                                   B = V_h as loaded (tokens x 64 = MN-major)
 //   out = O / rowsum                (deferred normalisation), bf16
 // The block-diagonal waste (x TP in MMA work) is irrelevant: the tile is latency-bound, not throughput-bound.
 // One CTA = 4 warps; thread r owns row r of the tile for the soft-max and the epilogue; lane 0 of warp 0 issues
-// the TMA loads and both MMAs. 80 KB of shared memory and 256 TMEM columns per CTA, so two CTAs share an SM and
-// hide each other's latencies. Reference: HF MultiHeadSelfAttention reached from encoder.py:27.
+// the TMA loads (one job ahead of the math) and both MMAs. 80 KB of shared memory and 256 TMEM columns per CTA,
+// so two CTAs share an SM and hide each other's latencies. Reference: HF MultiHeadSelfAttention reached from
+// encoder.py:27.
 #include "sm100.cuh"
 #include <cuda.h>
 
@@ -42,11 +46,14 @@ struct AttParams {
   const int* items;          // [n_items] table row of every title, or null (identity)
   const int* count_dev;      // optional device count of valid titles
   __nv_bfloat16* out;        // [n_items*T, heads*64]
-  int n_items, T, heads, TP;
+  int n_items, T, heads;
 };
 
+template <int SLOT>
 __global__ void __launch_bounds__(128, 2)
 bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const AttParams p) {
+  constexpr int TP = kAttTile / SLOT;          // titles per tile
+  constexpr int NCH = SLOT / 32;               // 32-column chunks of S a row needs
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -58,10 +65,10 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   uint64_t* bar_v = bar_qk + 1;                                     // V of the next (tile, head) has landed
   uint64_t* bar_mma = bar_v + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mma + 1);
-  float* sKeyBias = reinterpret_cast<float*>(tmem_slot + 2);     // [128] 0 or -inf per key column of the tile
+  float* sKeyBias = reinterpret_cast<float*>(smem + 81920 + 64);  // [128] per key column: 0 or -inf, pre-scaled domain
 
   const int tid = threadIdx.x, warp = tid >> 5;
-  const int T = p.T, TP = p.TP, heads = p.heads;
+  const int T = p.T, heads = p.heads;
   const int n_eff = p.count_dev ? min(p.n_items, *p.count_dev) : p.n_items;
   const int num_tiles = (n_eff + TP - 1) / TP;
   const int hd_all = heads * kAttHd;
@@ -73,62 +80,73 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
     mbar_init(bar_mma, 1);
     fence_barrier_init();
   }
+  // off-diagonal blocks of P stay zero for the whole kernel
+  {
+    const uint32_t prow = smem_u32(sP) + (uint32_t)tid * 128;
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(prow + (uint32_t)(c >> 3) * 16384 + (uint32_t)(c & 7) * 16), "r"(0u) : "memory");
+  }
   if (warp == 0) {
     __syncwarp();
     tmem_alloc(tmem_slot, 256);
   }
+  fence_proxy_async();
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem, tO = tmem + 128;
   uint32_t ph_qk = 0, ph_v = 0, ph_mma = 0;
+
   // Loads run one (tile, head) ahead of the math: Q/K of the next job are requested as soon as S = QK^T has been
-  // produced (their buffers are free), V as soon as O = PV has been produced.
+  // produced (their buffers are free), V as soon as O = PV has been produced. Title t of a tile lands at rows SLOT*t.
   auto load_qk = [&](int tile_, int h_) {
-    const int r0 = tile_ * TP * T;
     mbar_arrive_expect_tx(bar_qk, 2 * 16384);
-    tma_load_2d(sQ, &tmap_qkv, bar_qk, h_ * kAttHd, r0);
-    tma_load_2d(sK, &tmap_qkv, bar_qk, hd_all + h_ * kAttHd, r0);
+#pragma unroll
+    for (int t = 0; t < TP; ++t) {
+      const int r0 = (tile_ * TP + t) * T;
+      tma_load_2d(sQ + t * SLOT * 128, &tmap_qkv, bar_qk, h_ * kAttHd, r0);
+      tma_load_2d(sK + t * SLOT * 128, &tmap_qkv, bar_qk, hd_all + h_ * kAttHd, r0);
+    }
   };
   auto load_v = [&](int tile_, int h_) {
-    const int r0 = tile_ * TP * T;
     mbar_arrive_expect_tx(bar_v, 16384);
-    tma_load_2d(sV, &tmap_qkv, bar_v, 2 * hd_all + h_ * kAttHd, r0);
+#pragma unroll
+    for (int t = 0; t < TP; ++t)
+      tma_load_2d(sV + t * SLOT * 128, &tmap_qkv, bar_v, 2 * hd_all + h_ * kAttHd, (tile_ * TP + t) * T);
   };
   if (tid == 0 && (int)blockIdx.x < num_tiles) {
     load_qk(blockIdx.x, 0);
     load_v(blockIdx.x, 0);
   }
 
-  const int my_title = tid / T;                       // title slot of my row inside the tile
-  const bool row_in_tile = my_title < TP;
-  const int win_lo = my_title * T, win_hi = win_lo + T;   // my row may attend key columns [win_lo, win_hi)
-  // columns any row of this warp may need (warp-uniform chunk skipping)
-  const int w_lo = ((warp * 32) / T) * T;
-  const int w_hi = min(TP, (warp * 32 + 31) / T + 1) * T;
+  const int my_slot = tid / SLOT;                     // title slot of my row
+  const int my_tok = tid - my_slot * SLOT;            // token index of my row inside its title
+  const int col0 = my_slot * SLOT;                    // first key column of my title = first column I read from S
+  const uint32_t lane_base = ((uint32_t)(warp * 32) << 16);
+  constexpr float kScaleLog2 = 0.125f * 1.4426950408889634f;     // 1/sqrt(64) * log2(e): soft-max in the exp2 domain
 
   for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
     const int title0 = tile * TP;
-    const int row0 = title0 * T;
     // key bias for the 128 key columns of this tile (key column tid and row tid belong to the same title slot)
     bool my_uniform = false;
     {
-      const int kt = tid / T;                         // title slot of key column `tid`
       float bias = -INFINITY;
-      if (kt < TP && title0 + kt < n_eff) {
-        const int item = p.items ? p.items[title0 + kt] : (title0 + kt);
+      if (my_tok < T && title0 + my_slot < n_eff) {
+        const int item = p.items ? p.items[title0 + my_slot] : (title0 + my_slot);
         const int* mrow = p.mask_table ? p.mask_table + (size_t)item * T : nullptr;
         bool any = false;
         if (mrow) for (int j = 0; j < T; ++j) any |= (mrow[j] != 0);
-        const int mk = mrow ? mrow[tid - kt * T] : 1;
         my_uniform = mrow && !any;                    // fully masked title: HF's soft-max of a constant row = uniform
-        bias = (mk != 0 || my_uniform) ? 0.f : -INFINITY;
+        bias = (!mrow || mrow[my_tok] != 0 || my_uniform) ? 0.f : -INFINITY;
       }
+      __syncthreads();                                // previous tile's readers are done with sKeyBias
       sKeyBias[tid] = bias;
     }
-    __syncthreads();
-    const bool row_ok = row_in_tile && (title0 + my_title) < n_eff;
+    __syncthreads();                                  // sKeyBias is complete (every valid row of a title computed the same flag)
+    const bool row_ok = my_tok < T && (title0 + my_slot) < n_eff;
+    const size_t out_row = (size_t)(title0 + my_slot) * T + my_tok;
 
     for (int h = 0; h < heads; ++h) {
       // the job after this one (next head, or head 0 of this CTA's next tile)
@@ -151,55 +169,44 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
       tc_fence_after();
       if (tid == 0 && has_next) load_qk(ntile, nh);          // sQ / sK are free again
 
-      // ---- soft-max over my row (thread = row) ----
-      const uint32_t lane_base = ((uint32_t)(warp * 32) << 16);
+      // ---- soft-max over my row: only my title's SLOT key columns, held in registers ----
+      float t[NCH * 32];
       float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
-        if (c * 32 + 32 <= w_lo || c * 32 >= w_hi) continue;        // warp-uniform
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
         uint32_t r[32];
-        tmem_ld_32x32(tS + lane_base + c * 32, r);
+        tmem_ld_32x32(tS + lane_base + (uint32_t)(col0 + c * 32), r);
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int col = c * 32 + j;
-          const float s = (col >= win_lo && col < win_hi)
-                              ? (my_uniform ? 0.f : __uint_as_float(r[j]) * 0.125f + sKeyBias[col]) : -INFINITY;
-          mx = fmaxf(mx, s);
+        for (int j = 0; j < 32; j += 4) {
+          const float4 kb = *reinterpret_cast<const float4*>(&sKeyBias[col0 + c * 32 + j]);
+          t[c * 32 + j + 0] = my_uniform ? kb.x : fmaf(__uint_as_float(r[j + 0]), kScaleLog2, kb.x);
+          t[c * 32 + j + 1] = my_uniform ? kb.y : fmaf(__uint_as_float(r[j + 1]), kScaleLog2, kb.y);
+          t[c * 32 + j + 2] = my_uniform ? kb.z : fmaf(__uint_as_float(r[j + 2]), kScaleLog2, kb.z);
+          t[c * 32 + j + 3] = my_uniform ? kb.w : fmaf(__uint_as_float(r[j + 3]), kScaleLog2, kb.w);
         }
       }
+#pragma unroll
+      for (int j = 0; j < NCH * 32; ++j) mx = fmaxf(mx, t[j]);
+      if (mx == -INFINITY) mx = 0.f;                         // rows outside any valid title: keep the math finite
       float l = 0.f;
       const uint32_t prow = smem_u32(sP) + (uint32_t)tid * 128;
-#pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
         uint32_t packed[16];
-        if (c * 32 + 32 <= w_lo || c * 32 >= w_hi) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) packed[j] = 0u;
-        } else {
-          uint32_t r[32];
-          tmem_ld_32x32(tS + lane_base + c * 32, r);
-          tmem_ld_wait();
-          float e[32];
-#pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            const int col = c * 32 + j;
-            const bool in = (col >= win_lo && col < win_hi) && row_in_tile;
-            const float s = my_uniform ? 0.f : __uint_as_float(r[j]) * 0.125f + sKeyBias[in ? col : 0];
-            e[j] = in ? __expf(s - mx) : 0.f;
-            l += e[j];
-          }
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const __nv_bfloat162 b2 = __floats2bfloat162_rn(e[2 * j], e[2 * j + 1]);
-            packed[j] = *reinterpret_cast<const uint32_t*>(&b2);
-          }
+        for (int j = 0; j < 16; ++j) {
+          const float e0 = exp2f(t[c * 32 + 2 * j] - mx), e1 = exp2f(t[c * 32 + 2 * j + 1] - mx);
+          l += e0 + e1;
+          const __nv_bfloat162 b2 = __floats2bfloat162_rn(e0, e1);
+          packed[j] = *reinterpret_cast<const uint32_t*>(&b2);
         }
-        // 32 columns = 4 chunks of 16 bytes inside block (c / 2); chunk index XOR (row % 8) = 128B swizzle
-        const uint32_t blk = prow + (uint32_t)(c >> 1) * 16384;
+        // 32 columns = 4 chunks of 16 bytes inside 64-column block; chunk index XOR (row % 8) = 128B swizzle
+        const int cc = col0 + c * 32;
+        const uint32_t blk = prow + (uint32_t)(cc >> 6) * 16384;
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4) {
-          const uint32_t chunk = (uint32_t)((c & 1) * 4 + q4) ^ (uint32_t)(tid & 7);
+          const uint32_t chunk = (uint32_t)(((cc & 63) >> 3) + q4) ^ (uint32_t)(tid & 7);
           asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(blk + chunk * 16), "r"(packed[4 * q4]),
                        "r"(packed[4 * q4 + 1]), "r"(packed[4 * q4 + 2]), "r"(packed[4 * q4 + 3])
                        : "memory");
@@ -226,8 +233,8 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
       // ---- epilogue: O / l → bf16 → global ----
       {
         const float inv = 1.f / l;
-        __nv_bfloat16* op = p.out + (size_t)(row0 + tid) * hd_all + h * kAttHd;
-#pragma unroll 1
+        __nv_bfloat16* op = p.out + out_row * hd_all + h * kAttHd;
+#pragma unroll
         for (int c = 0; c < 2; ++c) {
           uint32_t r[32];
           tmem_ld_32x32(tO + lane_base + c * 32, r);
@@ -238,8 +245,8 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
               uint4 qv;
               __nv_bfloat162* hh = reinterpret_cast<__nv_bfloat162*>(&qv);
 #pragma unroll
-              for (int t = 0; t < 4; ++t)
-                hh[t] = __floats2bfloat162_rn(__uint_as_float(r[j + 2 * t]) * inv, __uint_as_float(r[j + 2 * t + 1]) * inv);
+              for (int u = 0; u < 4; ++u)
+                hh[u] = __floats2bfloat162_rn(__uint_as_float(r[j + 2 * u]) * inv, __uint_as_float(r[j + 2 * u + 1]) * inv);
               *reinterpret_cast<uint4*>(op + c * 32 + j) = qv;
             }
           }
@@ -266,21 +273,24 @@ FR_API int fr_bert_attention_tc(const void* qkv, const int* mask_table, const in
   FR_REQUIRE(head_dim == kAttHd, "fr_bert_attention_tc: head_dim=%d (only 64 is built)", head_dim);
   FR_REQUIRE(T >= 1 && T <= 64, "fr_bert_attention_tc: T=%d must be in [1,64]", T);
   if (n_items == 0) return 0;
-  const int TP = kAttTile / T;
+  const int slot = T <= 32 ? 32 : 64;
+  const int TP = kAttTile / slot;
   CUtensorMap tm;
-  if (int e = make_tmap_bf16_2d_box(&tm, qkv, (long long)n_items * T, 3LL * heads * kAttHd, 3LL * heads * kAttHd, kAttTile, 64)) return e;
+  if (int e = make_tmap_bf16_2d_box(&tm, qkv, (long long)n_items * T, 3LL * heads * kAttHd, 3LL * heads * kAttHd, slot, 64)) return e;
   AttParams p;
   p.mask_table = mask_table; p.items = items; p.count_dev = count_dev; p.out = (__nv_bfloat16*)out;
-  p.n_items = n_items; p.T = T; p.heads = heads; p.TP = TP;
+  p.n_items = n_items; p.T = T; p.heads = heads;
   constexpr int smem = 81920 + 64 + 512 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
-    FR_CHECK(cudaFuncSetAttribute(bert_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    FR_CHECK(cudaFuncSetAttribute(bert_attention_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    FR_CHECK(cudaFuncSetAttribute(bert_attention_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
   int tiles = (n_items + TP - 1) / TP;
   int grid = tiles < 2 * kNumSMs ? tiles : 2 * kNumSMs;
-  bert_attention_tc_kernel<<<grid, 128, smem, (cudaStream_t)stream>>>(tm, p);
+  if (slot == 32) bert_attention_tc_kernel<32><<<grid, 128, smem, (cudaStream_t)stream>>>(tm, p);
+  else bert_attention_tc_kernel<64><<<grid, 128, smem, (cudaStream_t)stream>>>(tm, p);
   FR_LAUNCH_CHECK();
   return 0;
 }

@@ -544,7 +544,7 @@ static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const
   // For single CTAs the staging boxes cost a pipeline stage, which only pays off when the epilogue dominates (short K).
   static const int env_epi = [] { const char* e = getenv("FEDREC_GEMM_EPI"); return !e ? 0 : (strcmp(e, "direct") == 0 ? -1 : 1); }();
   if (tma_epilogue == 0) tma_epilogue = env_epi;
-  bool tma_epi = !out_fp32 && block_n == 256 && (cta_group == 2 || K <= 1536);
+  bool tma_epi = !out_fp32 && block_n == 256 && K <= 1536;     // long K: the deeper pipeline wins (measured)
   if (tma_epilogue < 0) tma_epi = false;
   if (tma_epilogue > 0) tma_epi = !out_fp32 && block_n == 256;
   maps.o = maps.a; maps.r = maps.a;
