@@ -254,34 +254,23 @@ __global__ void __launch_bounds__(128) text_pool_kernel(const __nv_bfloat16* __r
 // [count*T, round_up(count*T, 64)) are zeroed: the weight-gradient GEMM reduces over whole 64-row blocks.
 // ---------------------------------------------------------------------------------------------
 constexpr int kMaxHq = 512;
+// stage 1, one warp per item: da[n*T + t] (fp32) and d_b2 += sum da
 __global__ void __launch_bounds__(128) text_pool_bwd_kernel(const __nv_bfloat16* __restrict__ hidden,
-                                                            const __nv_bfloat16* __restrict__ e,
                                                             const float* __restrict__ alpha,
                                                             const __nv_bfloat16* __restrict__ d_pooled,
-                                                            const float* __restrict__ w2, const int* __restrict__ count_dev,
-                                                            int n_items, int T, int Hq, __nv_bfloat16* __restrict__ d_pre,
-                                                            float* __restrict__ d_w2, float* __restrict__ d_b2) {
+                                                            const int* __restrict__ count_dev, int n_items, int T,
+                                                            float* __restrict__ da_out, float* __restrict__ d_b2) {
   __shared__ float sDa[4][kMaxT];
-  __shared__ float sW2[kMaxHq];
-  __shared__ float sAcc[kMaxHq];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
-  for (int c = threadIdx.x; c < Hq; c += 128) { sW2[c] = w2[c]; sAcc[c] = 0.f; }
-  if (blockIdx.x == 0) {                       // zero the tail rows up to the next 64-row boundary
-    const int r0 = n_eff * T, r1 = min(n_items * T, (r0 + 63) / 64 * 64);
-    for (int i = threadIdx.x; i < (r1 - r0) * Hq; i += 128) d_pre[(size_t)r0 * Hq + i] = __float2bfloat16(0.f);
-  }
-  __syncthreads();
   float db2 = 0.f;
-  float wacc[kMaxHq / 32];
-#pragma unroll
-  for (int i = 0; i < kMaxHq / 32; ++i) wacc[i] = 0.f;
   for (int n = blockIdx.x * 4 + w; n < n_eff; n += gridDim.x * 4) {
     const size_t row0 = (size_t)n * T;
     float dp[kPerLane];
 #pragma unroll
     for (int c = 0; c < 3; ++c) load8(d_pooled + (size_t)n * kHid + c * 256 + lane * 8, dp + c * 8);
     float dot = 0.f;
+#pragma unroll 2
     for (int t = 0; t < T; ++t) {
       float hv[8], s = 0.f;
 #pragma unroll
@@ -291,35 +280,76 @@ __global__ void __launch_bounds__(128) text_pool_bwd_kernel(const __nv_bfloat16*
         for (int i = 0; i < 8; ++i) s = fmaf(dp[c * 8 + i], hv[i], s);
       }
       s = warp_sum(s);
-      const float al = alpha[row0 + t];
       if (lane == 0) sDa[w][t] = s;
-      dot = fmaf(al, s, dot);
+      dot = fmaf(alpha[row0 + t], s, dot);
     }
     __syncwarp();
-    for (int t = 0; t < T; ++t) {
+    for (int t = lane; t < T; t += 32) {
       const float da = alpha[row0 + t] * (sDa[w][t] - dot);
-      if (lane == 0) db2 += da;
-#pragma unroll
-      for (int i = 0; i < kMaxHq / 32; ++i) {
-        const int c = lane + 32 * i;
-        if (c < Hq) {
-          const float ev = __bfloat162float(e[(row0 + t) * Hq + c]);
-          wacc[i] = fmaf(da, ev, wacc[i]);
-          d_pre[(row0 + t) * Hq + c] = __float2bfloat16(da * sW2[c] * (1.f - ev * ev));
-        }
-      }
+      da_out[row0 + t] = da;
+      db2 += da;
     }
     __syncwarp();
   }
-#pragma unroll
-  for (int i = 0; i < kMaxHq / 32; ++i) {
-    const int c = lane + 32 * i;
-    if (c < Hq) atomicAdd(&sAcc[c], wacc[i]);
-  }
+  db2 = warp_sum(db2);
   if (lane == 0 && db2 != 0.f) atomicAdd(d_b2, db2);
+}
+
+// stage 2, streaming over the rows: d_pre[r, c] = da[r] * w2[c] * (1 - e[r,c]^2) (bf16, the weight-gradient GEMM operand),
+// d_w2[c] += sum_r da[r] e[r,c], d_b1[c] += sum_r d_pre[r,c]. A thread owns 8 consecutive columns; a block owns a
+// contiguous range of rows. Rows in [rows_eff, round_up(rows_eff, 64)) are written as zeros.
+constexpr int kDpreRowLanes = 5;
+__global__ void __launch_bounds__(kDpreRowLanes * 64) text_dpre_kernel(const __nv_bfloat16* __restrict__ e,
+                                                                        const float* __restrict__ da,
+                                                                        const float* __restrict__ w2,
+                                                                        const int* __restrict__ count_dev, int rows_max,
+                                                                        int rows_per_item, int Hq, int rows_per_block,
+                                                                        __nv_bfloat16* __restrict__ d_pre,
+                                                                        float* __restrict__ d_w2, float* __restrict__ d_b1) {
+  __shared__ float sW2[kDpreRowLanes][64][8];
+  __shared__ float sB1[kDpreRowLanes][64][8];
+  const int cq = threadIdx.x & 63;                    // column chunk (8 columns)
+  const int rl = threadIdx.x >> 6;                    // row lane
+  const int rows_eff = count_dev ? min(rows_max, *count_dev * rows_per_item) : rows_max;
+  const int rows_pad = min(rows_max, (rows_eff + 63) / 64 * 64);
+  const int r0 = blockIdx.x * rows_per_block, r1 = min(rows_pad, r0 + rows_per_block);
+  const bool col_ok = cq * 8 < Hq;
+  float wv[8], aw[8], ab[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { wv[i] = col_ok ? w2[cq * 8 + i] : 0.f; aw[i] = 0.f; ab[i] = 0.f; }
+  if (col_ok) {
+    for (int r = r0 + rl; r < r1; r += kDpreRowLanes) {
+      float out[8];
+      if (r < rows_eff) {
+        float ev[8];
+        load8(e + (size_t)r * Hq + cq * 8, ev);
+        const float d = da[r];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          out[i] = d * wv[i] * (1.f - ev[i] * ev[i]);
+          aw[i] = fmaf(d, ev[i], aw[i]);
+          ab[i] += out[i];
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) out[i] = 0.f;
+      }
+      store8(d_pre + (size_t)r * Hq + cq * 8, out);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { sW2[rl][cq][i] = aw[i]; sB1[rl][cq][i] = ab[i]; }
   __syncthreads();
-  for (int c = threadIdx.x; c < Hq; c += 128)
-    if (sAcc[c] != 0.f) atomicAdd(d_w2 + c, sAcc[c]);
+  if (rl == 0 && col_ok) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float a = 0.f, b = 0.f;
+#pragma unroll
+      for (int k = 0; k < kDpreRowLanes; ++k) { a += sW2[k][cq][i]; b += sB1[k][cq][i]; }
+      if (a != 0.f) atomicAdd(d_w2 + cq * 8 + i, a);
+      if (b != 0.f) atomicAdd(d_b1 + cq * 8 + i, b);
+    }
+  }
 }
 
 // fp32 → bf16 cast of a contiguous buffer (weight packing, activations entering a GEMM)
@@ -392,14 +422,18 @@ FR_API int fr_text_pool(const void* hidden, const void* e, const float* w2, cons
 }
 
 FR_API int fr_text_pool_bwd(const void* hidden, const void* e, const float* alpha, const void* d_pooled, const float* w2,
-                            const int* count_dev, int n_items, int T, int Hq, int hidden_dim, void* d_pre, float* d_w2,
-                            float* d_b2, void* stream) {
+                            const int* count_dev, int n_items, int T, int Hq, int hidden_dim, void* d_pre, float* da_scratch,
+                            float* d_w2, float* d_b2, float* d_b1, void* stream) {
   FR_REQUIRE(hidden_dim == kHid, "fr_text_pool_bwd: hidden=%d (only %d is built)", hidden_dim, kHid);
-  FR_REQUIRE(T >= 1 && T <= kMaxT && Hq >= 1 && Hq <= kMaxHq, "fr_text_pool_bwd: T=%d Hq=%d", T, Hq);
+  FR_REQUIRE(T >= 1 && T <= kMaxT && Hq >= 8 && Hq <= kMaxHq && Hq % 8 == 0, "fr_text_pool_bwd: T=%d Hq=%d", T, Hq);
   if (n_items == 0) return 0;
-  text_pool_bwd_kernel<<<grid_for(n_items, 4, kNumSMs * 2), 128, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)hidden, (const __nv_bfloat16*)e, alpha, (const __nv_bfloat16*)d_pooled, w2, count_dev, n_items, T,
-      Hq, (__nv_bfloat16*)d_pre, d_w2, d_b2);
+  cudaStream_t s = (cudaStream_t)stream;
+  text_pool_bwd_kernel<<<grid_for(n_items, 4, kNumSMs * 8), 128, 0, s>>>(
+      (const __nv_bfloat16*)hidden, alpha, (const __nv_bfloat16*)d_pooled, count_dev, n_items, T, da_scratch, d_b2);
+  const int rows = n_items * T;
+  const int rows_per_block = 64;
+  text_dpre_kernel<<<(rows + rows_per_block - 1) / rows_per_block, kDpreRowLanes * 64, 0, s>>>(
+      (const __nv_bfloat16*)e, da_scratch, w2, count_dev, rows, T, Hq, rows_per_block, (__nv_bfloat16*)d_pre, d_w2, d_b1);
   FR_LAUNCH_CHECK();
   return 0;
 }

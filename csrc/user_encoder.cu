@@ -393,41 +393,47 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   }
 }
 
-// out[n] += sum_m X[m, n]   (bias gradients). X bf16 [M, N] with ld; rows limited by *m_dev * m_scale.
-__global__ void __launch_bounds__(256) colsum_bf16_kernel(const __nv_bfloat16* __restrict__ X, float* __restrict__ out, int M,
-                                                          int N, int ld, const int* __restrict__ m_dev, int m_scale) {
+// out[n] += sum_m X[m, n]   (bias gradients). X [M, N] with leading dimension ld; rows limited by *m_dev * m_scale.
+// A thread owns 8 (bf16) or 4 (fp32) consecutive columns = one 16-byte load per row; 8 row lanes per block.
+template <typename T, int VEC>
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ X, float* __restrict__ out, int M, int N, int ld,
+                                                     const int* __restrict__ m_dev, int m_scale) {
   if (m_dev) M = min(M, *m_dev * m_scale);
-  const int col = blockIdx.x * 32 + (threadIdx.x & 31);
-  const int rlane = threadIdx.x >> 5;            // 8 row lanes
-  __shared__ float sm[8][33];
-  float acc = 0.f;
-  if (col < N)
-    for (int r = blockIdx.y * 8 + rlane; r < M; r += gridDim.y * 8) acc += __bfloat162float(X[(size_t)r * ld + col]);
-  sm[rlane][threadIdx.x & 31] = acc;
-  __syncthreads();
-  if (rlane == 0 && col < N) {
-    float t = 0.f;
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int col = (blockIdx.x * 32 + cl) * VEC;
+  __shared__ float sm[8][32][VEC + 1];
+  float acc[VEC];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) t += sm[i][threadIdx.x];
-    atomicAdd(out + col, t);
+  for (int i = 0; i < VEC; ++i) acc[i] = 0.f;
+  if (col < N) {
+    for (int r = blockIdx.y * 8 + rl; r < M; r += gridDim.y * 8) {
+      const uint4 q = *reinterpret_cast<const uint4*>(X + (size_t)r * ld + col);
+      if (VEC == 8) {
+        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float2 f = __bfloat1622float2(h[i]);
+          acc[2 * i] += f.x;
+          acc[2 * i + 1] += f.y;
+        }
+      } else {
+        const float* f = reinterpret_cast<const float*>(&q);
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) acc[i] += f[i];
+      }
+    }
   }
-}
-__global__ void __launch_bounds__(256) colsum_f32_kernel(const float* __restrict__ X, float* __restrict__ out, int M, int N,
-                                                         int ld, const int* __restrict__ m_dev, int m_scale) {
-  if (m_dev) M = min(M, *m_dev * m_scale);
-  const int col = blockIdx.x * 32 + (threadIdx.x & 31);
-  const int rlane = threadIdx.x >> 5;
-  __shared__ float sm[8][33];
-  float acc = 0.f;
-  if (col < N)
-    for (int r = blockIdx.y * 8 + rlane; r < M; r += gridDim.y * 8) acc += X[(size_t)r * ld + col];
-  sm[rlane][threadIdx.x & 31] = acc;
-  __syncthreads();
-  if (rlane == 0 && col < N) {
-    float t = 0.f;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) t += sm[i][threadIdx.x];
-    atomicAdd(out + col, t);
+  for (int i = 0; i < VEC; ++i) sm[rl][cl][i] = acc[i];
+  __syncthreads();
+  if (rl == 0 && col < N) {
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+      float t = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) t += sm[k][cl][i];
+      if (col + i < N) atomicAdd(out + col + i, t);
+    }
   }
 }
 
@@ -541,12 +547,14 @@ FR_API int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, con
 FR_API int fr_colsum(const void* X, int is_bf16, float* out, int M, int N, int ld, const int* m_dev, int m_scale,
                      void* stream) {
   if (M == 0 || N == 0) return 0;
-  int rows_blocks = (M + 255) / 256;
-  if (rows_blocks > 64) rows_blocks = 64;
+  const int vec = is_bf16 ? 8 : 4;
+  FR_REQUIRE(N % vec == 0 && ld % vec == 0 && ((uintptr_t)X & 15) == 0, "fr_colsum: N=%d, ld=%d must be multiples of %d and X 16-byte aligned", N, ld, vec);
+  int rows_blocks = (M + 63) / 64;
+  if (rows_blocks > 128) rows_blocks = 128;
   if (rows_blocks < 1) rows_blocks = 1;
-  dim3 grid((N + 31) / 32, rows_blocks);
-  if (is_bf16) colsum_bf16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)X, out, M, N, ld, m_dev, m_scale);
-  else colsum_f32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)X, out, M, N, ld, m_dev, m_scale);
+  dim3 grid((N / vec + 31) / 32, rows_blocks);
+  if (is_bf16) colsum_kernel<__nv_bfloat16, 8><<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)X, out, M, N, ld, m_dev, m_scale);
+  else colsum_kernel<float, 4><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)X, out, M, N, ld, m_dev, m_scale);
   FR_LAUNCH_CHECK();
   return 0;
 }

@@ -95,7 +95,8 @@ class FusedStep:
              "news_vecs": z(K, self.cfg.news_dim, dt=torch.float32),
              # backward
              "d_news": z(K, self.cfg.news_dim, dt=torch.float32), "d_news_bf": z(K, self.cfg.news_dim),
-             "d_pooled": z(K, dim), "d_pre": z(R, hq), "wfcT": z(dim, self.cfg.news_dim)}
+             "d_pooled": z(K, dim), "d_pre": z(R, hq), "wfcT": z(dim, self.cfg.news_dim),
+             "da": z(R, dt=torch.float32)}
         self._bufs[K] = b
         return b
 
@@ -231,10 +232,10 @@ class FusedStep:
         D.gemm_grad(b["d_news_bf"], b["pooled"], g("text_encoder.fc.weight"), k_dev=count, k_scale=1)
         D.colsum(b["d_news"], g("text_encoder.fc.bias"), m_dev=count, m_scale=1)
         D.text_pool_bwd(b["x"], b["e"], b["alpha"], b["d_pooled"], aa.att_fc2.weight.data.view(-1), count, K, T,
-                        b["d_pre"], g("text_encoder.additive_attention.att_fc2.weight").view(-1),
-                        g("text_encoder.additive_attention.att_fc2.bias"))
+                        b["d_pre"], b["da"], g("text_encoder.additive_attention.att_fc2.weight").view(-1),
+                        g("text_encoder.additive_attention.att_fc2.bias"),
+                        g("text_encoder.additive_attention.att_fc1.bias"))
         D.gemm_grad(b["d_pre"], b["x"], g("text_encoder.additive_attention.att_fc1.weight"), k_dev=count, k_scale=T)
-        D.colsum(b["d_pre"], g("text_encoder.additive_attention.att_fc1.bias"), m_dev=count, m_scale=T)
 
     # ---- full step -----------------------------------------------------------------------------------------
     def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:

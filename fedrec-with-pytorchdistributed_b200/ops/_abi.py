@@ -29,7 +29,7 @@ SIGNATURES = {
     "fr_bert_attention_tc": (I, [P, P, P, P, I, I, I, I, P, P]),
     "fr_text_pool": (I, [P, P, P, P, P, P, P, I, I, I, I, P, P, P]),
     "fr_cast_f32_to_bf16": (I, [P, P, LL, P]),
-    "fr_text_pool_bwd": (I, [P, P, P, P, P, P, I, I, I, I, P, P, P, P]),
+    "fr_text_pool_bwd": (I, [P, P, P, P, P, P, I, I, I, I, P, P, P, P, P, P]),
     # user_encoder.cu
     "fr_ue_gather_dropout": (I, [P, P, P, I, I, F, c_ulonglong, P, P]),
     "fr_counter_advance": (I, [P, c_ulonglong, P]),

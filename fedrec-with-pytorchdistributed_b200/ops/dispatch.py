@@ -314,10 +314,11 @@ def gemm_grad(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, k_dev=None, k
     return out
 
 
-def text_pool_bwd(hidden, e, alpha, d_pooled, w2, count, n_items, T, d_pre, d_w2, d_b2):
+def text_pool_bwd(hidden, e, alpha, d_pooled, w2, count, n_items, T, d_pre, da_scratch, d_w2, d_b2, d_b1):
     lib = require_native()
     check(lib.fr_text_pool_bwd(hidden.data_ptr(), e.data_ptr(), alpha.data_ptr(), d_pooled.data_ptr(), w2.data_ptr(),
-                               _p(count), n_items, T, e.shape[1], hidden.shape[1], d_pre.data_ptr(), d_w2.data_ptr(),
-                               d_b2.data_ptr(), stream_ptr(hidden.device)), "fr_text_pool_bwd")
-    count_launches(1)
+                               _p(count), n_items, T, e.shape[1], hidden.shape[1], d_pre.data_ptr(),
+                               da_scratch.data_ptr(), d_w2.data_ptr(), d_b2.data_ptr(), d_b1.data_ptr(),
+                               stream_ptr(hidden.device)), "fr_text_pool_bwd")
+    count_launches(2)
     return d_pre

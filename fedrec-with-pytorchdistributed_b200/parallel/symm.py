@@ -51,11 +51,33 @@ class SymmetricHeap:
         self._local_heaps: Optional[List[int]] = None     # single-GPU emulation: all ranks' heaps are ours
         self._bytes_tensor: Optional[torch.Tensor] = None
         self.mc_ptr: int = 0
+        self.backend = "ipc"
+        self._vmm_handle = None
 
     # ---- construction -----------------------------------------------------------------------------------
     @classmethod
-    def create(cls, info, heap_bytes: int = 64 << 20) -> "SymmetricHeap":
+    def create(cls, info, heap_bytes: int = 64 << 20, backend: Optional[str] = None) -> "SymmetricHeap":
+        """``backend``: "ipc" (default; cudaMalloc + CUDA IPC, peer loads/stores) or "vmm" (driver VMM allocation through
+        ``torch.distributed._symmetric_memory``, which also yields an NVLS multicast mapping when the fabric supports
+        it, so the kernels switch to ``multimem.ld_reduce`` / ``multimem.st``). ``FEDREC_SYMM`` overrides."""
+        import os
+        backend = backend or os.environ.get("FEDREC_SYMM", "ipc")
         h = cls(info.device, info.rank, info.world_size, heap_bytes)
+        h.backend = backend
+        if backend == "vmm":
+            import torch.distributed._symmetric_memory as symm_mem
+            t = symm_mem.empty(h.heap_bytes, dtype=torch.uint8, device=info.device)
+            t.zero_()
+            hdl = symm_mem.rendezvous(t, dist.group.WORLD)
+            h._vmm_handle = hdl
+            h._bytes_tensor = t
+            h.local_ptr = t.data_ptr()
+            h.peer_ptrs = [int(x) for x in hdl.buffer_ptrs]
+            mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+            h.mc_ptr = mc if os.environ.get("FEDREC_NVLS", "1") != "0" else 0
+            torch.cuda.synchronize(info.device)
+            dist.barrier()
+            return h
         p = ctypes.c_void_p()
         with torch.cuda.device(info.device):
             check(h.lib.fr_symm_alloc(ctypes.byref(p), h.heap_bytes), "fr_symm_alloc")
@@ -135,7 +157,7 @@ class SymmetricHeap:
         assert self.peer_ptrs, "call finalize() first"
         bufs, pads = self._ptr_arrays(self.offset_of(g))
         n = (g.numel() + 3) // 4 * 4
-        check(self.lib.fr_grad_allreduce(bufs, pads, self.mc_ptr or None, self.W, self.rank if ranks_here == 1 else 0,
+        check(self.lib.fr_grad_allreduce(bufs, pads, (self.mc_ptr + self.offset_of(g)) if self.mc_ptr else None, self.W, self.rank if ranks_here == 1 else 0,
                                          ranks_here, n, self._next_epoch(), float(clip), float(noise_std), float(scale),
                                          int(seed) & (2 ** 64 - 1), blocks, stream_ptr(self.device)), "fr_grad_allreduce")
         count_launches(1)
@@ -146,7 +168,7 @@ class SymmetricHeap:
         bufs, pads = self._ptr_arrays(self.offset_of(buf))
         w = (ctypes.c_float * self.W)(*[float(x) for x in weights])
         n = (buf.numel() + 3) // 4 * 4
-        check(self.lib.fr_param_average(bufs, pads, self.mc_ptr or None, w, self.W, self.rank if ranks_here == 1 else 0,
+        check(self.lib.fr_param_average(bufs, pads, (self.mc_ptr + self.offset_of(buf)) if self.mc_ptr else None, w, self.W, self.rank if ranks_here == 1 else 0,
                                         ranks_here, n, self._next_epoch(), blocks, stream_ptr(self.device)), "fr_param_average")
         count_launches(1)
         return buf

@@ -90,11 +90,12 @@ int fr_text_pool(const void* hidden, const void* e, const float* w2, const float
 int fr_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
 
 /* Backward of fr_text_pool given d_pooled (bf16 [n,768]): writes d_pre = d(tanh input) bf16 [n*T,Hq] (tail rows
- * zeroed to a 64-row boundary), accumulates d_w2 [Hq], d_b2 [1]. The trunk is frozen, so no d_hidden.
+ * zeroed to a 64-row boundary), accumulates d_w2 [Hq], d_b2 [1] and the fc1 bias gradient d_b1 [Hq]. da_scratch:
+ * n*T floats of scratch (per-token d(logit)). The trunk is frozen, so no d_hidden.
  * Replaces the autograd of attention.py:16-25 inside news_vecs.backward(news_grad), model.py:86-87. */
 int fr_text_pool_bwd(const void* hidden, const void* e, const float* alpha, const void* d_pooled, const float* w2,
-                     const int* count_dev, int n_items, int T, int Hq, int hidden_dim, void* d_pre, float* d_w2,
-                     float* d_b2, void* stream);
+                     const int* count_dev, int n_items, int T, int Hq, int hidden_dim, void* d_pre, float* da_scratch,
+                     float* d_w2, float* d_b2, float* d_b1, void* stream);
 
 /* ---- user encoder + loss, forward and backward (csrc/user_encoder.cu) ---------------------------------- */
 

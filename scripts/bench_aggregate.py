@@ -77,12 +77,15 @@ def main():
             dist.all_reduce(plain)
             plain.mul_(1.0 / W)
         rec["nccl_plus_clip_noise_kernels_us"] = timed(nccl_clip_noise)
+        rec["symm_backend"] = heap.backend
+        rec["nvls"] = bool(heap.mc_ptr)
         rows.append(rec)
         if rank == 0:
             print(json.dumps(rec), flush=True)
     if rank == 0:
         os.makedirs("gpurun_out", exist_ok=True)
-        json.dump(rows, open(f"gpurun_out/agg_sweep_w{W}.json", "w"), indent=1)
+        tag = "" if heap.backend == "ipc" else ("_nvls" if heap.mc_ptr else "_vmm")
+        json.dump(rows, open(f"gpurun_out/agg_sweep_w{W}{tag}.json", "w"), indent=1)
     heap.close()
     dist.destroy_process_group()
 

@@ -31,6 +31,35 @@ elif what == "attention":
     out = torch.zeros(n * T, 768, device=DEV, dtype=torch.bfloat16)
     for _ in range(6):
         D.bert_attention(qkv, None, None, None, n, T, H, out)
+elif what == "layernorm":
+    x = torch.randn(M, 768, device=DEV).bfloat16()
+    g, b = torch.randn(768, device=DEV), torch.randn(768, device=DEV)
+    out = torch.empty_like(x)
+    for _ in range(6):
+        D.layernorm_bf16(x, g, b, out=out)
+elif what == "aggregate":
+    from fedrec_b200.parallel.symm import SymmetricHeap
+    W, n = 8, 1_164_896
+    hs = SymmetricHeap.local(W, heap_bytes=8 << 20)
+    bufs = [h.alloc_f32(n) for h in hs]
+    for b_ in bufs:
+        b_.normal_()
+    for _ in range(6):
+        hs[0].grad_allreduce_(bufs[0], clip=2.0, noise_std=0.1, seed=3, scale=1.0 / W, ranks_here=W)
+elif what == "step":
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.data import make_synthetic_mind
+    from fedrec_b200.engine import TrainStep
+    from fedrec_b200.models import UserModel
+    cfg = FedRecConfig(batch_size=50, title_len=30, num_news=8192, cuda_graph=False)
+    data = make_synthetic_mind(num_news=8192, num_train=8, num_valid=2, title_len=30, seed=0)
+    model = UserModel(None, data.news_index, DEV, config=cfg)
+    step = TrainStep(model, cfg)
+    for i in range(4):
+        cand = torch.randint(1, 8192, (50, 5), device=DEV, dtype=torch.int32)
+        his = torch.randint(1, 8192, (50, 50), device=DEV, dtype=torch.int32)
+        step.run(cand, his, train=True)
+        model.adam_step()
 elif what == "gemm_grad":
     A = (torch.randn(M, 384, device=DEV) * 0.3).bfloat16()
     B = (torch.randn(M, 768, device=DEV) * 0.3).bfloat16()

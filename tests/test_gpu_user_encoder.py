@@ -157,12 +157,14 @@ def test_text_head_backward_matches_autograd():
     D.text_pool(hidden, e, w2, b2, None, None, cnt, n, T, pooled, alpha)
     d_pooled = (torch.randn(n, Hd, device=DEV, generator=g) * 0.1).bfloat16()
     d_pre = torch.full((n * T, Hq), 9.0, device=DEV, dtype=torch.bfloat16)
-    d_w2, d_b2 = torch.zeros(Hq, device=DEV), torch.zeros(1, device=DEV)
-    D.text_pool_bwd(hidden, e, alpha, d_pooled, w2, cnt, n, T, d_pre, d_w2, d_b2)
+    d_w2, d_b2, db1 = torch.zeros(Hq, device=DEV), torch.zeros(1, device=DEV), torch.zeros(Hq, device=DEV)
+    da = torch.zeros(n * T, device=DEV)
+    D.text_pool_bwd(hidden, e, alpha, d_pooled, w2, cnt, n, T, d_pre, da, d_w2, d_b2, db1)
     dW1 = torch.zeros(Hq, Hd, device=DEV)
     D.gemm_grad(d_pre, hidden, dW1, k_dev=cnt, k_scale=T)
-    db1 = torch.zeros(Hq, device=DEV)
-    D.colsum(d_pre, db1, m_dev=cnt, m_scale=T)
+    db1_check = torch.zeros(Hq, device=DEV)
+    D.colsum(d_pre, db1_check, m_dev=cnt, m_scale=T)
+    torch.testing.assert_close(db1, db1_check, atol=1e-3, rtol=2e-2)
     torch.cuda.synchronize()
     m = 61
     h = hidden[: m * T].float().view(m, T, Hd)
