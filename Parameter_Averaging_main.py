@@ -6,6 +6,7 @@ as `--name value`. The work happens in `fedrec_b200.engine.federated`.
 import sys
 
 from fedrec_b200.engine.federated import run_entrypoint
+from fedrec_b200.engine.trainer import Trainer, process_news_grad, process_user_grad, train_on_step  # noqa: F401
 
 
 def main(argv=None):

@@ -6,6 +6,8 @@ as `--name value`. The work happens in `fedrec_b200.engine.federated`.
 import sys
 
 from fedrec_b200.engine.federated import run_entrypoint
+from fedrec_b200.engine.trainer import Trainer, process_news_grad, process_user_grad, train_on_step  # noqa: F401
+from fedrec_b200.utils.transport import send_saved_model  # noqa: F401  (upstream client.py:191-210)
 
 
 def main(argv=None):

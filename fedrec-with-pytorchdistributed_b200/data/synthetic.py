@@ -102,3 +102,24 @@ def make_synthetic_mind(num_news: int = 4096, num_train: int = 512, num_valid: i
         return sams
 
     return SyntheticMind(news_index, nid2index, make(num_train, 0), make(num_valid, num_train), topic)
+
+
+def _main(argv=None):
+    """``python -m fedrec_b200.data.synthetic --out UserData``: write a client shard in the upstream file layout."""
+    import argparse
+    ap = argparse.ArgumentParser(description=_main.__doc__)
+    ap.add_argument("--out", default="UserData")
+    ap.add_argument("--num_news", type=int, default=4096)
+    ap.add_argument("--num_train", type=int, default=512)
+    ap.add_argument("--num_valid", type=int, default=64)
+    ap.add_argument("--title_len", type=int, default=30)
+    ap.add_argument("--client", type=int, default=0)
+    ap.add_argument("--seed", type=int, default=0)
+    a = ap.parse_args(argv)
+    d = make_synthetic_mind(a.num_news, a.num_train, a.num_valid, a.title_len, seed=a.seed, client=a.client)
+    d.save(a.out)
+    print(f"wrote {a.out}: news_index {d.news_index.shape}, {len(d.train_sam)} train / {len(d.valid_sam)} valid impressions")
+
+
+if __name__ == "__main__":
+    _main()

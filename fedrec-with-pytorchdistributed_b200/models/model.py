@@ -108,9 +108,34 @@ class UserModel(nn.Module):
         ops.adam_flat(self.flat, self.cfg.lr, self.cfg.beta1, self.cfg.beta2, self.cfg.adam_eps)
 
     # ---- encoding ------------------------------------------------------------------
+    def _fused_engine(self):
+        """The sm_100a pipeline, created on first use for CUDA models (engine/fused.py)."""
+        if self._fused is None and self.device.type == "cuda" and self.cfg.fused:
+            from ..engine.fused import FusedStep
+            self._fused = FusedStep(self, self.cfg)
+        return self._fused
+
     def encode_unique(self, uniq: torch.Tensor, keep_cache: bool = True, with_grad: bool = False) -> torch.Tensor:
-        """``uniq`` int64 ``[U]`` news rows → ``[U, D]`` news vectors (trunk under no_grad/eval)."""
+        """``uniq`` int64 ``[U]`` news rows → ``[U, D]`` news vectors (trunk under no_grad/eval).
+
+        On CUDA the frozen trunk runs on the framework's own kernels (bf16 tcgen05 GEMMs, tensor-core attention); the
+        trainable head runs there too unless ``with_grad`` asks for an autograd graph through it."""
         te = self.text_encoder
+        fused = self._fused_engine()
+        if fused is not None:
+            U = uniq.numel()
+            cap = (U + 255) // 256 * 256                 # bucketed capacity: a bounded set of activation buffers
+            padded = torch.zeros(cap, dtype=torch.int32, device=self.device)
+            padded[:U] = uniq
+            b = fused.encode(padded, torch.tensor([U], dtype=torch.int32, device=self.device), cap)
+            T = self.news_tokens.shape[1]
+            hidden = b["x"][: U * T].view(U, T, -1).float()
+            msk = self.news_mask[uniq.long()]
+            if keep_cache:
+                self._cache = {"uniq": uniq, "hidden": hidden, "mask": msk}
+            if with_grad:
+                return te.head(hidden, msk)
+            return b["news_vecs"][:U].clone()
         was_training = te.DistillBert.training
         te.DistillBert.eval()
         with torch.no_grad():
@@ -124,6 +149,10 @@ class UserModel(nn.Module):
             return te.head(hidden, msk)
         with torch.no_grad():
             return te.head(hidden, msk)
+
+    def get_news_vecs(self, idx) -> torch.Tensor:
+        """Vectors of news rows ``idx`` (upstream ``get_news_vecs`` reads an attribute it never sets, model.py:63-64)."""
+        return self.gen_news_vecs(idx)
 
     def gen_news_vecs(self, nids: IdLike) -> torch.Tensor:
         """News vectors for an id array of any shape ``[...]`` → ``[..., D]`` (no grad).

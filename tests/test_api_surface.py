@@ -1,0 +1,74 @@
+"""Upstream-named modules and symbols import and behave (SURVEY.md §2.1 inventory)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_upstream_module_names_resolve():
+    import attention, dataset, encoder, evaluation_functions, model  # noqa: E401
+    assert model.UserModel and model.ServerUserModel
+    assert encoder.TextEncoder and encoder.UserEncoder
+    assert attention.AdditiveAttention and attention.ScaledDotProductAttention and attention.MultiHeadAttention
+    for n in ("TrainDataset", "NewsDataset", "NewsPartDataset", "NewsUpdatorDataset", "UserDataset", "newsample"):
+        assert hasattr(dataset, n)
+    assert dataset.npratio == 4 and dataset.max_his_len == 50
+    for n in ("dcg_score", "ndcg_score", "mrr_score", "compute_amn", "evaluation_split", "roc_auc_score"):
+        assert hasattr(evaluation_functions, n)
+
+
+def test_entrypoint_modules_export_training_loop_names():
+    import client, server  # noqa: E401
+    import main as main_mod
+    import Gradient_Averaging_main as ga
+    import Parameter_Averaging_main as pa
+    for m in (main_mod, ga, pa, client):
+        for n in ("train_on_step", "Trainer", "process_news_grad", "process_user_grad", "main"):
+            assert hasattr(m, n), (m.__name__, n)
+    assert client.send_saved_model and server.handle_client and server.average_all_params_rcvd
+
+
+def test_server_model_constructs_without_data(tiny_bert):
+    from model import ServerUserModel
+    m = ServerUserModel("cpu", bert_config=tiny_bert)                 # upstream raises TypeError here
+    assert m.news_index is None and len(list(m.parameters())) > 0
+
+
+def test_get_and_gen_news_vecs(tiny_bert, tiny_data):
+    from model import UserModel
+    m = UserModel(None, tiny_data.news_index, "cpu", bert_config=tiny_bert)
+    ids = np.array([[3, 4, 3], [7, 3, 0]])
+    v = m.gen_news_vecs(ids)
+    assert v.shape == (2, 3, 400)
+    torch.testing.assert_close(v[0, 0], v[1, 1])                      # same id, same vector (de-dup is exact)
+    torch.testing.assert_close(m.get_news_vecs([3])[0], v[0, 0])
+
+
+def test_synthetic_userdata_cli_and_loader(tmp_path):
+    out = str(tmp_path / "UserData")
+    r = subprocess.run([sys.executable, "-m", "fedrec_b200.data.synthetic", "--out", out, "--num_news", "200",
+                        "--num_train", "16", "--num_valid", "4", "--title_len", "10"], cwd=ROOT, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    from fedrec_b200.data import load_user_data
+    nid2index, news_index, train_sam, valid_sam = load_user_data(out)
+    assert news_index.shape == (200, 2, 10) and len(train_sam) == 16 and len(valid_sam) == 4 and nid2index["<unk>"] == 0
+
+
+def test_single_process_entrypoint_runs_and_resumes(tmp_path):
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    common = ["--synthetic", "--num_news", "128", "--num_train", "32", "--num_valid", "4", "--title_len", "8", "--bert_layers", "1",
+              "--bert_dim", "32", "--bert_ffn", "64", "--bert_heads", "2", "--device", "cpu", "--log_dir", str(tmp_path / "logs"),
+              "--snapshot_path", str(tmp_path / "snapshot.pt")]
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "main.py"), "2", "4", "1"] + common, env=env, cwd=str(tmp_path),
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
+    snap = torch.load(tmp_path / "snapshot.pt", weights_only=False)
+    assert snap["EPOCHS_RUN"] == 2 and "MODEL_STATE" in snap
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "main.py"), "3", "4", "1"] + common, env=env, cwd=str(tmp_path),
+                       capture_output=True, text=True)
+    assert r.returncode == 0 and "Resuming training from snapshot at Epoch 2" in r.stdout
+    assert r.stdout.count("training_loss") == 1                      # only epoch 2 ran: no repeated epoch
