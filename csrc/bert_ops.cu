@@ -82,20 +82,35 @@ __global__ void __launch_bounds__(256) embed_ln_kernel(const int* __restrict__ t
   }
 }
 
-__global__ void __launch_bounds__(256) layernorm_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
+// Persistent: a few fat blocks, every warp walks rows with two independent rows in flight so the
+// load latency of one row hides behind the reductions of the other.
+__global__ void __launch_bounds__(512) layernorm_kernel(const __nv_bfloat16* __restrict__ in, __nv_bfloat16* __restrict__ out,
                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
                                                         int rows_max, const int* __restrict__ count_dev, int rows_per_item,
                                                         float eps) {
   const int lane = threadIdx.x & 31;
   int rows = rows_max;
   if (count_dev) rows = min(rows_max, *count_dev * rows_per_item);
-  for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += gridDim.x * (blockDim.x >> 5)) {
-    float x[kPerLane];
+  const int nwarps = gridDim.x * (blockDim.x >> 5);
+  const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  for (int row = w; row < rows; row += 2 * nwarps) {
+    const int row2 = row + nwarps;
+    const bool has2 = row2 < rows;
+    float x[kPerLane], y[kPerLane];
 #pragma unroll
     for (int c = 0; c < 3; ++c) load8(in + (size_t)row * kHid + c * 256 + lane * 8, x + c * 8);
+    if (has2) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) load8(in + (size_t)row2 * kHid + c * 256 + lane * 8, y + c * 8);
+    }
     warp_layernorm(x, gamma, beta, lane, eps);
 #pragma unroll
     for (int c = 0; c < 3; ++c) store8(out + (size_t)row * kHid + c * 256 + lane * 8, x + c * 8);
+    if (has2) {
+      warp_layernorm(y, gamma, beta, lane, eps);
+#pragma unroll
+      for (int c = 0; c < 3; ++c) store8(out + (size_t)row2 * kHid + c * 256 + lane * 8, y + c * 8);
+    }
   }
 }
 
@@ -390,7 +405,7 @@ FR_API int fr_layernorm_bf16(const void* in, void* out, const float* gamma, cons
                              const int* count_dev, int rows_per_item, float eps, int hidden, void* stream) {
   FR_REQUIRE(hidden == kHid, "fr_layernorm_bf16: hidden=%d (only %d is built)", hidden, kHid);
   if (rows == 0) return 0;
-  layernorm_kernel<<<grid_for(rows, 8, kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(
+  layernorm_kernel<<<grid_for(rows, 32, kNumSMs * 3), 512, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)in, (__nv_bfloat16*)out, gamma, beta, rows, count_dev, rows_per_item, eps);
   FR_LAUNCH_CHECK();
   return 0;

@@ -190,6 +190,8 @@ class BatchSampler:
                 cand, his = cand.pin_memory(), his.pin_memory()
             self._bufs.append((cand, his))
         self._flip = 0
+        self._last = 0
+        self._events = [None, None]          # CUDA event of the last async copy out of each staging buffer
         self._order = np.zeros(0, dtype=np.int64)
         self._cursor = 0
         self.epoch = 0
@@ -211,7 +213,12 @@ class BatchSampler:
 
     def next(self) -> Tuple[torch.Tensor, torch.Tensor]:
         idx = self._next_indices()
+        ev = self._events[self._flip]
+        if ev is not None:                   # the host must not overwrite a pinned buffer an H2D copy still reads
+            ev.synchronize()
+            self._events[self._flip] = None
         cand, his = self._bufs[self._flip]
+        self._last = self._flip
         self._flip ^= 1
         t = self.table
         cand_np = cand.numpy()
@@ -230,6 +237,16 @@ class BatchSampler:
                 cand_np[j, 1 + n:] = 0
         his.numpy()[:] = t.his[idx]
         return cand, his
+
+    def copy_to(self, cand_dev: torch.Tensor, his_dev: torch.Tensor) -> None:
+        """Async H2D copy of the batch returned by the last ``next()``; remembers when the staging buffer is free again."""
+        cand, his = self._bufs[self._last]
+        cand_dev.copy_(cand, non_blocking=True)
+        his_dev.copy_(his, non_blocking=True)
+        if cand_dev.is_cuda:
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(cand_dev.device))
+            self._events[self._last] = ev
 
     def __iter__(self):
         while True:

@@ -43,7 +43,7 @@ def make_synthetic_mind(num_news: int = 4096, num_train: int = 512, num_valid: i
                         title_len: int = 30, max_his_len: int = 50, topics: int = 16,
                         vocab_size: int = 30522, seed: int = 0, client: int = 0,
                         negs_per_impression: int = 20, zipf_a: float = 1.1,
-                        min_his: int = 5) -> SyntheticMind:
+                        min_his: int = 5, generic_frac: float = 0.25, liked_topics: int = 2) -> SyntheticMind:
     rng = np.random.default_rng(seed)                       # news table: shared by all clients
     urng = np.random.default_rng(seed * 1000003 + 17 * (client + 1))  # users: per client
     N, T = num_news, title_len
@@ -58,7 +58,7 @@ def make_synthetic_mind(num_news: int = 4096, num_train: int = 512, num_valid: i
     base = lo + topic * span
     body = base[:, None] + rng.integers(0, min(span, 512), size=(N, T))
     generic = rng.integers(lo, vocab_size, size=(N, T))
-    use_generic = rng.random((N, T)) < 0.25
+    use_generic = rng.random((N, T)) < generic_frac
     body = np.where(use_generic, generic, body)
     pos = np.arange(T)[None, :]
     inside = (pos >= 1) & (pos < lengths[:, None])
@@ -88,7 +88,7 @@ def make_synthetic_mind(num_news: int = 4096, num_train: int = 512, num_valid: i
     def make(n: int, uid0: int) -> List[tuple]:
         sams = []
         for s in range(n):
-            liked = urng.choice(topics, size=2, replace=False)
+            liked = urng.choice(topics, size=liked_topics, replace=False)
             other = np.setdiff1d(np.arange(topics), liked)
             L = int(urng.integers(min_his, max_his_len + max_his_len // 2))
             his = draw(liked, L)

@@ -124,9 +124,8 @@ class FederatedRunner:
             self.model.on_weights_changed()
 
     def next_batch(self):
-        cand, his = self.sampler.next()
-        self._dev_cand.copy_(cand, non_blocking=True)
-        self._dev_his.copy_(his, non_blocking=True)
+        self.sampler.next()
+        self.sampler.copy_to(self._dev_cand, self._dev_his)
         return self._dev_cand, self._dev_his
 
     def local_step(self) -> torch.Tensor:
