@@ -65,7 +65,8 @@ class FederatedRunner:
         allocator = None
         if self.device.type == "cuda" and self.W > 1 and cfg.transport == "nvlink":
             from ..parallel.symm import SymmetricHeap
-            self.symm = SymmetricHeap.create(self.info)
+            heap_mb = 64 + (288 if cfg.average_frozen else 0)       # the full fp32 state_dict is 257.6 MiB
+            self.symm = SymmetricHeap.create(self.info, heap_bytes=heap_mb << 20)
             allocator = self.symm.alloc_f32
         # ---- model -------------------------------------------------------------------
         if self.is_server:
@@ -119,8 +120,7 @@ class FederatedRunner:
         self.param_agg.broadcast_(self.model.flat.param, src)
         # the frozen trunk is seeded identically on every rank; broadcast only when asked to
         if self.cfg.average_frozen:
-            for p in self.model.text_encoder.DistillBert.parameters():
-                dist.broadcast(p.data, src=src)
+            self.param_agg.broadcast_(self.model.flat_frozen.param, src)
             self.model.on_weights_changed()
 
     def next_batch(self):
@@ -195,10 +195,8 @@ class FederatedRunner:
         return float(loss)
 
     def _average_frozen(self, weights) -> None:
-        tot = sum(weights)
-        for p in self.model.text_encoder.DistillBert.parameters():
-            p.data.mul_(weights[self.rank] / tot)
-            dist.all_reduce(p.data)
+        """The frozen trunk too (upstream averages all 116 tensors): one kernel over the 265 MB flat buffer."""
+        self.param_agg.average_(self.model.flat_frozen.param, weights)
         self.model.on_weights_changed()
 
     def run_client_server(self) -> float:

@@ -69,6 +69,13 @@ class UserModel(nn.Module):
         self.set_news_index(news_index)
         trainable = [(n, p) for n, p in self.named_parameters() if p.requires_grad]
         self.flat = FlatState(trainable, self.device, allocator=flat_allocator)
+        # With average_frozen the 100 frozen DistilBERT tensors also become views of one flat buffer (in the peer-mapped
+        # heap when there is one), so the full 270 MB state_dict is averaged/broadcast by one kernel (upstream: 116
+        # all-reduces per epoch, Parameter_Averaging_main.py:144-148).
+        self.flat_frozen = None
+        if self.cfg.average_frozen:
+            frozen = [(n, p) for n, p in self.named_parameters() if not p.requires_grad]
+            self.flat_frozen = FlatState(frozen, self.device, allocator=flat_allocator, with_adam=False, with_grad=False)
         self._init_grad_param()
         self._cache: Optional[Dict[str, torch.Tensor]] = None
         self._fused = None        # engine.fused.FusedStep, attached lazily by the engine
@@ -251,6 +258,8 @@ class UserModel(nn.Module):
     def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
         out = super().load_state_dict(state_dict, strict=strict, assign=False)
         self.flat.rebind()
+        if self.flat_frozen is not None:
+            self.flat_frozen.rebind()
         self.on_weights_changed()
         return out
 

@@ -21,7 +21,8 @@ ALIGN_ELEMS = 32  # 128 bytes of fp32
 
 class FlatState:
     def __init__(self, named_params: List[Tuple[str, nn.Parameter]], device: torch.device,
-                 allocator: Optional[Callable[[int], torch.Tensor]] = None, with_adam: bool = True):
+                 allocator: Optional[Callable[[int], torch.Tensor]] = None, with_adam: bool = True,
+                 with_grad: bool = True):
         self.names = [n for n, _ in named_params]
         self.params = [p for _, p in named_params]
         self.offsets: Dict[str, Tuple[int, int]] = {}
@@ -33,9 +34,11 @@ class FlatState:
         self.payload_numel = sum(p.numel() for p in self.params)
         alloc = allocator or (lambda n: torch.zeros(n, dtype=torch.float32, device=device))
         self.param = alloc(self.numel)
-        self.grad = alloc(self.numel)
         self.param.zero_()
-        self.grad.zero_()
+        self.grad = None
+        if with_grad:
+            self.grad = alloc(self.numel)
+            self.grad.zero_()
         if with_adam:
             self.exp_avg = torch.zeros(self.numel, dtype=torch.float32, device=device)
             self.exp_avg_sq = torch.zeros(self.numel, dtype=torch.float32, device=device)
@@ -46,7 +49,8 @@ class FlatState:
                 view = self.param[o:o + k].view(p.shape)
                 view.copy_(p.data.to(device))
                 p.data = view
-                p.grad = self.grad[o:o + k].view(p.shape)
+                if with_grad:
+                    p.grad = self.grad[o:o + k].view(p.shape)
 
     def view(self, name: str, grad: bool = False) -> torch.Tensor:
         o, k = self.offsets[name]
@@ -62,7 +66,8 @@ class FlatState:
                 with torch.no_grad():
                     self.param[o:o + k].view(p.shape).copy_(p.data)
                 p.data = self.param[o:o + k].view(p.shape)
-            p.grad = self.grad[o:o + k].view(p.shape)
+            if self.grad is not None:
+                p.grad = self.grad[o:o + k].view(p.shape)
 
     def zero_grad(self) -> None:
         self.grad.zero_()
