@@ -47,6 +47,7 @@ struct AggParams {
   uint32_t epoch;             // > 0, strictly increasing per launch on this pad set
   float clip, noise_std, scale;
   unsigned long long seed;
+  int uniform_weights;        // param average: all participating weights equal → no in-place pre-scaling needed for NVLS
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -136,8 +137,10 @@ __global__ void __launch_bounds__(512) aggregate_kernel(const AggParams p) {
     const float sq = __uint_as_float(ld_relaxed_sys(my_pad + kPadSumSq));
     my_scale = fminf(1.f, p.clip / fmaxf(sqrtf(sq), 1e-30f));
   }
-  if (kNvls) {
-    // values read through the switch must be final in memory: apply scale/noise/weight in place
+  // The switch reduces what is in memory, so per-client factors have to be applied in place first — unless there are
+  // none (plain mean, or FedAvg with equal weights: one common factor after the reduction).
+  const bool prepass = kNvls && (kMode == 1 ? !p.uniform_weights : (p.clip > 0.f || p.noise_std > 0.f));
+  if (prepass) {
     const float wgt = (kMode == 1) ? p.weights[r] : my_scale;
     Philox rng(p.seed);
     for (size_t i = tid; i < n4; i += nth) {
@@ -172,13 +175,29 @@ __global__ void __launch_bounds__(512) aggregate_kernel(const AggParams p) {
   const size_t lo = (size_t)r * per;
   const size_t hi = lo + per < n4 ? lo + per : n4;
   Philox rng(p.seed);
-  for (size_t i = lo + tid; i < hi; i += nth) {
+  if (kNvls) {
+    // in-switch reduction + multicast store, four independent 16-byte requests in flight per thread
+    const float post = (kMode == 0) ? p.scale : (p.uniform_weights ? p.weights[r] : 1.f);
+    for (size_t i0 = lo + tid; i0 < hi; i0 += 4 * (size_t)nth) {
+      float4 a[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const size_t i = i0 + (size_t)u * nth;
+        if (i < hi) a[u] = multimem_ld_reduce_v4(p.mc_buf + 4 * i);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const size_t i = i0 + (size_t)u * nth;
+        if (i < hi) {
+          a[u].x *= post; a[u].y *= post; a[u].z *= post; a[u].w *= post;
+          multimem_st_v4(p.mc_buf + 4 * i, a[u]);
+        }
+      }
+    }
+  }
+  for (size_t i = lo + tid; i < hi && !kNvls; i += nth) {
     float4 acc;
-    if (kNvls) {
-      acc = multimem_ld_reduce_v4(p.mc_buf + 4 * i);
-      if (kMode == 0) { acc.x *= p.scale; acc.y *= p.scale; acc.z *= p.scale; acc.w *= p.scale; }
-      multimem_st_v4(p.mc_buf + 4 * i, acc);
-    } else {
+    {
       float4 v[kMaxRanks];
 #pragma unroll
       for (int q = 0; q < kMaxRanks; ++q)
@@ -279,6 +298,9 @@ FR_API int fr_param_average(void* const* bufs_host, void* const* pads_host, void
   }
   p.mc_buf = (float*)mc_buf; p.W = W; p.rank_base = rank_base; p.ranks_here = ranks_here; p.n = n; p.epoch = epoch;
   p.scale = 1.f;
+  p.uniform_weights = 1;                     // every weight equal (a zero-weight server rank breaks uniformity)
+  for (int i = 1; i < W; ++i)
+    if (weights_host[i] != weights_host[0]) p.uniform_weights = 0;
   if (blocks <= 0) blocks = 128;
   return launch_agg(1, mc_buf != nullptr, p, blocks, (cudaStream_t)stream);
 }
