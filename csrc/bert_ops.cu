@@ -31,6 +31,37 @@ __device__ __forceinline__ void store8(__nv_bfloat16* p, const float* v) {
   *reinterpret_cast<uint4*>(p) = q;
 }
 
+// gamma/beta slices of a lane (its 24 columns), loaded once per warp by the persistent kernels
+__device__ __forceinline__ void load_affine(const float* __restrict__ gamma, const float* __restrict__ beta, int lane,
+                                            float* g, float* b) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const int col = c * 256 + lane * 8;
+#pragma unroll
+    for (int i = 0; i < 8; i += 4) {
+      const float4 gv = *reinterpret_cast<const float4*>(gamma + col + i);
+      const float4 bv = *reinterpret_cast<const float4*>(beta + col + i);
+      g[c * 8 + i] = gv.x; g[c * 8 + i + 1] = gv.y; g[c * 8 + i + 2] = gv.z; g[c * 8 + i + 3] = gv.w;
+      b[c * 8 + i] = bv.x; b[c * 8 + i + 1] = bv.y; b[c * 8 + i + 2] = bv.z; b[c * 8 + i + 3] = bv.w;
+    }
+  }
+}
+__device__ __forceinline__ void warp_layernorm_reg(float* x, const float* g, const float* b, float eps) {
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < kPerLane; ++i) s += x[i];
+  const float mean = warp_sum(s) * (1.f / kHid);
+  float q = 0.f;
+#pragma unroll
+  for (int i = 0; i < kPerLane; ++i) {
+    const float d = x[i] - mean;
+    q += d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(q) * (1.f / kHid) + eps);
+#pragma unroll
+  for (int i = 0; i < kPerLane; ++i) x[i] = (x[i] - mean) * rstd * g[i] + b[i];
+}
+
 // x[24] per lane → normalised in place. Two-pass (mean, then centred variance) in registers.
 __device__ __forceinline__ void warp_layernorm(float* x, const float* __restrict__ gamma, const float* __restrict__ beta,
                                                int lane, float eps) {
@@ -63,6 +94,8 @@ __global__ void __launch_bounds__(256) embed_ln_kernel(const int* __restrict__ t
   const int lane = threadIdx.x & 31;
   const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
   const int rows = n_eff * T;
+  float g[kPerLane], b[kPerLane];
+  load_affine(gamma, beta, lane, g, b);
   for (int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); row < rows; row += gridDim.x * (blockDim.x >> 5)) {
     const int n = row / T, t = row - n * T;
     const int item = items ? items[n] : n;
@@ -76,7 +109,7 @@ __global__ void __launch_bounds__(256) embed_ln_kernel(const int* __restrict__ t
 #pragma unroll
       for (int i = 0; i < 8; ++i) x[c * 8 + i] += p[i];
     }
-    warp_layernorm(x, gamma, beta, lane, eps);
+    warp_layernorm_reg(x, g, b, eps);
 #pragma unroll
     for (int c = 0; c < 3; ++c) store8(out + (size_t)row * kHid + c * 256 + lane * 8, x + c * 8);
   }
@@ -93,6 +126,8 @@ __global__ void __launch_bounds__(512) layernorm_kernel(const __nv_bfloat16* __r
   if (count_dev) rows = min(rows_max, *count_dev * rows_per_item);
   const int nwarps = gridDim.x * (blockDim.x >> 5);
   const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  float g[kPerLane], b[kPerLane];
+  load_affine(gamma, beta, lane, g, b);
   for (int row = w; row < rows; row += 2 * nwarps) {
     const int row2 = row + nwarps;
     const bool has2 = row2 < rows;
@@ -103,11 +138,11 @@ __global__ void __launch_bounds__(512) layernorm_kernel(const __nv_bfloat16* __r
 #pragma unroll
       for (int c = 0; c < 3; ++c) load8(in + (size_t)row2 * kHid + c * 256 + lane * 8, y + c * 8);
     }
-    warp_layernorm(x, gamma, beta, lane, eps);
+    warp_layernorm_reg(x, g, b, eps);
 #pragma unroll
     for (int c = 0; c < 3; ++c) store8(out + (size_t)row * kHid + c * 256 + lane * 8, x + c * 8);
     if (has2) {
-      warp_layernorm(y, gamma, beta, lane, eps);
+      warp_layernorm_reg(y, g, b, eps);
 #pragma unroll
       for (int c = 0; c < 3; ++c) store8(out + (size_t)row2 * kHid + c * 256 + lane * 8, y + c * 8);
     }
@@ -394,7 +429,7 @@ FR_API int fr_bert_embed_ln(const int* tokens, const int* items, const int* coun
                             float eps, int hidden, void* stream) {
   FR_REQUIRE(hidden == kHid, "fr_bert_embed_ln: hidden=%d (only %d is built)", hidden, kHid);
   if (n_items == 0) return 0;
-  embed_ln_kernel<<<grid_for((long long)n_items * T, 8, kNumSMs * 8), 256, 0, (cudaStream_t)stream>>>(
+  embed_ln_kernel<<<grid_for((long long)n_items * T, 8, kNumSMs * 4), 256, 0, (cudaStream_t)stream>>>(
       tokens, items, count_dev, n_items, T, (const __nv_bfloat16*)word, (const __nv_bfloat16*)pos, gamma, beta,
       (__nv_bfloat16*)out, eps);
   FR_LAUNCH_CHECK();
