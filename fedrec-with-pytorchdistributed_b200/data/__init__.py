@@ -1,5 +1,5 @@
 from .dataset import (  # noqa: F401
     NewsDataset, NewsPartDataset, NewsUpdatorDataset, TrainDataset, UserDataset,
-    ImpressionTable, BatchSampler, newsample, npratio, max_his_len, load_user_data,
+    ImpressionTable, BatchSampler, DevicePrefetcher, newsample, npratio, max_his_len, load_user_data,
 )
 from .synthetic import SyntheticMind, make_synthetic_mind  # noqa: F401

@@ -253,6 +253,54 @@ class BatchSampler:
             yield self.next()
 
 
+class DevicePrefetcher:
+    """Keeps the next round's ids in flight: the H2D copy of batch i+1 runs on its own stream while step i computes.
+
+    ``next()`` returns device tensors ``(cand[B, C], his[B, L])`` that stay valid until the following ``next()``;
+    two device slots and two pinned slots alternate, ordered by CUDA events (no host synchronisation in steady state).
+    """
+
+    def __init__(self, sampler: BatchSampler, device: torch.device):
+        self.sampler, self.device = sampler, torch.device(device)
+        self.cuda = self.device.type == "cuda"
+        L = sampler.table.max_his_len
+        self._slots = [(torch.zeros(sampler.B, sampler.C, dtype=torch.int32, device=self.device),
+                        torch.zeros(sampler.B, L, dtype=torch.int32, device=self.device)) for _ in range(2)]
+        self._stream = torch.cuda.Stream(device=self.device) if self.cuda else None
+        self._ready = [None, None]           # copy finished (consumer waits)
+        self._free = [None, None]            # consumer finished with the slot (copy stream waits)
+        self._i = 0
+        self._issue(0)
+
+    def _issue(self, slot: int) -> None:
+        self.sampler.next()
+        c, h = self._slots[slot]
+        if not self.cuda:
+            self.sampler.copy_to(c, h)
+            return
+        with torch.cuda.stream(self._stream):
+            if self._free[slot] is not None:
+                self._stream.wait_event(self._free[slot])
+            self.sampler.copy_to(c, h)
+            ev = torch.cuda.Event()
+            ev.record(self._stream)
+            self._ready[slot] = ev
+
+    def next(self):
+        slot = self._i & 1
+        if self.cuda:
+            cur = torch.cuda.current_stream(self.device)
+            cur.wait_event(self._ready[slot])
+            prev = slot ^ 1                  # the slot handed out last time is free once work queued so far is done
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self._free[prev] = ev
+        self._i += 1
+        out = self._slots[slot]
+        self._issue(slot ^ 1)
+        return out
+
+
 def _floyd_sample(rng, n: int, k: int) -> np.ndarray:
     """k distinct integers from range(n) without materialising a permutation."""
     chosen: List[int] = []

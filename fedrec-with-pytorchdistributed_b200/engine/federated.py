@@ -30,7 +30,7 @@ import torch
 import torch.distributed as dist
 
 from ..config import FedRecConfig
-from ..data import BatchSampler, ImpressionTable, load_user_data, make_synthetic_mind
+from ..data import BatchSampler, DevicePrefetcher, ImpressionTable, load_user_data, make_synthetic_mind
 from ..models import ServerUserModel, UserModel
 from ..parallel import GradAggregator, ParamAggregator, init_distributed, shutdown_distributed
 from ..utils import checkpoint as ckpt
@@ -87,8 +87,7 @@ class FederatedRunner:
             table = ImpressionTable(train_sam, nid2index, cfg.max_his_len)
             self.sampler = BatchSampler(table, cfg.batch_size, cfg.npratio, seed=cfg.seed + 101 * self.rank,
                                         pin=self.device.type == "cuda")
-            self._dev_cand = torch.zeros(cfg.batch_size, cfg.num_candidates, dtype=torch.int32, device=self.device)
-            self._dev_his = torch.zeros(cfg.batch_size, cfg.max_his_len, dtype=torch.int32, device=self.device)
+            self.prefetch = DevicePrefetcher(self.sampler, self.device)
         self.logger = MetricsLogger(cfg.log_dir, cfg.run_name, self.rank, enabled=bool(cfg.log_dir))
         self.tracer = Tracer(enabled=os.environ.get("FEDREC_TRACE") == "1", device=self.device)
         self.faults = FaultInjector()
@@ -124,9 +123,7 @@ class FederatedRunner:
             self.model.on_weights_changed()
 
     def next_batch(self):
-        self.sampler.next()
-        self.sampler.copy_to(self._dev_cand, self._dev_his)
-        return self._dev_cand, self._dev_his
+        return self.prefetch.next()
 
     def local_step(self) -> torch.Tensor:
         cand, his = self.next_batch()

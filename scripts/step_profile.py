@@ -1,0 +1,35 @@
+"""In-situ per-kernel device time of one training step (warm caches, real clocks) via the PyTorch profiler (CUPTI)."""
+import os
+import sys
+
+import numpy as np
+import torch
+from torch.profiler import ProfilerActivity, profile
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
+from fedrec_b200.config import FedRecConfig  # noqa: E402
+from fedrec_b200.engine import TrainStep  # noqa: E402
+from fedrec_b200.models import UserModel  # noqa: E402
+
+DEV = "cuda:0"
+cfg = FedRecConfig(batch_size=50, title_len=30, num_news=bench.NUM_NEWS, cuda_graph=False, clip_norm=2.0, noise_multiplier=0.05)
+model = UserModel(None, bench.synthetic_news_index(np), DEV, config=cfg)
+step = TrainStep(model, cfg)
+cand_h, his_h = bench.make_batches(np, 16, 0)
+cand = torch.from_numpy(cand_h).to(torch.int32).to(DEV)
+his = torch.from_numpy(his_h).to(torch.int32).to(DEV)
+for i in range(6):
+    step.run(cand[i], his[i]); model.adam_step()
+torch.cuda.synchronize()
+N = 8
+with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+    for i in range(6, 6 + N):
+        step.run(cand[i], his[i]); model.adam_step()
+    torch.cuda.synchronize()
+rows = [(e.key, e.device_time_total / N, e.count / N) for e in prof.key_averages() if e.device_time_total > 0]
+rows.sort(key=lambda r: -r[1])
+tot = sum(r[1] for r in rows)
+print(f"device time per step: {tot:.1f} us over {sum(r[2] for r in rows):.0f} kernels")
+for k, us, n in rows[:28]:
+    print(f"{us:9.1f} us {100 * us / tot:5.1f}%  x{n:<4.0f} {k[:110]}")

@@ -72,3 +72,14 @@ def test_batch_sampler(tiny_data):
         pos2neg.setdefault(tiny_data.nid2index[s[1]], set()).update(tiny_data.nid2index[n] for n in s[2])
     for row in cand.numpy():
         assert set(row[1:].tolist()) <= pos2neg[int(row[0])] | {0}
+
+
+def test_device_prefetcher_yields_the_sampler_sequence(tiny_data):
+    from fedrec_b200.data import DevicePrefetcher
+    tab = ImpressionTable(tiny_data.train_sam, tiny_data.nid2index)
+    ref = BatchSampler(tab, 8, seed=3, pin=False)
+    pre = DevicePrefetcher(BatchSampler(tab, 8, seed=3, pin=False), torch.device("cpu"))
+    for _ in range(5):
+        c0, h0 = ref.next()
+        c1, h1 = pre.next()
+        assert torch.equal(c0, c1) and torch.equal(h0, h1)
