@@ -18,8 +18,7 @@
 namespace fr {
 
 constexpr int kMaxL = 64;       // history length limit (reference: 50)
-constexpr int kFwdWarps = 2;    // (user, head) jobs per block, forward
-constexpr int kBwdWarps = 1;    // backward keeps q, k, v, dctx of one job in shared memory
+constexpr int kJobThreads = 64; // one (user, head) job per block; thread t owns query row t (and key row t in the backward)
 
 __device__ __forceinline__ void red_add_f32x4(float* addr, float4 v) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
@@ -84,32 +83,31 @@ __global__ void __launch_bounds__(256) ue_scatter_dx_kernel(const float* __restr
 }
 
 // ---------------------------------------------------------------------------------------------------
-// Multi-head self-attention over the history, one warp per (user, head).
+// Multi-head self-attention over the history, one 64-thread block per (user, head).
 // qkv bf16 [B*L, 3*H*dk] (q | k | v), ctx bf16 [B*L, H*dk], stats fp32 [B*H*L, 2] = (row max, denominator).
-// Lane i owns query rows i and i+32.
+// Thread i owns query row i.
 // ---------------------------------------------------------------------------------------------------
 template <int DK>
-__global__ void __launch_bounds__(kFwdWarps * 32) ue_mha_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, const int* __restrict__ his_ids,
-                                                         __nv_bfloat16* __restrict__ ctx, float* __restrict__ stats,
-                                                         int B, int L, int H, float scale, int use_mask) {
-  __shared__ float sK[kFwdWarps][kMaxL][DK + 1];
-  __shared__ float sV[kFwdWarps][kMaxL][DK + 1];
-  __shared__ float sM[kFwdWarps][kMaxL];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int job = blockIdx.x * kFwdWarps + w;
-  if (job >= B * H) return;
+__global__ void __launch_bounds__(kJobThreads) ue_mha_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, const int* __restrict__ his_ids,
+                                                                 __nv_bfloat16* __restrict__ ctx, float* __restrict__ stats,
+                                                                 int B, int L, int H, float scale, int use_mask) {
+  __shared__ float sK[kMaxL][DK + 1];
+  __shared__ float sV[kMaxL][DK + 1];
+  __shared__ float sM[kMaxL];
+  const int tid = threadIdx.x;
+  const int job = blockIdx.x;
   const int b = job / H, h = job - b * H;
   const int ld = 3 * H * DK;
   const size_t row0 = (size_t)b * L;
-  for (int i = lane; i < L * DK; i += 32) {
+  for (int i = tid; i < L * DK; i += kJobThreads) {
     const int r = i / DK, d = i - r * DK;
     const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * DK + d;
-    sK[w][r][d] = __bfloat162float(base[H * DK]);
-    sV[w][r][d] = __bfloat162float(base[2 * H * DK]);
+    sK[r][d] = __bfloat162float(base[H * DK]);
+    sV[r][d] = __bfloat162float(base[2 * H * DK]);
   }
-  for (int j = lane; j < L; j += 32) sM[w][j] = (use_mask && his_ids[row0 + j] == 0) ? 0.f : 1.f;
-  __syncwarp();
-  for (int i = lane; i < L; i += 32) {
+  for (int j = tid; j < L; j += kJobThreads) sM[j] = (use_mask && his_ids[row0 + j] == 0) ? 0.f : 1.f;
+  __syncthreads();
+  for (int i = tid; i < L; i += kJobThreads) {
     float q[DK];
 #pragma unroll
     for (int d = 0; d < DK; ++d) q[d] = __bfloat162float(qkv[(row0 + i) * ld + h * DK + d]) * scale;
@@ -117,7 +115,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32) ue_mha_fwd_kernel(const __nv_b
     for (int j = 0; j < L; ++j) {
       float s = 0.f;
 #pragma unroll
-      for (int d = 0; d < DK; ++d) s = fmaf(q[d], sK[w][j][d], s);
+      for (int d = 0; d < DK; ++d) s = fmaf(q[d], sK[j][d], s);
       m = fmaxf(m, s);
     }
     float z = 0.f, acc[DK];
@@ -126,11 +124,11 @@ __global__ void __launch_bounds__(kFwdWarps * 32) ue_mha_fwd_kernel(const __nv_b
     for (int j = 0; j < L; ++j) {
       float s = 0.f;
 #pragma unroll
-      for (int d = 0; d < DK; ++d) s = fmaf(q[d], sK[w][j][d], s);
-      const float e = __expf(s - m) * sM[w][j];
+      for (int d = 0; d < DK; ++d) s = fmaf(q[d], sK[j][d], s);
+      const float e = __expf(s - m) * sM[j];
       z += e;
 #pragma unroll
-      for (int d = 0; d < DK; ++d) acc[d] = fmaf(e, sV[w][j][d], acc[d]);
+      for (int d = 0; d < DK; ++d) acc[d] = fmaf(e, sV[j][d], acc[d]);
     }
     z += 1e-8f * __expf(-m);
     const float inv = 1.f / z;
@@ -146,49 +144,48 @@ __global__ void __launch_bounds__(kFwdWarps * 32) ue_mha_fwd_kernel(const __nv_b
 // Backward of the attention: dctx bf16 [B*L, H*dk] → dqkv bf16 [B*L, 3*H*dk]. Probabilities are
 // recomputed from q, k and the saved (max, denominator).
 template <int DK>
-__global__ void __launch_bounds__(kBwdWarps * 32) ue_mha_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dctx,
-                                                         const float* __restrict__ stats, const int* __restrict__ his_ids,
-                                                         __nv_bfloat16* __restrict__ dqkv, int B, int L, int H, float scale,
-                                                         int use_mask) {
-  __shared__ float sQ[kBwdWarps][kMaxL][DK + 1];     // q * scale
-  __shared__ float sK[kBwdWarps][kMaxL][DK + 1];
-  __shared__ float sV[kBwdWarps][kMaxL][DK + 1];
-  __shared__ float sG[kBwdWarps][kMaxL][DK + 1];     // dctx
-  __shared__ float sMx[kBwdWarps][kMaxL], sZ[kBwdWarps][kMaxL], sDd[kBwdWarps][kMaxL], sMask[kBwdWarps][kMaxL];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int job = blockIdx.x * kBwdWarps + w;
-  if (job >= B * H) return;
+__global__ void __launch_bounds__(kJobThreads) ue_mha_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dctx,
+                                                                 const float* __restrict__ stats, const int* __restrict__ his_ids,
+                                                                 __nv_bfloat16* __restrict__ dqkv, int B, int L, int H, float scale,
+                                                                 int use_mask) {
+  __shared__ float sQ[kMaxL][DK + 1];     // q * scale
+  __shared__ float sK[kMaxL][DK + 1];
+  __shared__ float sV[kMaxL][DK + 1];
+  __shared__ float sG[kMaxL][DK + 1];     // dctx
+  __shared__ float sMx[kMaxL], sZ[kMaxL], sDd[kMaxL], sMask[kMaxL];
+  const int tid = threadIdx.x;
+  const int job = blockIdx.x;
   const int b = job / H, h = job - b * H;
   const int ld = 3 * H * DK;
   const size_t row0 = (size_t)b * L;
-  for (int i = lane; i < L * DK; i += 32) {
+  for (int i = tid; i < L * DK; i += kJobThreads) {
     const int r = i / DK, d = i - r * DK;
     const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * DK + d;
-    sQ[w][r][d] = __bfloat162float(base[0]) * scale;
-    sK[w][r][d] = __bfloat162float(base[H * DK]);
-    sV[w][r][d] = __bfloat162float(base[2 * H * DK]);
-    sG[w][r][d] = __bfloat162float(dctx[(row0 + r) * (size_t)(H * DK) + h * DK + d]);
+    sQ[r][d] = __bfloat162float(base[0]) * scale;
+    sK[r][d] = __bfloat162float(base[H * DK]);
+    sV[r][d] = __bfloat162float(base[2 * H * DK]);
+    sG[r][d] = __bfloat162float(dctx[(row0 + r) * (size_t)(H * DK) + h * DK + d]);
   }
-  for (int j = lane; j < L; j += 32) {
-    sMx[w][j] = stats[((size_t)job * L + j) * 2];
-    sZ[w][j] = stats[((size_t)job * L + j) * 2 + 1];
-    sMask[w][j] = (use_mask && his_ids[row0 + j] == 0) ? 0.f : 1.f;
+  for (int j = tid; j < L; j += kJobThreads) {
+    sMx[j] = stats[((size_t)job * L + j) * 2];
+    sZ[j] = stats[((size_t)job * L + j) * 2 + 1];
+    sMask[j] = (use_mask && his_ids[row0 + j] == 0) ? 0.f : 1.f;
   }
-  __syncwarp();
-  // pass 1 (lane = query i): Dd_i = sum_j P_ij dP_ij, then dQ_i = scale * sum_j dS_ij K_j
-  for (int i = lane; i < L; i += 32) {
-    const float m = sMx[w][i], invz = 1.f / sZ[w][i];
+  __syncthreads();
+  // pass 1 (thread = query i): Dd_i = sum_j P_ij dP_ij, then dQ_i = scale * sum_j dS_ij K_j
+  for (int i = tid; i < L; i += kJobThreads) {
+    const float m = sMx[i], invz = 1.f / sZ[i];
     float dd = 0.f;
     for (int j = 0; j < L; ++j) {
       float s = 0.f, dp = 0.f;
 #pragma unroll
       for (int d = 0; d < DK; ++d) {
-        s = fmaf(sQ[w][i][d], sK[w][j][d], s);
-        dp = fmaf(sG[w][i][d], sV[w][j][d], dp);
+        s = fmaf(sQ[i][d], sK[j][d], s);
+        dp = fmaf(sG[i][d], sV[j][d], dp);
       }
-      dd = fmaf(__expf(s - m) * sMask[w][j] * invz, dp, dd);
+      dd = fmaf(__expf(s - m) * sMask[j] * invz, dp, dd);
     }
-    sDd[w][i] = dd;
+    sDd[i] = dd;
     float dq[DK];
 #pragma unroll
     for (int d = 0; d < DK; ++d) dq[d] = 0.f;
@@ -196,38 +193,38 @@ __global__ void __launch_bounds__(kBwdWarps * 32) ue_mha_bwd_kernel(const __nv_b
       float s = 0.f, dp = 0.f;
 #pragma unroll
       for (int d = 0; d < DK; ++d) {
-        s = fmaf(sQ[w][i][d], sK[w][j][d], s);
-        dp = fmaf(sG[w][i][d], sV[w][j][d], dp);
+        s = fmaf(sQ[i][d], sK[j][d], s);
+        dp = fmaf(sG[i][d], sV[j][d], dp);
       }
-      const float ds = __expf(s - m) * sMask[w][j] * invz * (dp - dd);
+      const float ds = __expf(s - m) * sMask[j] * invz * (dp - dd);
 #pragma unroll
-      for (int d = 0; d < DK; ++d) dq[d] = fmaf(ds, sK[w][j][d], dq[d]);
+      for (int d = 0; d < DK; ++d) dq[d] = fmaf(ds, sK[j][d], dq[d]);
     }
     __nv_bfloat16* op = dqkv + (row0 + i) * ld + h * DK;
 #pragma unroll
     for (int d = 0; d < DK; d += 2)
       *reinterpret_cast<__nv_bfloat162*>(op + d) = __floats2bfloat162_rn(dq[d] * scale, dq[d + 1] * scale);
   }
-  __syncwarp();
-  // pass 2 (lane = key j): dV_j = sum_i P_ij dctx_i ; dK_j = sum_i dS_ij (q_i * scale)
-  for (int j = lane; j < L; j += 32) {
+  __syncthreads();
+  // pass 2 (thread = key j): dV_j = sum_i P_ij dctx_i ; dK_j = sum_i dS_ij (q_i * scale)
+  for (int j = tid; j < L; j += kJobThreads) {
     float dk[DK], dv[DK];
 #pragma unroll
     for (int d = 0; d < DK; ++d) { dk[d] = 0.f; dv[d] = 0.f; }
-    const float mk = sMask[w][j];
+    const float mk = sMask[j];
     for (int i = 0; i < L; ++i) {
       float s = 0.f, dp = 0.f;
 #pragma unroll
       for (int d = 0; d < DK; ++d) {
-        s = fmaf(sQ[w][i][d], sK[w][j][d], s);
-        dp = fmaf(sG[w][i][d], sV[w][j][d], dp);
+        s = fmaf(sQ[i][d], sK[j][d], s);
+        dp = fmaf(sG[i][d], sV[j][d], dp);
       }
-      const float pij = __expf(s - sMx[w][i]) * mk / sZ[w][i];
-      const float ds = pij * (dp - sDd[w][i]);
+      const float pij = __expf(s - sMx[i]) * mk / sZ[i];
+      const float ds = pij * (dp - sDd[i]);
 #pragma unroll
       for (int d = 0; d < DK; ++d) {
-        dv[d] = fmaf(pij, sG[w][i][d], dv[d]);
-        dk[d] = fmaf(ds, sQ[w][i][d], dk[d]);     // sQ already carries the 1/sqrt(dk) factor
+        dv[d] = fmaf(pij, sG[i][d], dv[d]);
+        dk[d] = fmaf(ds, sQ[i][d], dk[d]);     // sQ already carries the 1/sqrt(dk) factor
       }
     }
     __nv_bfloat16* op = dqkv + (row0 + j) * ld + h * DK;
@@ -497,10 +494,10 @@ FR_API int fr_ue_mha_fwd(const void* qkv, const int* his_ids, void* ctx, float* 
   FR_REQUIRE(dk == 20 || dk == 32 || dk == 16, "fr_ue_mha_fwd: head dim %d not built (16, 20, 32)", dk);
   FR_REQUIRE(!use_mask || his_ids, "fr_ue_mha_fwd: mask needs his_ids");
   if (B == 0) return 0;
-  const int blocks = (B * H + kFwdWarps - 1) / kFwdWarps;
+  const int blocks = B * H;
   const float scale = 1.f / sqrtf((float)dk);
   cudaStream_t s = (cudaStream_t)stream;
-#define FR_GO(DK) ue_mha_fwd_kernel<DK><<<blocks, kFwdWarps * 32, 0, s>>>((const __nv_bfloat16*)qkv, his_ids, (__nv_bfloat16*)ctx, stats, B, L, H, scale, use_mask)
+#define FR_GO(DK) ue_mha_fwd_kernel<DK><<<blocks, kJobThreads, 0, s>>>((const __nv_bfloat16*)qkv, his_ids, (__nv_bfloat16*)ctx, stats, B, L, H, scale, use_mask)
   if (dk == 20) FR_GO(20); else if (dk == 32) FR_GO(32); else FR_GO(16);
 #undef FR_GO
   FR_LAUNCH_CHECK();
@@ -512,10 +509,10 @@ FR_API int fr_ue_mha_bwd(const void* qkv, const void* dctx, const float* stats, 
   FR_REQUIRE(L >= 1 && L <= kMaxL, "fr_ue_mha_bwd: L=%d must be in [1,%d]", L, kMaxL);
   FR_REQUIRE(dk == 20 || dk == 32 || dk == 16, "fr_ue_mha_bwd: head dim %d not built (16, 20, 32)", dk);
   if (B == 0) return 0;
-  const int blocks = (B * H + kBwdWarps - 1) / kBwdWarps;
+  const int blocks = B * H;
   const float scale = 1.f / sqrtf((float)dk);
   cudaStream_t s = (cudaStream_t)stream;
-#define FR_GO(DK) ue_mha_bwd_kernel<DK><<<blocks, kBwdWarps * 32, 0, s>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dctx, stats, his_ids, (__nv_bfloat16*)dqkv, B, L, H, scale, use_mask)
+#define FR_GO(DK) ue_mha_bwd_kernel<DK><<<blocks, kJobThreads, 0, s>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dctx, stats, his_ids, (__nv_bfloat16*)dqkv, B, L, H, scale, use_mask)
   if (dk == 20) FR_GO(20); else if (dk == 32) FR_GO(32); else FR_GO(16);
 #undef FR_GO
   FR_LAUNCH_CHECK();

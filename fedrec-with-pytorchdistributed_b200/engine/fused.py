@@ -61,6 +61,29 @@ class PackedTrunk:
         self.ffn = b.config.hidden_dim
 
 
+def fused_unsupported_reason(model, cfg: FedRecConfig) -> Optional[str]:
+    """Why the sm_100a pipeline cannot run this model/config (None = it can). The kernels are built for the reference's
+    architecture family: DistilBERT width 768 with 64-wide heads, short titles and histories."""
+    bert = model.text_encoder.DistillBert.config
+    mha = model.user_encoder.multihead_attention
+    q = model.user_encoder.additive_attention.att_fc1.out_features
+    T = model.news_tokens.shape[1] if model.news_tokens is not None else cfg.title_len
+    checks = [
+        (bert.dim == 768 and bert.dim // bert.n_heads == 64, f"DistilBERT width {bert.dim} / head dim {bert.dim // bert.n_heads} (kernels: 768 / 64)"),
+        (bert.hidden_dim % 8 == 0, f"FFN width {bert.hidden_dim} is not a multiple of 8"),
+        (T <= 64, f"title length {T} > 64 tokens"),
+        (cfg.max_his_len <= 64, f"history length {cfg.max_his_len} > 64"),
+        (mha.d_k in (16, 20, 32) and mha.d_k == mha.d_v, f"user-encoder head dim {mha.d_k} (kernels: 16, 20, 32)"),
+        (mha.n_heads * mha.d_k <= 512 and (mha.n_heads * mha.d_k) % 8 == 0 and mha.d_model % 8 == 0, "user-encoder width"),
+        (q <= 256 and q % 8 == 0, f"additive-attention query dim {q}"),
+        (cfg.num_candidates <= 32, f"{cfg.num_candidates} candidates per impression > 32"),
+    ]
+    for ok, why in checks:
+        if not ok:
+            return why
+    return None
+
+
 class FusedStep:
     def __init__(self, model, cfg: FedRecConfig):
         ops.require_native()
@@ -71,6 +94,8 @@ class FusedStep:
         self._bufs: Dict[int, Dict[str, torch.Tensor]] = {}
         self._ubufs: Dict[tuple, Dict[str, torch.Tensor]] = {}
         self._step_no = 0
+        self._pk: Optional[Dict[str, torch.Tensor]] = None
+        self._side = torch.cuda.Stream(device=self.dev)       # branch for work off the critical path (also inside graphs)
         self._seed_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)   # RNG salt, bumped on the stream every step
         self._graphs: Dict[tuple, dict] = {}
         self._dedup_ws: Optional[torch.Tensor] = None
@@ -79,6 +104,47 @@ class FusedStep:
 
     def repack_trunk(self) -> None:
         self.trunk.repack()
+
+    # ---- bf16 / transposed copies of the *trainable* weights (they change every step) -------------------------
+    def _packed(self) -> Dict[str, torch.Tensor]:
+        if self._pk is None:
+            m = self.model
+            te, ue = m.text_encoder, m.user_encoder
+            mha, aa = ue.multihead_attention, ue.additive_attention
+            HD, Dm, Q = mha.n_heads * mha.d_k, mha.d_model, aa.att_fc1.out_features
+            hq, dim, nd = te.additive_attention.att_fc1.out_features, self.trunk.dim, self.cfg.news_dim
+            z = lambda *sh, dt=torch.bfloat16: torch.zeros(*sh, device=self.dev, dtype=dt)  # noqa: E731
+            self._pk = {"t_w1": z(hq, dim), "t_wfc": z(nd, dim), "t_wfcT": z(dim, nd),
+                        "u_wqkv": z(3 * HD, Dm), "u_bqkv": z(3 * HD, dt=torch.float32), "u_wqkvT": z(Dm, 3 * HD),
+                        "u_w1": z(Q, HD), "u_w1T": z(HD, Q)}
+        return self._pk
+
+    def _pack_weights(self, train: bool) -> None:
+        """Casts / transposes of the 16 trainable tensors. Independent of the frozen trunk, so the step runs this on a
+        side stream while the trunk computes."""
+        m, pk = self.model, self._packed()
+        te, ue = m.text_encoder, m.user_encoder
+        mha, aa = ue.multihead_attention, ue.additive_attention
+        HD = mha.n_heads * mha.d_k
+        D.cast_bf16(te.additive_attention.att_fc1.weight.data, out=pk["t_w1"])
+        D.cast_bf16(te.fc.weight.data, out=pk["t_wfc"])
+        for i, lin in enumerate((mha.W_Q, mha.W_K, mha.W_V)):
+            D.cast_bf16(lin.weight.data, out=pk["u_wqkv"][i * HD:(i + 1) * HD])
+            pk["u_bqkv"][i * HD:(i + 1) * HD].copy_(lin.bias.data)
+        D.cast_bf16(aa.att_fc1.weight.data, out=pk["u_w1"])
+        if train:
+            D.transpose_cast(te.fc.weight.data, out=pk["t_wfcT"])
+            D.transpose_cast(aa.att_fc1.weight.data, out=pk["u_w1T"])
+            for i, lin in enumerate((mha.W_Q, mha.W_K, mha.W_V)):
+                D.transpose_cast(lin.weight.data, out=pk["u_wqkvT"][:, i * HD:(i + 1) * HD])
+
+    def _fork(self):
+        """Start a side branch that sees everything queued on the current stream so far."""
+        self._side.wait_stream(torch.cuda.current_stream(self.dev))
+        return torch.cuda.stream(self._side)
+
+    def _join(self) -> None:
+        torch.cuda.current_stream(self.dev).wait_stream(self._side)
 
     # ---- buffers ---------------------------------------------------------------------------------
     def _buffers(self, K: int) -> Dict[str, torch.Tensor]:
@@ -95,16 +161,21 @@ class FusedStep:
              "news_vecs": z(K, self.cfg.news_dim, dt=torch.float32),
              # backward
              "d_news": z(K, self.cfg.news_dim, dt=torch.float32), "d_news_bf": z(K, self.cfg.news_dim),
-             "d_pooled": z(K, dim), "d_pre": z(R, hq), "wfcT": z(dim, self.cfg.news_dim),
-             "da": z(R, dt=torch.float32)}
+             "d_pooled": z(K, dim), "d_pre": z(R, hq), "da": z(R, dt=torch.float32)}
         self._bufs[K] = b
         return b
 
     # ---- trunk + head forward ------------------------------------------------------------------------
     @torch.no_grad()
-    def encode(self, uniq: torch.Tensor, count: Optional[torch.Tensor], K: int) -> Dict[str, torch.Tensor]:
-        """``uniq`` int32 [K] news rows (first ``*count`` valid) → buffers with ``hidden`` (=x) and ``news_vecs``."""
+    def encode(self, uniq: torch.Tensor, count: Optional[torch.Tensor], K: int, packed: bool = False) -> Dict[str, torch.Tensor]:
+        """``uniq`` int32 [K] news rows (first ``*count`` valid) → buffers with ``hidden`` (=x) and ``news_vecs``.
+
+        ``packed=True`` means the caller already refreshed the bf16 weight copies on the side stream (joined here,
+        after the trunk)."""
         m, tr, b = self.model, self.trunk, self._buffers(K)
+        if not packed:
+            with self._fork():
+                self._pack_weights(train=False)
         T = m.news_tokens.shape[1]
         x, y, ctx, qkv, ffn = b["x"], b["y"], b["ctx"], b["qkv"], b["ffn"]
         D.bert_embed_ln(m.news_tokens, uniq, count, K, T, tr.word, tr.pos, tr.emb_g, tr.emb_b, x)
@@ -118,13 +189,13 @@ class FusedStep:
             D.layernorm_bf16(y, L["ln2_g"], L["ln2_b"], out=x, count=count, rows_per_item=T)
         te = m.text_encoder
         aa = te.additive_attention
-        w1 = D.cast_bf16(aa.att_fc1.weight.data)
-        D.linear_bf16(x, w1, aa.att_fc1.bias.data, "tanh", out=b["e"], m_dev=count, m_scale=T)
+        pk = self._packed()
+        self._join()                                   # packed weights are ready
+        D.linear_bf16(x, pk["t_w1"], aa.att_fc1.bias.data, "tanh", out=b["e"], m_dev=count, m_scale=T)
         mask = m.news_mask if te.mask_padding else None
         D.text_pool(x, b["e"], aa.att_fc2.weight.data.view(-1), aa.att_fc2.bias.data, mask, uniq, count, K, T,
                     b["pooled"], b["alpha"])
-        wfc = D.cast_bf16(te.fc.weight.data)
-        D.linear_bf16(b["pooled"], wfc, te.fc.bias.data, "bias", out=b["news_vecs"], m_dev=count, m_scale=1)
+        D.linear_bf16(b["pooled"], pk["t_wfc"], te.fc.bias.data, "bias", out=b["news_vecs"], m_dev=count, m_scale=1)
         return b
 
     def _ids(self, cand, his):
@@ -154,9 +225,7 @@ class FusedStep:
         u = {"X": z(R, D), "qkv": z(R, 3 * H * dk), "ctx": z(R, H * dk), "stats": z(B * H * L, 2, dt=torch.float32),
              "E": z(R, Q), "score": z(B, C, dt=torch.float32), "loss": z((), dt=torch.float32),
              "user": z(B, H * dk, dt=torch.float32), "d_ctx_pool": z(R, H * dk), "d_pre": z(R, Q), "d_ctx": z(R, H * dk),
-             "dqkv": z(R, 3 * H * dk), "dX": z(R, D, dt=torch.float32),
-             "wqkv": z(3 * H * dk, D), "bqkv": z(3 * H * dk, dt=torch.float32), "wqkvT": z(D, 3 * H * dk),
-             "w1": z(Q, H * dk), "w1T": z(H * dk, Q)}
+             "dqkv": z(R, 3 * H * dk), "dX": z(R, D, dt=torch.float32)}
         self._ubufs[key] = u
         return u
 
@@ -171,15 +240,11 @@ class FusedStep:
         p = float(ue.dropout_rate) if train else 0.0
         use_mask = bool(cfg.mask_padding)
         his_flat = his.reshape(-1).to(torch.int32) if use_mask else None
-        HD = H * dk
-        for i, lin in enumerate((mha.W_Q, mha.W_K, mha.W_V)):
-            D.cast_bf16(lin.weight.data, out=u["wqkv"][i * HD:(i + 1) * HD])
-            u["bqkv"][i * HD:(i + 1) * HD].copy_(lin.bias.data)
-        D.cast_bf16(aa.att_fc1.weight.data, out=u["w1"])
+        pk = self._packed()
         D.ue_gather_dropout(nv, inv_his, u["X"], p, seed, self._seed_dev)
-        D.linear_bf16(u["X"], u["wqkv"], u["bqkv"], "bias", out=u["qkv"])
+        D.linear_bf16(u["X"], pk["u_wqkv"], pk["u_bqkv"], "bias", out=u["qkv"])
         D.ue_mha_fwd(u["qkv"], his_flat, u["ctx"], u["stats"], B, L, H, dk, use_mask)
-        D.linear_bf16(u["ctx"], u["w1"], aa.att_fc1.bias.data, "tanh", out=u["E"])
+        D.linear_bf16(u["ctx"], pk["u_w1"], aa.att_fc1.bias.data, "tanh", out=u["E"])
         fl = m.flat
         if train:
             D.ue_pool_score(u["ctx"], u["E"], aa.att_fc2.weight.data.view(-1), aa.att_fc2.bias.data, nv, inv_cand,
@@ -194,28 +259,27 @@ class FusedStep:
         return u, p, his_flat, use_mask
 
     def _user_backward(self, u, b, inv, his_flat, use_mask, B, L, C, p, seed):
+        """Critical path: data gradients down to d_news. Weight / bias gradients go to the side branch."""
         m, cfg = self.model, self.cfg
         ue = m.user_encoder
-        mha, aa = ue.multihead_attention, ue.additive_attention
+        mha = ue.multihead_attention
         H, dk = mha.n_heads, mha.d_k
         HD = H * dk
-        fl = m.flat
+        fl, pk = m.flat, self._packed()
         g = lambda name: fl.view(name, grad=True)  # noqa: E731
         inv_his = inv[: B * L]
-        # additive attention fc1: data gradient (+ pooling path as the residual), weight and bias gradients
-        D.transpose_cast(aa.att_fc1.weight.data, out=u["w1T"])
-        D.linear_bf16(u["d_pre"], u["w1T"], None, "resid", resid=u["d_ctx_pool"], out=u["d_ctx"])
-        D.gemm_grad(u["d_pre"], u["ctx"], g("user_encoder.additive_attention.att_fc1.weight"))
-        D.colsum(u["d_pre"], g("user_encoder.additive_attention.att_fc1.bias"))
-        # attention
+        with self._fork():                                   # needs d_pre, ctx
+            D.gemm_grad(u["d_pre"], u["ctx"], g("user_encoder.additive_attention.att_fc1.weight"))
+            D.colsum(u["d_pre"], g("user_encoder.additive_attention.att_fc1.bias"))
+        # additive attention fc1 data gradient (+ pooling path as the residual), then attention
+        D.linear_bf16(u["d_pre"], pk["u_w1T"], None, "resid", resid=u["d_ctx_pool"], out=u["d_ctx"])
         D.ue_mha_bwd(u["qkv"], u["d_ctx"], u["stats"], his_flat, u["dqkv"], B, L, H, dk, use_mask)
-        # Q/K/V projections
-        for i, nm in enumerate(("W_Q", "W_K", "W_V")):
-            sl = u["dqkv"][:, i * HD:(i + 1) * HD]
-            D.gemm_grad(sl, u["X"], g(f"user_encoder.multihead_attention.{nm}.weight"))
-            D.colsum(sl, g(f"user_encoder.multihead_attention.{nm}.bias"))
-            D.transpose_cast(getattr(mha, nm).weight.data, out=u["wqkvT"][:, i * HD:(i + 1) * HD])
-        D.linear_bf16(u["dqkv"], u["wqkvT"], None, "bias", out=u["dX"])
+        with self._fork():                                   # needs dqkv, X
+            for i, nm in enumerate(("W_Q", "W_K", "W_V")):
+                sl = u["dqkv"][:, i * HD:(i + 1) * HD]
+                D.gemm_grad(sl, u["X"], g(f"user_encoder.multihead_attention.{nm}.weight"))
+                D.colsum(sl, g(f"user_encoder.multihead_attention.{nm}.bias"))
+        D.linear_bf16(u["dqkv"], pk["u_wqkvT"], None, "bias", out=u["dX"])
         D.ue_scatter_dx(u["dX"], inv_his, b["d_news"], p, seed, cfg.news_grad_noise, seed + 2, self._seed_dev)
 
     def _text_head_backward(self, b, count, K):
@@ -224,18 +288,19 @@ class FusedStep:
         te = m.text_encoder
         aa = te.additive_attention
         T = m.news_tokens.shape[1]
-        fl = m.flat
+        fl, pk = m.flat, self._packed()
         g = lambda name: fl.view(name, grad=True)  # noqa: E731
         D.cast_bf16(b["d_news"], out=b["d_news_bf"])
-        D.transpose_cast(te.fc.weight.data, out=b["wfcT"])
-        D.linear_bf16(b["d_news_bf"], b["wfcT"], None, "bias", out=b["d_pooled"], m_dev=count, m_scale=1)
-        D.gemm_grad(b["d_news_bf"], b["pooled"], g("text_encoder.fc.weight"), k_dev=count, k_scale=1)
-        D.colsum(b["d_news"], g("text_encoder.fc.bias"), m_dev=count, m_scale=1)
+        with self._fork():                                   # needs d_news(_bf), pooled
+            D.gemm_grad(b["d_news_bf"], b["pooled"], g("text_encoder.fc.weight"), k_dev=count, k_scale=1)
+            D.colsum(b["d_news"], g("text_encoder.fc.bias"), m_dev=count, m_scale=1)
+        D.linear_bf16(b["d_news_bf"], pk["t_wfcT"], None, "bias", out=b["d_pooled"], m_dev=count, m_scale=1)
         D.text_pool_bwd(b["x"], b["e"], b["alpha"], b["d_pooled"], aa.att_fc2.weight.data.view(-1), count, K, T,
                         b["d_pre"], b["da"], g("text_encoder.additive_attention.att_fc2.weight").view(-1),
                         g("text_encoder.additive_attention.att_fc2.bias"),
                         g("text_encoder.additive_attention.att_fc1.bias"))
         D.gemm_grad(b["d_pre"], b["x"], g("text_encoder.additive_attention.att_fc1.weight"), k_dev=count, k_scale=T)
+        self._join()                                         # every gradient is in the flat buffer
 
     # ---- full step -----------------------------------------------------------------------------------------
     def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
@@ -282,10 +347,13 @@ class FusedStep:
         self._step_no += 1
         seed = self.cfg.seed * 1000003 + 3 * self._step_no
         D.counter_advance(self._seed_dev, 0x9E3779B97F4A7C15 & (2 ** 63 - 1))
+        with self._fork():                                   # trainable-weight copies: off the critical path
+            self._pack_weights(train)
         ids, uniq, count, inv, K = self._ids(cand, his)
-        b = self.encode(uniq, count, K)
         if train:
             m.flat.zero_grad()
+        b = self.encode(uniq, count, K, packed=True)
+        if train:
             b["d_news"].zero_()
         u, p, his_flat, use_mask = self._user_forward(b, inv, his, B, L, C, train, seed)
         if train:
@@ -298,7 +366,9 @@ class FusedStep:
     def scores(self, cand: torch.Tensor, his: torch.Tensor) -> torch.Tensor:
         B, C = cand.shape
         L = his.shape[1]
+        with self._fork():
+            self._pack_weights(False)
         ids, uniq, count, inv, K = self._ids(cand, his)
-        b = self.encode(uniq, count, K)
+        b = self.encode(uniq, count, K, packed=True)
         u, _, _, _ = self._user_forward(b, inv, his, B, L, C, False, 0)
         return u["score"].clone()

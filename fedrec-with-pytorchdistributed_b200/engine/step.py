@@ -30,6 +30,14 @@ class TrainStep:
         dev = model.device
         if impl is None:
             impl = "fused" if (dev.type == "cuda" and self.cfg.fused) else "torch"
+            if impl == "fused":
+                from .fused import fused_unsupported_reason
+                why = fused_unsupported_reason(model, self.cfg)
+                if why is not None:          # outside the shapes the kernels are built for: say so, use the oracle path
+                    import warnings
+                    warnings.warn(f"fedrec_b200: sm_100a step pipeline not available for this model ({why}); "
+                                  f"running the PyTorch path", RuntimeWarning)
+                    impl = "torch"
         self.impl = impl
         self._fused = None
         if impl == "fused":

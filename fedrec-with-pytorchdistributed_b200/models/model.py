@@ -118,8 +118,9 @@ class UserModel(nn.Module):
     def _fused_engine(self):
         """The sm_100a pipeline, created on first use for CUDA models (engine/fused.py)."""
         if self._fused is None and self.device.type == "cuda" and self.cfg.fused:
-            from ..engine.fused import FusedStep
-            self._fused = FusedStep(self, self.cfg)
+            from ..engine.fused import FusedStep, fused_unsupported_reason
+            if fused_unsupported_reason(self, self.cfg) is None:
+                self._fused = FusedStep(self, self.cfg)
         return self._fused
 
     def encode_unique(self, uniq: torch.Tensor, keep_cache: bool = True, with_grad: bool = False) -> torch.Tensor:
