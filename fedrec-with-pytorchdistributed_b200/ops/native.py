@@ -111,6 +111,14 @@ def lib() -> ctypes.CDLL:
     global _lib, _load_error
     if _lib is not None:
         return _lib
+    if not os.path.exists(_LIB) or (os.environ.get("FEDREC_AUTOBUILD", "1") != "0" and _stale()):
+        # a fresh checkout has sources only (the .so is a build artefact): build it now, ~20 s with nvcc on PATH
+        try:
+            build()
+        except Exception as e:  # noqa: BLE001
+            if not os.path.exists(_LIB):
+                _load_error = f"{_LIB} is not built and building it failed: {e}"
+                raise RuntimeError(_load_error) from e
     with _lock:
         if _lib is None:
             if not os.path.exists(_LIB):
