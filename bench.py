@@ -147,7 +147,7 @@ def run_ours(args):
     from fedrec_b200.config import FedRecConfig
     from fedrec_b200.engine.federated import FederatedRunner
     from fedrec_b200.ops import dispatch as D
-    cfg = FedRecConfig(mode="grad_avg", batch_size=B_USERS, max_his_len=HIS_LEN, npratio=NPRATIO, title_len=TITLE_LEN,
+    cfg = FedRecConfig(mode=args.mode, local_steps=args.local_steps, average_frozen=args.average_frozen, batch_size=B_USERS, max_his_len=HIS_LEN, npratio=NPRATIO, title_len=TITLE_LEN,
                        num_news=NUM_NEWS, clip_norm=CLIP, noise_multiplier=SIGMA, synthetic=True, snapshot_path="",
                        log_dir="", transport=args.transport, num_train=8, num_valid=1, seed=1234)
     news_index = synthetic_news_index(np)
@@ -159,10 +159,21 @@ def run_ours(args):
     his_pin = torch.from_numpy(his_h).to(torch.int32).pin_memory()
     cand_d, his_d = cand_pin.to(dev), his_pin.to(dev)
 
+    weights = runner.fedavg_weights()
+    state = {"n": 0}
+
     def one_step(c, h):
         loss = runner.step.run(c, h, train=True)
-        runner.grad_agg.allreduce_mean_()
-        runner.model.adam_step()
+        if args.mode == "grad_avg":                     # BASELINE.json config 2/4: average gradients, then Adam
+            runner.grad_agg.allreduce_mean_()
+            runner.model.adam_step()
+        else:                                           # config 3: local Adam steps, FedAvg every `local_steps`
+            runner.model.adam_step()
+            state["n"] += 1
+            if state["n"] % args.local_steps == 0:
+                runner.param_agg.average_(runner.model.flat.param, weights)
+                if args.average_frozen:
+                    runner._average_frozen(weights)
         return loss
 
     def barrier():
@@ -200,7 +211,10 @@ def run_ours(args):
     e2e_ms = t0.elapsed_time(t1) / args.steps
     h2d = cand_pin[0].numel() * 4 + his_pin[0].numel() * 4
     finish(args, "ours", rank, world, ms, e2e_ms, h2d, 4, launches, clocks,
-           {"transport": runner.grad_agg.transport, "step_impl": runner.step.impl, "last_loss": host_loss})
+           {"transport": runner.grad_agg.transport, "step_impl": runner.step.impl, "last_loss": host_loss,
+            **({} if args.mode == "grad_avg" else
+               {"mode": f"Parameter_Averaging_main: FedAvg every {args.local_steps} local steps"
+                        f"{' incl. the frozen trunk (270 MB)' if args.average_frozen else ' (trainable state)'}"})})
     runner.close()
 
 
@@ -274,9 +288,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--transport", default="nvlink", choices=["nvlink", "collective"])
+    ap.add_argument("--mode", default="grad_avg", choices=["grad_avg", "param_avg"],
+                    help="grad_avg = BASELINE.json configs 2/4 (default, the headline); param_avg = config 3")
+    ap.add_argument("--local_steps", type=int, default=5)
+    ap.add_argument("--average_frozen", action="store_true")
     args = ap.parse_args()
     if args.steps is None:
-        args.steps = 20 if args.impl == "ours" else 5
+        args.steps = 100 if args.impl == "ours" else 5
     args.warmup = max(args.warmup, 3)
     if args.gpus > 1 and "RANK" not in os.environ:
         # convenience: re-launch under torch.distributed.run

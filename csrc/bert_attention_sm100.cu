@@ -73,6 +73,7 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   const int num_tiles = (n_eff + TP - 1) / TP;
   const int hd_all = heads * kAttHd;
 
+  griddep_launch();                            // the out-projection GEMM may start its prologue
   if (tid == 0) {
     prefetch_tmap(&tmap_qkv);
     mbar_init(bar_qk, 1);

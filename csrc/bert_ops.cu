@@ -122,6 +122,7 @@ __global__ void __launch_bounds__(512) layernorm_kernel(const __nv_bfloat16* __r
                                                         int rows_max, const int* __restrict__ count_dev, int rows_per_item,
                                                         float eps) {
   const int lane = threadIdx.x & 31;
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // a following GEMM may start its prologue
   int rows = rows_max;
   if (count_dev) rows = min(rows_max, *count_dev * rows_per_item);
   const int nwarps = gridDim.x * (blockDim.x >> 5);

@@ -154,6 +154,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_base_slot;
+  // Programmatic dependent launch: everything above (barriers, TMEM, descriptor prefetch) may overlap the tail of the
+  // previous kernel in the stream; from here on we read its output. Our own dependents may begin their prologue now.
+  griddep_launch();
+  griddep_wait();
 
   if (warp == 0) {
     // ------------------------------- TMA producer -------------------------------
@@ -454,13 +458,20 @@ static int launch(const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = C::kSmemBytes;
   cfg.stream = s;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = CG;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
+  int na = CG == 2 ? 1 : 0;
+  static const bool use_pdl = [] { const char* e = getenv("FEDREC_PDL"); return !(e && atoi(e) == 0); }();
+  if (use_pdl) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = CG == 2 ? 1 : 0;
+  cfg.numAttrs = na;
   FR_CHECK(cudaLaunchKernelEx(&cfg, kern, m.a, m.b, m.o, m.r, p));
   return 0;
 }

@@ -20,6 +20,13 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---- programmatic dependent launch ----------------------------------------------------------------------
+// griddep_wait: block until every grid this launch depends on has finished and its writes are visible (no-op when the
+// kernel was launched without the programmatic attribute). griddep_launch: let a dependent that was launched with the
+// attribute start its prologue now (it still has to griddep_wait before touching our results).
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- mbarrier ----------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
