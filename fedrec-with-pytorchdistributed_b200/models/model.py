@@ -175,6 +175,36 @@ class UserModel(nn.Module):
             raise ValueError("news_vecs contains nan")
         return vec[inv].view(*ids.shape, -1)
 
+    # ---- precomputed-vector inference (the path upstream's UserDataset / evaluation_split anticipate) ---------------
+    @torch.no_grad()
+    def encode_all_news(self, batch: int = 2048) -> torch.Tensor:
+        """News vectors of the whole table ``[N, D]`` (fp32, on the model device), ``batch`` rows per pass."""
+        N = self.news_tokens.shape[0]
+        out = torch.empty(N, self.cfg.news_dim, device=self.device)
+        for i in range(0, N, batch):
+            ids = torch.arange(i, min(N, i + batch), device=self.device)
+            out[i:i + ids.numel()] = self.encode_unique(ids, keep_cache=False)
+        return out
+
+    @torch.no_grad()
+    def encode_users(self, samples, nid2index, news_vecs: torch.Tensor, batch: int = 1024) -> torch.Tensor:
+        """User vectors ``[S, D]`` from precomputed ``news_vecs`` for sample tuples ``(_, _, _, history, _)``."""
+        L = self.cfg.max_his_len
+        his = torch.zeros(len(samples), L, dtype=torch.long)
+        for s, sam in enumerate(samples):
+            h = [nid2index[n] for n in sam[3]][-L:]
+            his[s, : len(h)] = torch.tensor(h, dtype=torch.long)
+        his = his.to(self.device)
+        was = self.user_encoder.training
+        self.user_encoder.eval()
+        outs = []
+        for i in range(0, len(samples), batch):
+            hb = his[i:i + batch]
+            mask = (hb != 0) if self.cfg.mask_padding else None
+            outs.append(self.user_encoder(news_vecs[hb], mask))
+        self.user_encoder.train(was)
+        return torch.cat(outs) if outs else torch.empty(0, self.cfg.news_dim, device=self.device)
+
     # ---- forward / backward plumbing (reference-style API) -----------------------------
     def forward(self, candidate_news: IdLike, his_news: IdLike, labels: Optional[IdLike] = None,
                 compute_loss: bool = True):
