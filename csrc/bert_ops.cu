@@ -403,6 +403,41 @@ __global__ void __launch_bounds__(kDpreRowLanes * 64) text_dpre_kernel(const __n
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Trunk-output cache (opt-in). DistilBERT is frozen, so the hidden states of a news item never change: with 180 GB of
+// HBM the [N, T, 768] bf16 table of a whole news corpus (3 GB for 65k items) simply stays resident and the trunk only
+// runs for items seen for the first time. No counterpart upstream (it re-encodes every id every batch, model.py:41-61).
+//   cache_select: ids among uniq[0..count) whose `valid` flag is 0 → miss[0..*miss_count)   (order unspecified)
+//   rows_copy:    dst[(di)*R + r, :] = src[(si)*R + r, :] for i < count, si/di = optional index arrays (gather / scatter),
+//                 optionally raising valid[dst_idx[i]]
+// ---------------------------------------------------------------------------------------------
+__global__ void cache_select_kernel(const int* __restrict__ uniq, const int* __restrict__ count_dev, int n_items,
+                                    const int* __restrict__ valid, int* __restrict__ miss, int* __restrict__ miss_count) {
+  const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
+  const int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k < n_eff) {
+    const int id = uniq[k];
+    if (valid[id] == 0) miss[atomicAdd(miss_count, 1)] = id;
+  }
+}
+
+__global__ void __launch_bounds__(256) rows_copy_kernel(const uint4* __restrict__ src, const int* __restrict__ src_idx,
+                                                        uint4* __restrict__ dst, const int* __restrict__ dst_idx,
+                                                        const int* __restrict__ count_dev, int n_items, int rows_per_item,
+                                                        int vec_per_row, int* __restrict__ valid) {
+  const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
+  const size_t per_item = (size_t)rows_per_item * vec_per_row;
+  const size_t total = (size_t)n_eff * per_item;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int it = (int)(i / per_item);
+    const size_t off = i - (size_t)it * per_item;
+    const size_t s = (size_t)(src_idx ? src_idx[it] : it) * per_item + off;
+    const int di = dst_idx ? dst_idx[it] : it;
+    dst[(size_t)di * per_item + off] = src[s];
+    if (valid && off == 0) valid[di] = 1;
+  }
+}
+
 // fp32 → bf16 cast of a contiguous buffer (weight packing, activations entering a GEMM)
 __global__ void __launch_bounds__(256) cast_bf16_kernel(const float4* __restrict__ in, uint2* __restrict__ out, size_t n4) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
@@ -485,6 +520,30 @@ FR_API int fr_text_pool_bwd(const void* hidden, const void* e, const float* alph
   const int rows_per_block = 64;
   text_dpre_kernel<<<(rows + rows_per_block - 1) / rows_per_block, kDpreRowLanes * 64, 0, s>>>(
       (const __nv_bfloat16*)e, da_scratch, w2, count_dev, rows, T, Hq, rows_per_block, (__nv_bfloat16*)d_pre, d_w2, d_b1);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+FR_API int fr_cache_select(const int* uniq, const int* count_dev, int n_items, const int* valid, int* miss, int* miss_count,
+                           void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  FR_CHECK(cudaMemsetAsync(miss_count, 0, sizeof(int), s));
+  if (n_items == 0) return 0;
+  cache_select_kernel<<<(n_items + 255) / 256, 256, 0, s>>>(uniq, count_dev, n_items, valid, miss, miss_count);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+// Row-block copy with optional gather (src_idx) / scatter (dst_idx) by item; row_bytes must be a multiple of 16.
+FR_API int fr_rows_copy(const void* src, const int* src_idx, void* dst, const int* dst_idx, const int* count_dev,
+                        int n_items, int rows_per_item, int row_bytes, int* valid, void* stream) {
+  FR_REQUIRE(row_bytes % 16 == 0, "fr_rows_copy: row_bytes=%d must be a multiple of 16", row_bytes);
+  if (n_items == 0) return 0;
+  const size_t total = (size_t)n_items * rows_per_item * (row_bytes / 16);
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
+  rows_copy_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const uint4*)src, src_idx, (uint4*)dst, dst_idx, count_dev,
+                                                            n_items, rows_per_item, row_bytes / 16, valid);
   FR_LAUNCH_CHECK();
   return 0;
 }

@@ -74,6 +74,7 @@ class FedRecConfig:
     mask_padding: bool = False     # the reference never masks
     trunk_dropout_in_update: bool = False  # model.py:73 runs DistilBERT in train() for the 2nd pass
     cuda_graph: bool = True
+    trunk_cache: bool = False      # keep the frozen trunk's hidden states of every news item seen resident in HBM
     seed: int = 1234
     snapshot_path: str = "snapshot.pt"
     log_dir: str = "logs"

@@ -95,6 +95,7 @@ class FusedStep:
         self._ubufs: Dict[tuple, Dict[str, torch.Tensor]] = {}
         self._step_no = 0
         self._pk: Optional[Dict[str, torch.Tensor]] = None
+        self._cache: Optional[Dict[str, torch.Tensor]] = None
         self._side = torch.cuda.Stream(device=self.dev)       # branch for work off the critical path (also inside graphs)
         self._seed_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)   # RNG salt, bumped on the stream every step
         self._graphs: Dict[tuple, dict] = {}
@@ -104,6 +105,16 @@ class FusedStep:
 
     def repack_trunk(self) -> None:
         self.trunk.repack()
+        if self._cache is not None:
+            self._cache["valid"].zero_()          # new trunk weights: every cached hidden state is stale
+
+    def _trunk_cache(self) -> Dict[str, torch.Tensor]:
+        """[N*T, 768] bf16 table of trunk outputs + per-item valid flags (opt-in, ``cfg.trunk_cache``)."""
+        if self._cache is None:
+            N, T = self.model.news_tokens.shape
+            self._cache = {"hidden": torch.empty(N * T, self.trunk.dim, device=self.dev, dtype=torch.bfloat16),
+                           "valid": torch.zeros(N, device=self.dev, dtype=torch.int32)}
+        return self._cache
 
     # ---- bf16 / transposed copies of the *trainable* weights (they change every step) -------------------------
     def _packed(self) -> Dict[str, torch.Tensor]:
@@ -161,7 +172,10 @@ class FusedStep:
              "news_vecs": z(K, self.cfg.news_dim, dt=torch.float32),
              # backward
              "d_news": z(K, self.cfg.news_dim, dt=torch.float32), "d_news_bf": z(K, self.cfg.news_dim),
-             "d_pooled": z(K, dim), "d_pre": z(R, hq), "da": z(R, dt=torch.float32)}
+             "d_pooled": z(K, dim), "d_pre": z(R, hq), "da": z(R, dt=torch.float32),
+             # trunk cache bookkeeping
+             "miss": z(K, dt=torch.int32), "miss_count": z(1, dt=torch.int32),
+             "full_count": torch.full((1,), K, device=dev, dtype=torch.int32)}
         self._bufs[K] = b
         return b
 
@@ -178,6 +192,14 @@ class FusedStep:
                 self._pack_weights(train=False)
         T = m.news_tokens.shape[1]
         x, y, ctx, qkv, ffn = b["x"], b["y"], b["ctx"], b["qkv"], b["ffn"]
+        want_uniq, want_count = uniq, count
+        cache = self._trunk_cache() if self.cfg.trunk_cache else None
+        if cache is not None:
+            # only news items never seen before go through the trunk; everything else is gathered from HBM below
+            if count is None:
+                count = b["full_count"]
+            D.cache_select(uniq, count, K, cache["valid"], b["miss"], b["miss_count"])
+            uniq, count = b["miss"], b["miss_count"]
         D.bert_embed_ln(m.news_tokens, uniq, count, K, T, tr.word, tr.pos, tr.emb_g, tr.emb_b, x)
         for L in tr.layers:
             D.linear_bf16(x, L["wqkv"], L["bqkv"], "bias", out=qkv, m_dev=count, m_scale=T)
@@ -187,6 +209,10 @@ class FusedStep:
             D.linear_bf16(x, L["w1"], L["b1"], "gelu", out=ffn, m_dev=count, m_scale=T)
             D.linear_bf16(ffn, L["w2"], L["b2"], "resid", resid=x, out=y, m_dev=count, m_scale=T)
             D.layernorm_bf16(y, L["ln2_g"], L["ln2_b"], out=x, count=count, rows_per_item=T)
+        if cache is not None:
+            D.rows_copy(x, None, cache["hidden"], uniq, count, K, T, valid=cache["valid"])      # new items → cache
+            uniq, count = want_uniq, (want_count if want_count is not None else b["full_count"])
+            D.rows_copy(cache["hidden"], uniq, x, None, count, K, T)                            # this step's items ← cache
         te = m.text_encoder
         aa = te.additive_attention
         pk = self._packed()

@@ -29,6 +29,8 @@ SIGNATURES = {
     "fr_bert_attention_tc": (I, [P, P, P, P, I, I, I, I, P, P]),
     "fr_text_pool": (I, [P, P, P, P, P, P, P, I, I, I, I, P, P, P]),
     "fr_cast_f32_to_bf16": (I, [P, P, LL, P]),
+    "fr_cache_select": (I, [P, P, I, P, P, P, P]),
+    "fr_rows_copy": (I, [P, P, P, P, P, I, I, I, P, P]),
     "fr_text_pool_bwd": (I, [P, P, P, P, P, P, I, I, I, I, P, P, P, P, P, P]),
     # user_encoder.cu
     "fr_ue_gather_dropout": (I, [P, P, P, I, I, F, c_ulonglong, P, P]),

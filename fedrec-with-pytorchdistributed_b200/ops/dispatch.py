@@ -322,3 +322,19 @@ def text_pool_bwd(hidden, e, alpha, d_pooled, w2, count, n_items, T, d_pre, da_s
                                stream_ptr(hidden.device)), "fr_text_pool_bwd")
     count_launches(2)
     return d_pre
+
+
+def cache_select(uniq, count, n_items, valid, miss, miss_count):
+    lib = require_native()
+    check(lib.fr_cache_select(uniq.data_ptr(), _p(count), n_items, valid.data_ptr(), miss.data_ptr(), miss_count.data_ptr(),
+                              stream_ptr(uniq.device)), "fr_cache_select")
+    count_launches(1)
+
+
+def rows_copy(src, src_idx, dst, dst_idx, count, n_items, rows_per_item, valid=None):
+    """Item-block row copy with optional gather (``src_idx``) / scatter (``dst_idx``); 2-D tensors of equal row width."""
+    lib = require_native()
+    assert src.shape[1] == dst.shape[1] and src.dtype == dst.dtype and src.stride(1) == 1 and dst.stride(1) == 1
+    check(lib.fr_rows_copy(src.data_ptr(), _p(src_idx), dst.data_ptr(), _p(dst_idx), _p(count), n_items, rows_per_item,
+                           src.shape[1] * src.element_size(), _p(valid), stream_ptr(src.device)), "fr_rows_copy")
+    count_launches(1)

@@ -89,6 +89,15 @@ int fr_text_pool(const void* hidden, const void* e, const float* w2, const float
 
 int fr_cast_f32_to_bf16(const float* in, void* out, long long n, void* stream);
 
+/* Trunk-output cache helpers (opt-in feature; the frozen trunk's hidden states of a news item never change, so they can
+ * stay resident in HBM). fr_cache_select: miss[0..*miss_count) = ids in uniq[0..count) with valid[id] == 0.
+ * fr_rows_copy: dst[dst_idx?[i]] = src[src_idx?[i]] for item blocks of rows_per_item rows, i < count; raises valid[] of
+ * the destination item when given. No counterpart upstream (model.py:41-61 re-encodes every id every batch). */
+int fr_cache_select(const int* uniq, const int* count_dev, int n_items, const int* valid, int* miss, int* miss_count,
+                    void* stream);
+int fr_rows_copy(const void* src, const int* src_idx, void* dst, const int* dst_idx, const int* count_dev, int n_items,
+                 int rows_per_item, int row_bytes, int* valid, void* stream);
+
 /* Backward of fr_text_pool given d_pooled (bf16 [n,768]): writes d_pre = d(tanh input) bf16 [n*T,Hq] (tail rows
  * zeroed to a 64-row boundary), accumulates d_w2 [Hq], d_b2 [1] and the fc1 bias gradient d_b1 [Hq]. da_scratch:
  * n*T floats of scratch (per-token d(logit)). The trunk is frozen, so no d_hidden.

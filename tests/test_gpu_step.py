@@ -12,10 +12,10 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _models():
+def _models(**kw):
     ops.require_native()
     data = make_synthetic_mind(num_news=600, num_train=8, num_valid=2, title_len=30, seed=5)
-    cfg = FedRecConfig(title_len=30, dropout=0.0, batch_size=6)
+    cfg = FedRecConfig(title_len=30, dropout=0.0, batch_size=6, **kw)
     torch.manual_seed(0)
     a = UserModel(None, data.news_index, DEV, config=cfg)
     torch.manual_seed(0)
@@ -24,8 +24,10 @@ def _models():
     return a, b
 
 
-def test_fused_step_matches_oracle():
-    a, b = _models()
+@pytest.mark.parametrize("kw", [{}, {"mask_padding": True}, {"dedup": False}, {"cuda_graph": False}],
+                         ids=["default", "mask_padding", "no_dedup", "no_graph"])
+def test_fused_step_matches_oracle(kw):
+    a, b = _models(**kw)
     g = torch.Generator(device=DEV).manual_seed(1)
     cand = torch.randint(1, 600, (6, 5), device=DEV, generator=g, dtype=torch.int32)
     his = torch.randint(0, 600, (6, 50), device=DEV, generator=g, dtype=torch.int32)
@@ -55,3 +57,27 @@ def test_few_steps_track_oracle_loss():
         la, lb = fused.run(cand, his), oracle.run(cand, his)
         a.adam_step(); b.adam_step()
         assert float(la) == pytest.approx(float(lb), abs=1e-2)
+
+
+def test_trunk_cache_is_exact_across_steps():
+    """With the opt-in trunk cache, hidden states of news seen before are gathered from HBM instead of recomputed:
+    losses and gradients must be bit-for-bit those of the uncached run (the trunk is frozen, the kernels deterministic
+    up to the order of the atomics in the gradient accumulation)."""
+    a, b = _models(trunk_cache=True)
+    c, d = _models()
+    c.load_state_dict(a.state_dict())
+    cached, plain = TrainStep(a, impl="fused"), TrainStep(c, impl="fused")
+    g = torch.Generator(device=DEV).manual_seed(3)
+    for it in range(4):
+        cand = torch.randint(1, 80, (6, 5), device=DEV, generator=g, dtype=torch.int32)      # small id range: many hits
+        his = torch.randint(0, 80, (6, 50), device=DEV, generator=g, dtype=torch.int32)
+        la, lc = cached.run(cand, his), plain.run(cand, his)
+        assert float(la) == pytest.approx(float(lc), abs=1e-6), it
+        rel = float((a.flat.grad - c.flat.grad).norm() / c.flat.grad.norm())
+        assert rel < 1e-4, (it, rel)
+        a.adam_step(); c.adam_step()
+    valid = a._fused._cache["valid"]
+    assert 0 < int(valid.sum()) <= 80
+    # replacing the trunk weights invalidates the cache
+    a.on_weights_changed()
+    assert int(a._fused._cache["valid"].sum()) == 0
