@@ -65,7 +65,13 @@ class TrainStep:
         was = m.training
         m.eval()
         with torch.no_grad():
-            score, _, _ = m(cand, his, None, compute_loss=False)
+            ids = torch.cat([his.reshape(-1), cand.reshape(-1)]).long()
+            uniq, inv = torch.unique(ids, return_inverse=True)
+            vec = m.encode_unique(uniq, keep_cache=False, use_fused=False)
+            B, L = his.shape
+            his_mask = (his != 0) if self.cfg.mask_padding else None
+            user = m.user_encoder(vec[inv[: B * L]].view(B, L, -1), his_mask)
+            score = torch.sigmoid(torch.bmm(vec[inv[B * L:]].view(B, cand.shape[1], -1), user.unsqueeze(-1)).squeeze(-1))
         m.train(was)
         return score
 
@@ -87,7 +93,7 @@ class TrainStep:
                 hidden = m.text_encoder.trunk(m.news_tokens[uniq].long(), m.news_mask[uniq])
             vec = m.text_encoder.head(hidden, m.news_mask[uniq])
         else:
-            vec = m.encode_unique(uniq, keep_cache=False, with_grad=True)
+            vec = m.encode_unique(uniq, keep_cache=False, with_grad=True, use_fused=False)   # the oracle stays pure PyTorch
         his_vec = vec[inv[: B * L]].view(B, L, -1)
         cand_vec = vec[inv[B * L:]].view(B, C, -1)
         if train and cfg.news_grad_noise > 0:

@@ -123,13 +123,14 @@ class UserModel(nn.Module):
                 self._fused = FusedStep(self, self.cfg)
         return self._fused
 
-    def encode_unique(self, uniq: torch.Tensor, keep_cache: bool = True, with_grad: bool = False) -> torch.Tensor:
+    def encode_unique(self, uniq: torch.Tensor, keep_cache: bool = True, with_grad: bool = False,
+                      use_fused: Optional[bool] = None) -> torch.Tensor:
         """``uniq`` int64 ``[U]`` news rows → ``[U, D]`` news vectors (trunk under no_grad/eval).
 
         On CUDA the frozen trunk runs on the framework's own kernels (bf16 tcgen05 GEMMs, tensor-core attention); the
         trainable head runs there too unless ``with_grad`` asks for an autograd graph through it."""
         te = self.text_encoder
-        fused = self._fused_engine()
+        fused = self._fused_engine() if use_fused in (None, True) else None
         if fused is not None:
             U = uniq.numel()
             cap = (U + 255) // 256 * 256                 # bucketed capacity: a bounded set of activation buffers
