@@ -39,7 +39,7 @@ from ..utils.logging import MetricsLogger
 from ..utils.privacy import get_noise_multiplier
 from ..utils.trace import Tracer
 from .step import TrainStep
-from .trainer import Trainer
+from .trainer import validate_impressions
 
 
 class FederatedRunner:
@@ -145,9 +145,7 @@ class FederatedRunner:
     def validate(self):
         if self.is_server or not self.valid_sam:
             return None
-        t = Trainer.__new__(Trainer)
-        t.model, t.step = self.model, self.step
-        return Trainer.validate(t, self.valid_sam, self.nid2index)
+        return validate_impressions(self.step, self.model, self.valid_sam, self.nid2index)
 
     def save(self, epoch: int) -> None:
         ckpt.save_snapshot(self.cfg.snapshot_path, self.model, next_epoch=epoch + 1, rank=self.rank,

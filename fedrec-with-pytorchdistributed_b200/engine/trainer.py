@@ -70,6 +70,37 @@ def train_on_step(model, train_dl, optimizer=None, dp_enabled: bool = False, sig
     return total
 
 
+@torch.no_grad()
+def validate_impressions(step: TrainStep, model, valid_sam, nid2index, batch: int = 256):
+    """Mean loss / AUC / MRR / nDCG@5 / nDCG@10 over validation impressions, computed on the device.
+
+    Candidates per impression: the positive + the *last* ``npratio`` negatives (client.py:160). Upstream returns the last
+    sample's metrics only (client.py:171); means are reported here.
+    """
+    cfg = model.cfg
+    L, K = cfg.max_his_len, cfg.npratio
+    cands, hiss = [], []
+    for s in valid_sam:
+        _, pos, neg, his, _ = s
+        pos = pos[0] if isinstance(pos, (list, tuple)) else pos
+        negs = list(neg)[-K:]
+        negs = negs + ["<unk>"] * (K - len(negs))
+        cands.append([nid2index[pos]] + [nid2index[n] for n in negs])
+        h = [nid2index[n] for n in his][-L:]
+        hiss.append(h + [0] * (L - len(h)))
+    if not cands:
+        return 0.0, 0.0, 0.0, 0.0, 0.0
+    cand = torch.tensor(cands, device=model.device)
+    his = torch.tensor(hiss, device=model.device)
+    scores = torch.cat([step.scores(cand[i:i + batch], his[i:i + batch]) for i in range(0, len(cands), batch)])
+    labels = torch.zeros_like(scores)
+    labels[:, 0] = 1
+    loss = torch.nn.functional.cross_entropy(scores, torch.zeros(len(cands), dtype=torch.long, device=scores.device))
+    m = batched_ranking_metrics(scores, labels)
+    return (float(loss), float(m["auc"].mean()), float(m["mrr"].mean()), float(m["ndcg5"].mean()),
+            float(m["ndcg10"].mean()))
+
+
 class Trainer:
     def __init__(self, model, train_data, optimizer=None, save_every: int = 1, snapshot_path: str = "snapshot.pt",
                  isTrain: bool = True, aggregator=None, logger=None):
@@ -97,34 +128,9 @@ class Trainer:
         if ckpt.save_snapshot(self.snapshot_path, self.model, next_epoch=epoch + 1, rank=self.global_rank):
             print(f"Epoch {epoch} | Training snapshot saved at {self.snapshot_path}")
 
-    @torch.no_grad()
     def validate(self, valid_sam, nid2index, news_index=None, device=None, batch: int = 256):
-        """Mean loss / AUC / MRR / nDCG@5 / nDCG@10 over validation impressions.
-
-        Candidates per impression: the positive + the *last* ``npratio`` negatives (client.py:160).
-        """
-        cfg = self.model.cfg
-        L, K = cfg.max_his_len, cfg.npratio
-        cands, hiss = [], []
-        for s in valid_sam:
-            _, pos, neg, his, _ = s
-            pos = pos[0] if isinstance(pos, (list, tuple)) else pos
-            negs = list(neg)[-K:]
-            negs = negs + ["<unk>"] * (K - len(negs))
-            cands.append([nid2index[pos]] + [nid2index[n] for n in negs])
-            h = [nid2index[n] for n in his][-L:]
-            hiss.append(h + [0] * (L - len(h)))
-        if not cands:
-            return 0.0, 0.0, 0.0, 0.0, 0.0
-        cand = torch.tensor(cands, device=self.model.device)
-        his = torch.tensor(hiss, device=self.model.device)
-        scores = torch.cat([self.step.scores(cand[i:i + batch], his[i:i + batch]) for i in range(0, len(cands), batch)])
-        labels = torch.zeros_like(scores)
-        labels[:, 0] = 1
-        loss = torch.nn.functional.cross_entropy(scores, torch.zeros(len(cands), dtype=torch.long, device=scores.device))
-        m = batched_ranking_metrics(scores, labels)
-        return (float(loss), float(m["auc"].mean()), float(m["mrr"].mean()), float(m["ndcg5"].mean()),
-                float(m["ndcg10"].mean()))
+        """Mean loss / AUC / MRR / nDCG@5 / nDCG@10 over validation impressions (see ``validate_impressions``)."""
+        return validate_impressions(self.step, self.model, valid_sam, nid2index, batch)
 
     def train(self, max_epochs: int, valid_sam=None, nid2index=None, news_index=None, device=None,
               dp_enabled: bool = False, sigma: Optional[float] = None):

@@ -47,9 +47,6 @@ def _worker(rank, world, port, mode, tmp, q):
         res["params_equal"] = bool(torch.equal(ps[0], ps[1]))
         res["loss"] = float(loss)
         r.close()
-    else:
-        res["loss"] = r.run() if False else None
-        # run() closes the group; gather state before that by running the mode body directly
     q.put((rank, res))
 
 
