@@ -96,6 +96,7 @@ class FederatedRunner:
             store = dist.distributed_c10d._get_default_store()
             self.heartbeat = Heartbeat(store, self.rank, self.W, period_s=cfg.heartbeat_s,
                                        stale_s=max(10 * cfg.heartbeat_s, 30.0), on_stale=self._on_stale).start()
+        self._tcp_server = None
         self.round = 0
         self.epochs_run = 0
         if cfg.snapshot_path and os.path.exists(cfg.snapshot_path):
@@ -230,7 +231,10 @@ class FederatedRunner:
                                 "val_ndcg@5": v[3], "val_ndcg@10": v[4]})
                 self.logger.log(rec, step=rnd)
             with self.tracer.span("aggregate"):
-                self.param_agg.average_(self.model.flat.param, weights)   # X9 + K23 in one kernel
+                if cfg.transport == "tcp" and self.W > 1:
+                    self._tcp_upload_and_average(src, weights)            # X9 + K23 the upstream way (other hosts)
+                else:
+                    self.param_agg.average_(self.model.flat.param, weights)   # X9 + K23 in one kernel
             rnd += 1
             self.round = rnd
             if self.heartbeat:
@@ -238,6 +242,25 @@ class FederatedRunner:
             if cfg.snapshot_path and rnd % cfg.save_every == 0 and self.rank == src:
                 ckpt.save_snapshot(cfg.snapshot_path, self.model, next_epoch=rnd, rank=0, extra={"ROUND": rnd})
         return float(loss)
+
+    def _tcp_upload_and_average(self, src: int, weights) -> None:
+        """Clients stream their state_dict to the server over TCP; the server averages the files and loads the result
+        (client.py:191-210, 286-290; server.py:25-55, 80-103). The next round's model sync distributes it."""
+        from ..utils import transport
+        cfg = self.cfg
+        out_dir = cfg.log_dir or "."
+        if self.rank == src:
+            if self._tcp_server is None:
+                self._tcp_server = transport.StateDictServer("0.0.0.0", cfg.server_port, out_dir=out_dir)
+            dist.barrier()                                              # the server is listening
+            paths = self._tcp_server.receive_round(self.W - 1, timeout_s=cfg.timeout_s)
+            ids = self._tcp_server.last_client_ids                    # slot (1-based) → uploading rank
+            w = [weights[ids.get(i + 1, 0)] for i in range(len(paths))]
+            self.model.load_state_dict(transport.average_state_dicts(paths, w if len(set(w)) > 1 else None))
+        else:
+            dist.barrier()
+            transport.send_state_dict(ckpt.model_state_fp32_cpu(self.model), cfg.server_host, cfg.server_port,
+                                      client_id=self.rank, timeout_s=cfg.timeout_s)
 
     def _end_of_epoch(self, epoch: int, loss: torch.Tensor, reduce_loss: bool, save: bool = True) -> None:
         cfg = self.cfg
@@ -272,6 +295,8 @@ class FederatedRunner:
         self.logger.close()
         if self.symm is not None:
             self.symm.close()
+        if self._tcp_server is not None:
+            self._tcp_server.close()
         shutdown_distributed(self.info)
 
 

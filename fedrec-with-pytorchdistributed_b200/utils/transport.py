@@ -48,11 +48,13 @@ class StateDictServer:
         self.sock.bind((host, port))
         self.sock.listen(64)
         self.port = self.sock.getsockname()[1]
+        self.last_client_ids = {}       # slot → client id announced in the upload header (for weighted means)
 
     def _handle(self, conn: socket.socket, slot: int, paths: List[Optional[str]]) -> None:
         with conn:
             hdr = _recv_exact(conn, 12)
-            _cid, n = struct.unpack("!IQ", hdr)
+            cid, n = struct.unpack("!IQ", hdr)
+            self.last_client_ids[slot] = cid
             path = os.path.join(self.out_dir, f"received_model_{slot}.pt")
             with open(path, "wb") as f:
                 left = n
@@ -66,6 +68,7 @@ class StateDictServer:
 
     def receive_round(self, expected: int, timeout_s: float = 600.0) -> List[str]:
         paths: List[Optional[str]] = [None] * expected
+        self.last_client_ids = {}
         threads = []
         self.sock.settimeout(timeout_s)
         for slot in range(1, expected + 1):

@@ -105,6 +105,43 @@ def test_gradient_averaging_two_ranks(tmp_path, mode):
     assert out[0]["differs"]                              # the clients really had different gradients
 
 
+def _run_tcp(rank, world, port, tcp_port, tmp, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    from fedrec_b200.models.distilbert import DistilBertConfigLite
+    bert = DistilBertConfigLite(n_layers=1, dim=32, hidden_dim=64, n_heads=2, hidden_size=32)
+    cfg = FedRecConfig(mode="client_server", synthetic=True, num_news=128, num_train=32, num_valid=4, title_len=8,
+                       batch_size=4, total_epochs=1, global_epochs=2, dropout=0.0, device="cpu", backend="gloo",
+                       snapshot_path="", log_dir=os.path.join(tmp, f"r{rank}"), server_rank=2, lr=1e-2,
+                       transport="tcp", server_host="127.0.0.1", server_port=tcp_port)
+    r = FederatedRunner(cfg, bert_config=bert)
+    init = r.model.flat.param.clone()
+    try:
+        r.run_client_server()
+        q.put((rank, {"moved": bool(not torch.equal(init, r.model.flat.param)), "is_server": r.is_server,
+                      "files": sorted(os.listdir(cfg.log_dir)) if r.is_server else []}))
+    finally:
+        r.close()
+
+
+def test_client_server_over_tcp_three_ranks(tmp_path):
+    """Upstream's transport: clients upload state_dicts over a socket, the server averages the files (rank 2 = server)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port, tcp_port = _free_port(), _free_port()
+    procs = [ctx.Process(target=_run_tcp, args=(r, 3, port, tcp_port, str(tmp_path), q)) for r in range(3)]
+    [p.start() for p in procs]
+    out = dict(q.get(timeout=300) for _ in range(3))
+    [p.join(60) for p in procs]
+    assert out[2]["is_server"] and not out[0]["is_server"]
+    assert out[2]["moved"]                                            # the server ended up with the clients' average
+    assert "received_model_1.pt" in out[2]["files"] and "received_model_2.pt" in out[2]["files"]
+
+
 @pytest.mark.parametrize("mode", ["param_avg", "client_server"])
 def test_parameter_modes_two_ranks(tmp_path, mode):
     ctx = mp.get_context("spawn")
