@@ -66,8 +66,17 @@ class FederatedRunner:
         if self.device.type == "cuda" and self.W > 1 and cfg.transport == "nvlink":
             from ..parallel.symm import SymmetricHeap
             heap_mb = 64 + (288 if cfg.average_frozen else 0)       # the full fp32 state_dict is 257.6 MiB
-            self.symm = SymmetricHeap.create(self.info, heap_bytes=heap_mb << 20)
-            allocator = self.symm.alloc_f32
+            ok = torch.zeros(1, device=self.device)
+            try:
+                self.symm = SymmetricHeap.create(self.info, heap_bytes=heap_mb << 20)
+                ok.fill_(1.0)
+            except Exception as e:  # noqa: BLE001  (no peer access / IPC not permitted in this container)
+                print(f"[fedrec r{self.rank}] peer-mapped heap unavailable ({e}); aggregation falls back to NCCL", flush=True)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)               # every rank must agree on the transport
+            if float(ok) < 1.0:
+                self.symm = None
+            else:
+                allocator = self.symm.alloc_f32
         # ---- model -------------------------------------------------------------------
         if self.is_server:
             self.model = ServerUserModel(self.device, config=cfg, bert_config=bert_config, flat_allocator=allocator)
