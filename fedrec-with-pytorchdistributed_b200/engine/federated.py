@@ -84,7 +84,11 @@ class FederatedRunner:
             self.model = UserModel(None, news_index, self.device, config=cfg, bert_config=bert_config,
                                    flat_allocator=allocator)
         if self.symm is not None:
-            self.symm.finalize()
+            try:
+                self.symm.finalize()
+            except RuntimeError as e:                           # raised on every rank together (see finalize)
+                print(f"[fedrec r{self.rank}] {e}; aggregation falls back to NCCL", flush=True)
+                self.symm = None
         self.step = None if self.is_server else TrainStep(self.model, cfg)
         transport = "nvlink" if self.symm is not None else "collective"
         participants = [r for r in range(self.W) if not (cfg.mode == "client_server" and self.W > 1 and r == cfg.server_rank)]

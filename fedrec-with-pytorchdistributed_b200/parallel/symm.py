@@ -93,16 +93,23 @@ class SymmetricHeap:
         check(self.lib.fr_symm_export(self.local_ptr, handle), "fr_symm_export")
         gathered: List[Optional[bytes]] = [None] * self.W
         dist.all_gather_object(gathered, handle.raw)
-        ptrs = []
+        ptrs, err = [], None
         with torch.cuda.device(self.device):
             for r, raw in enumerate(gathered):
                 if r == self.rank:
                     ptrs.append(self.local_ptr)
                     continue
                 q = ctypes.c_void_p()
-                check(self.lib.fr_symm_import(ctypes.create_string_buffer(raw, 64), ctypes.byref(q)), "fr_symm_import")
+                rc = self.lib.fr_symm_import(ctypes.create_string_buffer(raw, 64), ctypes.byref(q))
+                if rc != 0:
+                    err = f"mapping rank {r}'s heap failed: {self.lib.fr_last_error().decode()}"
+                    break
                 ptrs.append(q.value)
                 self._imported.append(q.value)
+        ok = torch.tensor([0.0 if err else 1.0], device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)           # all ranks map every peer, or nobody uses the heap
+        if float(ok) < 1.0:
+            raise RuntimeError(err or "a peer rank could not map this rank's heap (no peer access between the GPUs?)")
         self.peer_ptrs = ptrs
         torch.cuda.synchronize(self.device)
         dist.barrier()
