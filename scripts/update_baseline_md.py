@@ -1,0 +1,108 @@
+"""Rewrite section 3 of BASELINE.md from the evidence under profiles/ (run after copying fresh JSON there)."""
+import glob
+import json
+import os
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def last_json(path):
+    lines = [l for l in open(path).read().splitlines() if l.startswith("{")]
+    return json.loads(lines[-1])
+
+
+def main():
+    tables = subprocess.run([sys.executable, os.path.join(ROOT, "scripts", "make_tables.py")], capture_output=True, text=True).stdout
+    bench, sweep = tables.split("\n\n", 1)
+    P = os.path.join(ROOT, "profiles")
+    o = {n: last_json(os.path.join(P, f"r1_bench_ours_{n}.json")) for n in (1, 2, 4, 8)}
+    r1, r8 = last_json(os.path.join(P, "r1_bench_ref_1.json")), last_json(os.path.join(P, "r1_bench_ref_8.json"))
+    pa = last_json(os.path.join(P, "r1_bench_ours_8_paramavg.json"))
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"bf16_tflops": 1665.4}
+    gem = json.load(open(os.path.join(P, "gemm_bench.json")))
+    grows = []
+    names = {"bert_qkv": "QKV (bias)", "bert_out": "out-proj (bias + residual)", "bert_ffn1": "FFN1 (bias + GELU)",
+             "bert_ffn2": "FFN2 (bias + residual)", "text_fc1": "text-head fc1 (bias + tanh)", "square_8k": "8192³ (bias)"}
+    for g in gem:
+        if g["name"] in names:
+            best = max([g["ours_tflops"]] + [v for k, v in g.items() if k.startswith("cg")])
+            grows.append(f"| {names[g['name']]} {g['M']}×{g['N']}×{g['K']} | {g['ours_tflops']:.0f} | {best:.0f} | "
+                         f"{best / peaks['bf16_tflops']:.2f} | {g['cublas_tflops']:.0f} |")
+    w8 = {r["mb"]: r for r in json.load(open(os.path.join(P, "agg_sweep_w8.json")))}
+    n8 = {r["mb"]: r for r in json.load(open(os.path.join(P, "agg_sweep_w8_nvls.json")))}
+    eff = o[1]["ms_per_step"] / o[8]["ms_per_step"]
+    sec = f'''## 3. The baseline to beat, measured: reference code with NCCL + cuBLAS on the same 8×B200 box
+
+The reference arm is the **unmodified** upstream code (`baseline/_ref`, copied by `baseline/install_ref.sh`) driven through
+`Gradient_Averaging_main.Trainer` / `train_on_step` with DDP over NCCL by `bench.py --impl reference` (harness:
+`baseline/harness.py`; the only shims are the ones its environment needs: `pickle5` alias, from-config DistilBERT, labels
+created on the device). Both arms run the same config: one client per GPU, 50 users per client per round, history 50,
+4 negatives, title length 30, full DistilBERT-base + user encoder, 65,536-row synthetic news table with Zipf popularity,
+random-init weights. One step = forward + backward + aggregation + Adam. CUDA events, max over ranks, ≥3 warm-up steps.
+Our arm additionally clips (C=2) and adds LDP noise (σ=0.05) inside the aggregation; the reference has neither in this mode.
+
+### 3.1 Training throughput (BASELINE.json configs 2, 3 and 4)
+
+{bench}
+
+* Reference as written: {r1['value']:.0f} impressions/s on one GPU, {r8['value']:.0f} on eight (its step is ~0.41 s: 100 tiny DistilBERT
+  calls through numpy per batch plus a second DistilBERT pass with grad).
+* This framework: **{o[1]['value']:,.0f} impressions/s on one GPU ({o[1]['value'] / r1['value']:.0f}× the reference), {o[8]['value']:,.0f} on eight
+  ({o[8]['value'] / r8['value']:.0f}×)**; weak-scaling efficiency 1→8 GPUs {eff:.2f} ({o[1]['ms_per_step']:.2f} → {o[8]['ms_per_step']:.2f} ms/step).
+  End to end (pinned host ids in, loss read back every step) costs 2–4 % on top.
+* Config 3 (`--mode param_avg --average_frozen`: local Adam steps, FedAvg of the **whole 270 MB state_dict** every 5 steps with
+  one `fr_param_average` kernel): {pa['value']:,.0f} impressions/s on eight GPUs.
+* With NCCL as the aggregation transport instead of the fused kernels the same run is
+  {last_json(os.path.join(P, 'r1_bench_ours_8_nccl.json'))['value']:,.0f} impressions/s.
+* `sw_power_cap` is the only throttle reason seen (normal for dense tensor work on a 1 kW part; SM clock ≈1.8 GHz under
+  load); no thermal or hardware slowdown.
+* Not the headline, reported separately: with the opt-in trunk-output cache (`--trunk_cache`, hidden states of news seen before
+  stay in HBM; exact because DistilBERT is frozen) one GPU reaches 39.6 k impressions/s in steady state.
+
+### 3.2 Aggregation latency (BASELINE.json configs 2, 3 and 5)
+
+Kernels: `fr_grad_allreduce` (clip + Gaussian noise + mean fused with the NVLink reduction) and `fr_param_average` (weighted
+FedAvg + redistribution). Baselines on the same buffers: NCCL all-reduce followed by a scale kernel, and for the gradient path
+NCCL plus separate norm / clip / noise kernels (what a non-fused implementation has to run). 4.66 MB is the real flat gradient
+(16 trainable tensors), 270.1 MB the full fp32 state_dict. Median of 10, max over ranks, device-timed. `scripts/bench_aggregate.py`.
+Rows `w8_nvls` / `w2_nvls` use the VMM heap and the `multimem.ld_reduce` / `multimem.st` variant (default from 4 ranks on).
+
+{sweep}
+* Gradient path at the real size (4.66 MB), 8 GPUs: **{n8[4.66]['fused_grad_clip_noise_us']:.1f} µs** fused (clip + noise + mean) vs
+  {n8[4.66]['nccl_plus_clip_noise_kernels_us']:.1f} µs for NCCL + separate kernels and {n8[4.66]['nccl_allreduce_mean_us']:.1f} µs for a bare NCCL all-reduce of the same bytes.
+* Parameter path, 8 GPUs, full state_dict (270 MB): **{n8[270.1]['fused_param_avg_us']:.0f} µs ({n8[270.1]['fused_param_busbw_gbs']:.0f} GB/s bus bandwidth)** with the NVLS
+  variant vs {n8[270.1]['nccl_allreduce_mean_us']:.0f} µs ({n8[270.1]['nccl_busbw_gbs']:.0f} GB/s) for NCCL (which also uses NVLS) and {w8[270.1]['fused_param_avg_us']:.0f} µs for our peer-load
+  variant; at 1 GB {n8[1024]['fused_param_avg_us']:.0f} µs ({n8[1024]['fused_param_busbw_gbs']:.0f} GB/s) vs {n8[1024]['nccl_allreduce_mean_us']:.0f} µs ({n8[1024]['nccl_busbw_gbs']:.0f} GB/s).
+* Roofline (B200_PROFILING.md: 770 GB/s per direction per GPU measured peer copy, 725 GB/s NCCL all-reduce bus bandwidth at
+  1 GiB): the NVLS variant reaches {n8[1024]['fused_param_busbw_gbs']:.0f} GB/s bus bandwidth at 1 GB on 8 GPUs — above the peer-copy figure because the switch
+  reduces in flight, so each GPU sends its shard once instead of 7/8 of the buffer twice. The peer-load variant reaches
+  {w8[1024]['fused_param_busbw_gbs']:.0f} GB/s = {w8[1024]['fused_param_busbw_gbs'] / 770:.2f} of the measured link rate. At the 4.66 MB gradient size the kernel is latency-bound
+  (two cross-GPU flag round trips + three grid barriers ≈ 45–60 µs).
+
+### 3.3 GEMM and kernel rooflines
+
+`scripts/bench_gemm.py` (CUDA events, L2 flushed between iterations, M = 82,500 = every id distinct). "auto" is what
+`fr_gemm_bf16` picks; "best variant" the fastest of {{single CTA, CTA pair}} × {{direct, staged-TMA epilogue}}. Fractions are of the
+measured cuBLAS bf16 burst peak in `MEASURED_PEAKS.json` ({peaks['bf16_tflops']:.0f} TFLOP/s). The cuBLAS column is a plain `torch.matmul`
+without any epilogue. Evidence: `profiles/gemm_bench.json`, ncu summaries `profiles/ncu_*.md`, SASS `profiles/sass/`.
+
+| GEMM (epilogue) M×N×K | auto TFLOP/s | best variant TFLOP/s | of measured peak | plain cuBLAS TFLOP/s |
+|---|---|---|---|---|
+{chr(10).join(grows)}
+
+In-situ (inside the training step, warm caches, power-capped clocks, `scripts/step_profile.py`, `profiles/step_profile.txt`):
+the four trunk GEMMs run at 0.9–1.4 PFLOP/s and account for ≈62 % of the step; attention ≈9 %, LayerNorm ≈7 %.
+
+'''
+    p = os.path.join(ROOT, "BASELINE.md")
+    s = open(p).read()
+    a = s.index("## 3. The baseline to beat")
+    b = s.index("## 4. Device peaks for roofline fractions")
+    open(p, "w").write(s[:a] + sec + s[b:])
+    print("BASELINE.md section 3 rewritten")
+
+
+if __name__ == "__main__":
+    main()

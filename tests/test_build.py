@@ -32,3 +32,19 @@ def test_sass_has_tcgen05_and_tma():
     assert "UTMALDG" in sass            # TMA tensor load
     assert "LDTM" in sass               # tcgen05.ld
     assert "HGMMA" not in sass and "sm_100a" in sass
+
+
+def test_ctypes_signatures_match_header_arity():
+    """Every bound function has as many ctypes argument types as the header declares parameters."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hdr = open(os.path.join(root, "include", "fedrec_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    decls = dict()
+    for m in re.finditer(r"\b(\w+)\s*\(([^;{}]*?)\)\s*;", hdr):
+        name, args = m.group(1), m.group(2).strip()
+        n = 0 if args in ("", "void") else args.count(",") + 1
+        decls[name] = n
+    for name, (_res, argtypes) in SIGNATURES.items():
+        assert name in decls, name
+        assert decls[name] == len(argtypes), (name, decls[name], len(argtypes))
