@@ -106,3 +106,37 @@ def test_evaluate_script_runs(tmp_path):
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-1500:]
     assert "auc=" in r.stdout and "ndcg@10=" in r.stdout
+
+
+def test_upstream_toy_shard_loads_and_trains(tiny_bert):
+    """The four files upstream ships in UserData/ (T=50 titles, 76-click history) load and drive a step unchanged."""
+    import pytest
+    d = "/root/reference/UserData"
+    if not os.path.isdir(d):
+        pytest.skip("upstream toy shard not available")
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.data import BatchSampler, ImpressionTable, TrainDataset, load_user_data
+    from fedrec_b200.engine import TrainStep
+    from fedrec_b200.models import UserModel
+    nid2index, news_index, train_sam, valid_sam = load_user_data(d)
+    assert news_index.shape == (225, 2, 50) and len(train_sam) == 4 and len(valid_sam) == 1
+    ds = TrainDataset(train_sam, nid2index, news_index, seed=0)
+    cand, his, label = ds[0]
+    assert cand.shape == (5,) and his.shape == (50,) and label == 0      # 76-click history truncated to the last 50
+    assert list(his) == [nid2index[n] for n in train_sam[0][3]][-50:]
+    m = UserModel(None, news_index, "cpu", config=FedRecConfig(title_len=50, dropout=0.0), bert_config=tiny_bert)
+    c, h = BatchSampler(ImpressionTable(train_sam, nid2index), 4, seed=0, pin=False).next()
+    loss = TrainStep(m, impl="torch").run(c, h)
+    assert torch.isfinite(loss) and float(m.flat.grad.abs().sum()) > 0
+
+
+def test_shipped_userdata_directory_works_like_upstream(tmp_path):
+    """`main.py <epochs> <batch> <save_every>` with no other argument reads ./UserData, as upstream does."""
+    import shutil
+    shutil.copytree(os.path.join(ROOT, "UserData"), tmp_path / "UserData")
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "main.py"), "1", "4", "1", "--bert_layers", "1", "--bert_dim", "32",
+                        "--bert_ffn", "64", "--bert_heads", "2", "--device", "cpu", "--log_dir", ""], env=env, cwd=str(tmp_path),
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-1500:]
+    assert (tmp_path / "snapshot.pt").exists() and "training_loss" in r.stdout

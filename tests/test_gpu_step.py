@@ -87,3 +87,22 @@ def test_trunk_cache_is_exact_across_steps():
     # replacing the trunk weights invalidates the cache
     a.on_weights_changed()
     assert int(a._fused._cache["valid"].sum()) == 0
+
+
+def test_fused_step_with_upstream_toy_shapes():
+    """Title length 50 (the shipped toy shard) uses the 64-row attention slots; 3 users per batch."""
+    ops.require_native()
+    data = make_synthetic_mind(num_news=300, num_train=8, num_valid=2, title_len=50, seed=9)
+    cfg = FedRecConfig(title_len=50, dropout=0.0, batch_size=3)
+    torch.manual_seed(0)
+    a = UserModel(None, data.news_index, DEV, config=cfg)
+    torch.manual_seed(0)
+    b = UserModel(None, data.news_index, DEV, config=cfg)
+    b.load_state_dict(a.state_dict())
+    g = torch.Generator(device=DEV).manual_seed(4)
+    cand = torch.randint(1, 300, (3, 5), device=DEV, generator=g, dtype=torch.int32)
+    his = torch.randint(0, 300, (3, 50), device=DEV, generator=g, dtype=torch.int32)
+    la, lb = TrainStep(a, impl="fused").run(cand, his), TrainStep(b, impl="torch").run(cand, his)
+    assert float(la) == pytest.approx(float(lb), abs=5e-3)
+    rel = float((a.flat.grad - b.flat.grad).norm() / b.flat.grad.norm())
+    assert rel < 5e-2, rel
