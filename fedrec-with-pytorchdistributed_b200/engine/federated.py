@@ -52,6 +52,8 @@ class FederatedRunner:
         torch.manual_seed(cfg.seed)                       # identical initial weights on every rank
         # ---- data: each rank is one client with its own shard (README.md:22) ----------
         if news_index is None:
+            # every rank is a client with its own shard: "UserData_{rank}" picks a per-rank directory on a shared box
+            cfg.data_dir = cfg.data_dir.format(rank=self.rank, local_rank=self.info.local_rank)
             if cfg.synthetic or not os.path.isdir(cfg.data_dir):
                 d = make_synthetic_mind(cfg.num_news, cfg.num_train, cfg.num_valid, cfg.title_len,
                                         cfg.max_his_len, seed=cfg.seed, client=self.rank)

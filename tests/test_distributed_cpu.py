@@ -156,3 +156,51 @@ def test_parameter_modes_two_ranks(tmp_path, mode):
     else:
         assert out[0]["equal"] and out[1]["equal"] and out[1]["is_server"] and not out[0]["is_server"], out
         assert out[0]["moved"] and out[1]["moved"]        # the server received the clients' average
+
+
+def _run_faulty(rank, world, port, tmp, fault, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port), FEDREC_FAULT=fault)
+    torch.set_num_threads(2)
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    from fedrec_b200.models.distilbert import DistilBertConfigLite
+    bert = DistilBertConfigLite(n_layers=1, dim=32, hidden_dim=64, n_heads=2, hidden_size=32)
+    cfg = FedRecConfig(mode="grad_avg", synthetic=True, num_news=128, num_train=32, num_valid=4, title_len=8, batch_size=4,
+                       total_epochs=4, save_every=1, dropout=0.0, device="cpu", backend="gloo", timeout_s=20.0,
+                       snapshot_path=os.path.join(tmp, "snap.pt"), log_dir="")
+    try:
+        r = FederatedRunner(cfg, bert_config=bert)
+        start = r.epochs_run
+        r.run()
+        q.put((rank, {"ok": True, "start": start}))
+    except BaseException as e:  # noqa: BLE001
+        q.put((rank, {"ok": False, "err": type(e).__name__}))
+
+
+def test_client_failure_is_detected_and_training_resumes_from_snapshot(tmp_path):
+    """A client dies at round 2 (fault injection): the survivor gets an error instead of hanging, and a relaunch resumes
+    from the last snapshot instead of starting over (upstream: 'if a client fails the entire training will fail')."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_run_faulty, args=(r, 2, port, str(tmp_path), "kill:1:2", q)) for r in range(2)]
+    [p.start() for p in procs]
+    [p.join(120) for p in procs]
+    assert procs[1].exitcode == 17                                   # the injected fault
+    got = {}
+    while not q.empty():
+        r, res = q.get()
+        got[r] = res
+    assert 0 in got and not got[0]["ok"], got                         # rank 0 saw an error within the timeout, not a hang
+    snap = torch.load(os.path.join(str(tmp_path), "snap.pt"), weights_only=False)
+    assert snap["EPOCHS_RUN"] == 2                                    # rounds 0 and 1 were saved
+    q2 = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_run_faulty, args=(r, 2, port, str(tmp_path), "", q2)) for r in range(2)]
+    [p.start() for p in procs]
+    out = dict(q2.get(timeout=240) for _ in range(2))
+    [p.join(60) for p in procs]
+    assert out[0]["ok"] and out[1]["ok"] and out[0]["start"] == 2 and out[1]["start"] == 2
+    assert torch.load(os.path.join(str(tmp_path), "snap.pt"), weights_only=False)["EPOCHS_RUN"] == 4
