@@ -213,6 +213,7 @@ def run_ours(args):
     h2d = cand_pin[0].numel() * 4 + his_pin[0].numel() * 4
     finish(args, "ours", rank, world, ms, e2e_ms, h2d, 4, launches, clocks,
            {"transport": runner.grad_agg.transport, "step_impl": runner.step.impl, "last_loss": host_loss,
+            "peer_heap": (f"{runner.symm.backend}{'+nvls-multimem' if runner.symm.mc_ptr else ''}" if runner.symm else "none"),
             **({"trunk_cache": "ON — trunk outputs cached across steps; not comparable with the headline number"}
                if args.trunk_cache else {}),
             **({} if args.mode == "grad_avg" else
