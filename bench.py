@@ -166,8 +166,8 @@ def run_ours(args):
     def one_step(c, h):
         loss = runner.step.run(c, h, train=True)
         if args.mode == "grad_avg":                     # BASELINE.json config 2/4: average gradients, then Adam
-            runner.grad_agg.allreduce_mean_()
-            runner.model.adam_step()
+            c_ = runner.cfg
+            runner.grad_agg.allreduce_mean_and_adam_(c_.lr, c_.beta1, c_.beta2, c_.adam_eps)   # one kernel when W > 1
         else:                                           # config 3: local Adam steps, FedAvg every `local_steps`
             runner.model.adam_step()
             state["n"] += 1

@@ -48,6 +48,11 @@ struct AggParams {
   float clip, noise_std, scale;
   unsigned long long seed;
   int uniform_weights;        // param average: all participating weights equal → no in-place pre-scaling needed for NVLS
+  // optional fused Adam tail (gradient mode): parameters / moments of each logical rank handled by this launch
+  float* adam_p[kMaxRanks];
+  float* adam_m[kMaxRanks];
+  float* adam_v[kMaxRanks];
+  float lr, b1, b2, eps, bc1, bc2;
 };
 
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
@@ -228,11 +233,30 @@ __global__ void __launch_bounds__(512) aggregate_kernel(const AggParams p) {
   // ---- done: all my blocks finished writing → tell every peer; wait for everyone ---------------------------
   __threadfence_system();
   rank_grid_sync(my_pad + kPadEndCtr + (epoch & 1u), gridDim.x);
-  if (blockIdx.x == 0) {
-    if (threadIdx.x < W) {
-      st_release_sys(p.pads[threadIdx.x] + kPadDone + r, epoch);
-      spin_until_ge(my_pad + kPadDone + threadIdx.x, epoch);
+  if (blockIdx.x == 0 && threadIdx.x < W) st_release_sys(p.pads[threadIdx.x] + kPadDone + r, epoch);
+  if (kMode == 0 && p.adam_p[r] != nullptr) {
+    // ---- fused optimiser tail: once every peer has delivered its slice, my buffer holds the averaged gradient;
+    //      every block waits on the (local) done flags and applies Adam to its share of the flat parameter vector.
+    if (threadIdx.x < W) spin_until_ge(my_pad + kPadDone + threadIdx.x, epoch);
+    __syncthreads();
+    float4* pp = reinterpret_cast<float4*>(p.adam_p[r]);
+    float4* mm = reinterpret_cast<float4*>(p.adam_m[r]);
+    float4* vv = reinterpret_cast<float4*>(p.adam_v[r]);
+    const float step_size = p.lr / p.bc1, inv_sqrt_bc2 = rsqrtf(p.bc2);
+    for (size_t i = tid; i < n4; i += nth) {
+      const float4 g = reinterpret_cast<const float4*>(my_buf)[i];
+      float4 w = pp[i], m1 = mm[i], v2 = vv[i];
+#define FR_ADAM1(c)                                                        \
+      m1.c = p.b1 * m1.c + (1.f - p.b1) * g.c;                             \
+      v2.c = p.b2 * v2.c + (1.f - p.b2) * g.c * g.c;                       \
+      w.c -= step_size * (m1.c / (sqrtf(v2.c) * inv_sqrt_bc2 + p.eps));
+      FR_ADAM1(x) FR_ADAM1(y) FR_ADAM1(z) FR_ADAM1(w)
+#undef FR_ADAM1
+      pp[i] = w; mm[i] = m1; vv[i] = v2;
     }
+  }
+  if (blockIdx.x == 0) {
+    if (threadIdx.x < W) spin_until_ge(my_pad + kPadDone + threadIdx.x, epoch);
     __syncthreads();
     if (threadIdx.x == 0) {
       // every block of this rank is past the earlier barriers: make the pad ready for the next launch.
@@ -282,6 +306,30 @@ FR_API int fr_grad_allreduce(void* const* bufs_host, void* const* pads_host, voi
   for (int i = 0; i < W; ++i) { p.bufs[i] = (float*)bufs_host[i]; p.pads[i] = (uint32_t*)pads_host[i]; }
   p.mc_buf = (float*)mc_buf; p.W = W; p.rank_base = rank_base; p.ranks_here = ranks_here; p.n = n; p.epoch = epoch;
   p.clip = clip; p.noise_std = noise_std; p.scale = scale; p.seed = seed;
+  if (blocks <= 0) blocks = 128;
+  return launch_agg(0, mc_buf != nullptr, p, blocks, (cudaStream_t)stream);
+}
+
+// fr_grad_allreduce followed, inside the same kernel, by one Adam step of every rank on the averaged gradient
+// (params/m/v: per-rank fp32 buffers of n floats, local memory; only entries rank_base .. rank_base+ranks_here-1 are used).
+// bc1 = 1 - b1^t, bc2 = 1 - b2^t for the 1-based step count t. One launch replaces DDP all-reduce + clip/noise + Adam.
+FR_API int fr_grad_allreduce_adam(void* const* bufs_host, void* const* pads_host, void* mc_buf, int W, int rank_base,
+                                  int ranks_here, long long n, unsigned epoch, float clip, float noise_std, float scale,
+                                  unsigned long long seed, void* const* params_host, void* const* m_host,
+                                  void* const* v_host, float lr, float b1, float b2, float eps, float bc1, float bc2,
+                                  int blocks, void* stream) {
+  FR_REQUIRE(W >= 1 && W <= kMaxRanks, "fr_grad_allreduce_adam: W=%d must be in [1,%d]", W, kMaxRanks);
+  FR_REQUIRE(n % 4 == 0 && epoch > 0, "fr_grad_allreduce_adam: n=%lld must be a multiple of 4 and epoch > 0", n);
+  FR_REQUIRE(ranks_here >= 1 && rank_base >= 0 && rank_base + ranks_here <= W, "fr_grad_allreduce_adam: bad rank range");
+  AggParams p{};
+  for (int i = 0; i < W; ++i) { p.bufs[i] = (float*)bufs_host[i]; p.pads[i] = (uint32_t*)pads_host[i]; }
+  for (int i = rank_base; i < rank_base + ranks_here; ++i) {
+    p.adam_p[i] = (float*)params_host[i]; p.adam_m[i] = (float*)m_host[i]; p.adam_v[i] = (float*)v_host[i];
+    FR_REQUIRE(p.adam_p[i] && p.adam_m[i] && p.adam_v[i], "fr_grad_allreduce_adam: missing optimiser buffers of rank %d", i);
+  }
+  p.mc_buf = (float*)mc_buf; p.W = W; p.rank_base = rank_base; p.ranks_here = ranks_here; p.n = n; p.epoch = epoch;
+  p.clip = clip; p.noise_std = noise_std; p.scale = scale; p.seed = seed;
+  p.lr = lr; p.b1 = b1; p.b2 = b2; p.eps = eps; p.bc1 = bc1; p.bc2 = bc2;
   if (blocks <= 0) blocks = 128;
   return launch_agg(0, mc_buf != nullptr, p, blocks, (cudaStream_t)stream);
 }

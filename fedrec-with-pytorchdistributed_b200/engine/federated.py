@@ -174,10 +174,8 @@ class FederatedRunner:
         for epoch in range(self.epochs_run, cfg.total_epochs):
             self.faults.maybe_fire(self.rank, epoch)
             loss = self.local_step()
-            with self.tracer.span("aggregate"):
-                self.grad_agg.allreduce_mean_()
-            with self.tracer.span("adam"):
-                self.model.adam_step()
+            with self.tracer.span("aggregate+adam"):          # one kernel over NVLink: clip, noise, mean and the Adam step
+                self.grad_agg.allreduce_mean_and_adam_(cfg.lr, cfg.beta1, cfg.beta2, cfg.adam_eps)
             self.round += 1
             if self.heartbeat:
                 self.heartbeat.beat(self.round)

@@ -45,6 +45,7 @@ SIGNATURES = {
     "fr_gemm_grad_bf16": (I, [P, P, P, I, I, I, I, I, I, P, I, I, P]),
     # aggregate.cu
     "fr_grad_allreduce": (I, [P, P, P, I, I, I, LL, c_uint, F, F, F, c_ulonglong, I, P]),
+    "fr_grad_allreduce_adam": (I, [P, P, P, I, I, I, LL, c_uint, F, F, F, c_ulonglong, P, P, P, F, F, F, F, F, F, I, P]),
     "fr_param_average": (I, [P, P, P, P, I, I, I, LL, c_uint, I, P]),
     "fr_signal_pad_bytes": (I, []),
     "fr_symm_alloc": (I, [P, LL]),

@@ -48,6 +48,25 @@ class GradAggregator:
         # sigma is relative to the clip bound when clipping is on (DP-SGD convention)
         return self.sigma * (self.clip if self.clip > 0 else 1.0)
 
+    def allreduce_mean_and_adam_(self, lr: float, b1: float, b2: float, eps: float) -> torch.Tensor:
+        """Clip + noise + mean over participants + one Adam step on the flat parameters.
+
+        With the NVLink transport this is a single kernel (``fr_grad_allreduce_adam``); otherwise aggregation followed by
+        the separate fused Adam kernel. Either way ``flat.step`` advances by one."""
+        from .. import ops as _ops
+        fl = self.flat
+        if self.transport == "nvlink" and self.symm is not None and self.W > 1:
+            self.round += 1
+            fl.step += 1
+            self.symm.grad_allreduce_adam_(fl.grad, clip=self.clip, noise_std=self.noise_std,
+                                           seed=self.seed + 7919 * self.round, scale=1.0 / len(self.participants),
+                                           params=fl.param, exp_avg=fl.exp_avg, exp_avg_sq=fl.exp_avg_sq, step=fl.step,
+                                           lr=lr, b1=b1, b2=b2, eps=eps)
+            return fl.grad
+        self.allreduce_mean_()
+        _ops.adam_flat(fl, lr, b1, b2, eps)
+        return fl.grad
+
     def allreduce_mean_(self, buf: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Clip + noise this client's gradient, then replace it by the mean over participants."""
         g = self.flat.grad if buf is None else buf

@@ -180,6 +180,33 @@ class SymmetricHeap:
         count_launches(1)
         return g
 
+    def grad_allreduce_adam_(self, g: torch.Tensor, clip: float, noise_std: float, seed: int, scale: float,
+                             params, exp_avg, exp_avg_sq, step: int, lr: float, b1: float, b2: float, eps: float,
+                             ranks_here: int = 1, blocks: int = 0) -> torch.Tensor:
+        """``grad_allreduce_`` + one Adam step in the same kernel. ``params`` / ``exp_avg`` / ``exp_avg_sq`` are this
+        rank's flat fp32 buffers (or, with ``ranks_here > 1``, lists with one entry per emulated rank); ``step`` is the
+        1-based step count after this update."""
+        assert self.peer_ptrs, "call finalize() first"
+        bufs, pads = self._ptr_arrays(self.offset_of(g))
+        n = (g.numel() + 3) // 4 * 4
+
+        def arr(x):
+            xs = x if isinstance(x, (list, tuple)) else [x]
+            base = 0 if ranks_here > 1 else self.rank
+            slots = [None] * self.W
+            for i, t in enumerate(xs):
+                assert t.numel() >= n and t.dtype == torch.float32
+                slots[base + i] = t.data_ptr()
+            return (ctypes.c_void_p * self.W)(*slots)
+        check(self.lib.fr_grad_allreduce_adam(
+            bufs, pads, (self.mc_ptr + self.offset_of(g)) if self.mc_ptr else None, self.W,
+            self.rank if ranks_here == 1 else 0, ranks_here, n, self._next_epoch(), float(clip), float(noise_std),
+            float(scale), int(seed) & (2 ** 64 - 1), arr(params), arr(exp_avg), arr(exp_avg_sq), float(lr), float(b1),
+            float(b2), float(eps), 1.0 - b1 ** step, 1.0 - b2 ** step, blocks, stream_ptr(self.device)),
+            "fr_grad_allreduce_adam")
+        count_launches(1)
+        return g
+
     def param_average_(self, buf: torch.Tensor, weights: Sequence[float], ranks_here: int = 1, blocks: int = 0) -> torch.Tensor:
         assert self.peer_ptrs, "call finalize() first"
         bufs, pads = self._ptr_arrays(self.offset_of(buf))

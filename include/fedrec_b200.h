@@ -157,6 +157,13 @@ int fr_transpose_cast(const float* in, void* out, int R, int Ccols, int ld_out, 
 int fr_grad_allreduce(void* const* bufs_host, void* const* pads_host, void* mc_buf, int W, int rank_base,
                       int ranks_here, long long n, unsigned epoch, float clip, float noise_std, float scale,
                       unsigned long long seed, int blocks, void* stream);
+/* fr_grad_allreduce with the optimiser fused in: after the averaged gradient has arrived, the same kernel applies one Adam
+ * step (torch.optim.Adam defaults) to each local rank's flat parameters. params/m/v_host: W pointers (only the local ranks'
+ * entries are read), bc1 = 1 - b1^t, bc2 = 1 - b2^t. Replaces DDP all-reduce + model.py:89,93 (two Adam steps). */
+int fr_grad_allreduce_adam(void* const* bufs_host, void* const* pads_host, void* mc_buf, int W, int rank_base,
+                           int ranks_here, long long n, unsigned epoch, float clip, float noise_std, float scale,
+                           unsigned long long seed, void* const* params_host, void* const* m_host, void* const* v_host,
+                           float lr, float b1, float b2, float eps, float bc1, float bc2, int blocks, void* stream);
 int fr_param_average(void* const* bufs_host, void* const* pads_host, void* mc_buf, const float* weights_host, int W,
                      int rank_base, int ranks_here, long long n, unsigned epoch, int blocks, void* stream);
 int fr_signal_pad_bytes(void);

@@ -89,3 +89,32 @@ def test_param_average_weighted_and_broadcast(heaps8, W):
     torch.cuda.synchronize()
     for b in bufs:
         assert torch.equal(b, src[W - 1])
+
+
+@pytest.mark.parametrize("W", [2, 8])
+def test_grad_mean_with_fused_adam_tail(heaps8, W):
+    """Aggregation + Adam in one kernel == aggregation, then torch.optim.Adam on the averaged gradient."""
+    hs = heaps8[W]
+    bufs = [getattr(h, "_g", None) if getattr(h, "_g", None) is not None else h.alloc_f32(N) for h in hs]
+    torch.manual_seed(30 + W)
+    dev = bufs[0].device
+    params = [torch.randn(N, device=dev) for _ in range(W)]
+    ms = [torch.zeros(N, device=dev) for _ in range(W)]
+    vs = [torch.zeros(N, device=dev) for _ in range(W)]
+    refs = [torch.nn.Parameter(p.clone()) for p in params]
+    opts = [torch.optim.Adam([r], lr=5e-5) for r in refs]
+    for step in (1, 2, 3):
+        for h, b in zip(hs, bufs):
+            h._g = b
+            b.copy_(torch.randn(N, device=dev) * 0.01 * (1 + h.rank))
+        want = torch.stack([b.clone() for b in bufs]).sum(0) / W
+        hs[0].grad_allreduce_adam_(bufs[0], clip=0.0, noise_std=0.0, seed=1, scale=1.0 / W, params=params, exp_avg=ms,
+                                   exp_avg_sq=vs, step=step, lr=5e-5, b1=0.9, b2=0.999, eps=1e-8, ranks_here=W)
+        torch.cuda.synchronize()
+        for r, o in zip(refs, opts):
+            r.grad = want.clone()
+            o.step()
+        for b in bufs:
+            torch.testing.assert_close(b, want, atol=1e-7, rtol=1e-5)
+    for p_, r in zip(params, refs):
+        torch.testing.assert_close(p_, r.data, atol=1e-6, rtol=1e-5)

@@ -58,8 +58,12 @@ def _worker(rank, world, port, q):
         gathered = [torch.zeros_like(p) for _ in range(world)]
         dist.all_gather(gathered, p)
         res["identical"] = all(torch.equal(gathered[0], x) for x in gathered)
-        loss = r.run_gradient_averaging()
+        loss = r.run_gradient_averaging()                   # aggregation + Adam fused in one kernel per round
         res["loss"] = loss
+        p2 = r.model.flat.param
+        g2 = [torch.zeros_like(p2) for _ in range(world)]
+        dist.all_gather(g2, p2)
+        res["identical_after_training"] = all(torch.equal(g2[0], x) for x in g2)
         r.close()
     except Exception as e:  # noqa: BLE001
         import traceback
@@ -81,7 +85,7 @@ def test_nvlink_aggregation_matches_nccl():
         assert "error" not in out[r], out[r].get("error")
         assert out[r]["grad_rel_err"] < 1e-5, out
         assert out[r]["param_rel_err"] < 1e-5, out
-        assert out[r]["identical"]
+        assert out[r]["identical"] and out[r]["identical_after_training"]
         assert out[r]["loss"] == out[r]["loss"]
 
 
