@@ -254,18 +254,30 @@ __global__ void __launch_bounds__(128) text_pool_kernel(const __nv_bfloat16* __r
   for (int n = blockIdx.x * 4 + w; n < n_eff; n += gridDim.x * 4) {
     const size_t row0 = (size_t)n * T;
     const int item = items ? items[n] : n;
+    // logits a_t = e_t · w2 + b2, four rows per pass: 8 lanes share a row (16-byte loads), 3 shuffle steps per row
     float mx = -INFINITY;
-    for (int t = 0; t < T; ++t) {
+    const int sub = lane & 7, rgrp = lane >> 3;
+    for (int t0 = 0; t0 < T; t0 += 4) {
+      const int t = t0 + rgrp;
       float s = 0.f;
-      for (int c = lane * 2; c < Hq; c += 64) {
-        const float2 ef = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(e + (row0 + t) * Hq + c));
-        s = fmaf(ef.x, w2[c], s);
-        s = fmaf(ef.y, w2[c + 1], s);
+      if (t < T) {
+        for (int c = sub * 8; c < Hq; c += 64) {
+          float ev[8];
+          load8(e + (row0 + t) * Hq + c, ev);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) s = fmaf(ev[i], w2[c + i], s);
+        }
       }
-      s = warp_sum(s) + b2[0];
-      if (lane == 0) sA[w][t] = s;
-      mx = fmaxf(mx, s);
+      s += __shfl_xor_sync(0xffffffffu, s, 4);
+      s += __shfl_xor_sync(0xffffffffu, s, 2);
+      s += __shfl_xor_sync(0xffffffffu, s, 1);
+      s += b2[0];
+      if (t < T) {
+        if (sub == 0) sA[w][t] = s;
+        mx = fmaxf(mx, s);
+      }
     }
+    mx = warp_max(mx);
     __syncwarp();
     float z = 0.f;
     for (int t = lane; t < T; t += 32) {
@@ -280,6 +292,7 @@ __global__ void __launch_bounds__(128) text_pool_kernel(const __nv_bfloat16* __r
     float acc[kPerLane];
 #pragma unroll
     for (int i = 0; i < kPerLane; ++i) acc[i] = 0.f;
+#pragma unroll 4
     for (int t = 0; t < T; ++t) {
       const float a = sA[w][t] * invz;
       if (lane == 0 && alpha_out) alpha_out[row0 + t] = a;
@@ -369,6 +382,7 @@ __global__ void __launch_bounds__(kDpreRowLanes * 64) text_dpre_kernel(const __n
 #pragma unroll
   for (int i = 0; i < 8; ++i) { wv[i] = col_ok ? w2[cq * 8 + i] : 0.f; aw[i] = 0.f; ab[i] = 0.f; }
   if (col_ok) {
+#pragma unroll 4
     for (int r = r0 + rl; r < r1; r += kDpreRowLanes) {
       float out[8];
       if (r < rows_eff) {
@@ -498,7 +512,7 @@ FR_API int fr_text_pool(const void* hidden, const void* e, const float* w2, cons
                         const int* items, const int* count_dev, int n_items, int T, int Hq, int hidden_dim,
                         void* pooled, float* alpha_out, void* stream) {
   FR_REQUIRE(hidden_dim == kHid, "fr_text_pool: hidden=%d (only %d is built)", hidden_dim, kHid);
-  FR_REQUIRE(T >= 1 && T <= kMaxT && Hq % 2 == 0, "fr_text_pool: T=%d Hq=%d", T, Hq);
+  FR_REQUIRE(T >= 1 && T <= kMaxT && Hq % 8 == 0, "fr_text_pool: T=%d Hq=%d (Hq must be a multiple of 8)", T, Hq);
   if (n_items == 0) return 0;
   text_pool_kernel<<<grid_for(n_items, 4, kNumSMs * 8), 128, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)hidden, (const __nv_bfloat16*)e, w2, b2, mask_table, items, count_dev, n_items, T, Hq,
@@ -517,7 +531,7 @@ FR_API int fr_text_pool_bwd(const void* hidden, const void* e, const float* alph
   text_pool_bwd_kernel<<<grid_for(n_items, 4, kNumSMs * 8), 128, 0, s>>>(
       (const __nv_bfloat16*)hidden, alpha, (const __nv_bfloat16*)d_pooled, count_dev, n_items, T, da_scratch, d_b2);
   const int rows = n_items * T;
-  const int rows_per_block = 64;
+  const int rows_per_block = 160;
   text_dpre_kernel<<<(rows + rows_per_block - 1) / rows_per_block, kDpreRowLanes * 64, 0, s>>>(
       (const __nv_bfloat16*)e, da_scratch, w2, count_dev, rows, T, Hq, rows_per_block, (__nv_bfloat16*)d_pre, d_w2, d_b1);
   FR_LAUNCH_CHECK();

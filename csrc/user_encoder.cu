@@ -238,8 +238,9 @@ __global__ void __launch_bounds__(kJobThreads) ue_mha_bwd_kernel(const __nv_bflo
 
 // ---------------------------------------------------------------------------------------------------
 // Additive pooling + candidate scoring + sigmoid + soft-max CE, forward and (optionally) backward.
-// One block (128 threads) per user. D <= 512, Q <= 256, L <= 64, C <= 32.
+// One block (512 threads) per user. D <= 512, Q <= 256, L <= 64, C <= 32.
 // ---------------------------------------------------------------------------------------------------
+constexpr int kPoolThreads = 512;   // one block per user; B is small (50), so latency per user is what matters
 struct PoolScoreArgs {
   const __nv_bfloat16* ctx;     // [B*L, D]
   const __nv_bfloat16* e;       // [B*L, Q]  tanh(fc1)
@@ -263,7 +264,7 @@ struct PoolScoreArgs {
   const unsigned long long* seed_dev;
 };
 
-__global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs a) {
+__global__ void __launch_bounds__(kPoolThreads) ue_pool_score_kernel(const PoolScoreArgs a) {
   __shared__ float sA[kMaxL];          // logits → exp → alpha
   __shared__ float sU[512];            // user vector, later d_u
   __shared__ float sS[32];             // candidate logits / ds
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   const int L = a.L, D = a.D, Q = a.Q, C = a.C;
   const size_t row0 = (size_t)b * L;
   // a_l = e_l · w2 + b2  (one warp per row, 4 rows in flight)
-  for (int l = w; l < L; l += 4) {
+  for (int l = w; l < L; l += kPoolThreads / 32) {
     float s = 0.f;
     for (int c = lane; c < Q; c += 32) s = fmaf(__bfloat162float(a.e[(row0 + l) * Q + c]), a.w2[c], s);
     s = warp_sum(s);
@@ -281,10 +282,10 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   }
   __syncthreads();
   float mx = -INFINITY;
-  for (int l = tid; l < L; l += 128) mx = fmaxf(mx, sA[l]);
+  for (int l = tid; l < L; l += kPoolThreads) mx = fmaxf(mx, sA[l]);
   mx = block_max(mx, red);
   float z = 0.f;
-  for (int l = tid; l < L; l += 128) {
+  for (int l = tid; l < L; l += kPoolThreads) {
     const float mk = (a.use_mask && a.his_ids[row0 + l] == 0) ? 0.f : 1.f;
     const float ex = __expf(sA[l] - mx) * mk;
     sA[l] = ex;
@@ -292,10 +293,10 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   }
   z = block_sum(z, red) + 1e-8f * __expf(-mx);
   __syncthreads();
-  for (int l = tid; l < L; l += 128) sA[l] *= 1.f / z;
+  for (int l = tid; l < L; l += kPoolThreads) sA[l] *= 1.f / z;
   __syncthreads();
   // u = sum_l alpha_l ctx_l
-  for (int d = tid; d < D; d += 128) {
+  for (int d = tid; d < D; d += kPoolThreads) {
     float acc = 0.f;
     for (int l = 0; l < L; ++l) acc = fmaf(sA[l], __bfloat162float(a.ctx[(row0 + l) * D + d]), acc);
     sU[d] = acc;
@@ -303,7 +304,7 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   }
   __syncthreads();
   // candidate logits
-  for (int c = w; c < C; c += 4) {
+  for (int c = w; c < C; c += kPoolThreads / 32) {
     const float* cv = a.news_vecs + (size_t)a.inv_cand[b * C + c] * D;
     float s = 0.f;
     for (int d = lane; d < D; d += 32) s = fmaf(cv[d], sU[d], s);
@@ -331,7 +332,7 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   {
     const Philox nrng(a.noise_seed + (a.seed_dev ? *a.seed_dev : 0ull));
     const int D4 = D / 4;
-    for (int i = tid; i < C * D4; i += 128) {
+    for (int i = tid; i < C * D4; i += kPoolThreads) {
       const int c = i / D4, q = i - c * D4;
       const float ds = sS[c];
       float4 v = make_float4(ds * sU[4 * q], ds * sU[4 * q + 1], ds * sU[4 * q + 2], ds * sU[4 * q + 3]);
@@ -344,14 +345,14 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
     }
   }
   __syncthreads();
-  for (int d = tid; d < D; d += 128) {
+  for (int d = tid; d < D; d += kPoolThreads) {
     float du = 0.f;
     for (int c = 0; c < C; ++c) du = fmaf(sS[c], a.news_vecs[(size_t)a.inv_cand[b * C + c] * D + d], du);
     sU[d] = du;                       // from here on sU holds d_u
   }
   __syncthreads();
   // d_alpha_l = d_u · ctx_l ; d_ctx_pool[l] = alpha_l * d_u
-  for (int l = w; l < L; l += 4) {
+  for (int l = w; l < L; l += kPoolThreads / 32) {
     float s = 0.f;
     const float al = sA[l];
     for (int d = lane * 2; d < D; d += 64) {
@@ -365,11 +366,11 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   }
   __syncthreads();
   float dot = 0.f;
-  for (int l = tid; l < L; l += 128) dot = fmaf(sA[l], sDal[l], dot);
+  for (int l = tid; l < L; l += kPoolThreads) dot = fmaf(sA[l], sDal[l], dot);
   dot = block_sum(dot, red);
   __syncthreads();
   float db2 = 0.f;
-  for (int l = tid; l < L; l += 128) {
+  for (int l = tid; l < L; l += kPoolThreads) {
     const float da = sA[l] * (sDal[l] - dot);
     sDal[l] = da;
     db2 += da;
@@ -378,7 +379,7 @@ __global__ void __launch_bounds__(128) ue_pool_score_kernel(const PoolScoreArgs 
   if (tid == 0) atomicAdd(a.d_b2, db2);
   __syncthreads();
   // d_w2 += sum_l da_l e_l ; d_pre[l] = da_l * w2 * (1 - e^2)
-  for (int c = tid; c < Q; c += 128) {
+  for (int c = tid; c < Q; c += kPoolThreads) {
     float acc = 0.f;
     const float wc = a.w2[c];
     for (int l = 0; l < L; ++l) {
@@ -536,7 +537,7 @@ FR_API int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, con
   a.d_ctx_pool = (__nv_bfloat16*)d_ctx_pool; a.d_pre = (__nv_bfloat16*)d_pre; a.d_w2 = d_w2; a.d_b2 = d_b2; a.d_news = d_news;
   a.B = B; a.L = L; a.C = C; a.D = D; a.Q = Q; a.use_mask = use_mask; a.train = train; a.noise_std = noise_std;
   a.noise_seed = noise_seed; a.seed_dev = seed_dev;
-  ue_pool_score_kernel<<<B, 128, 0, s>>>(a);
+  ue_pool_score_kernel<<<B, kPoolThreads, 0, s>>>(a);
   FR_LAUNCH_CHECK();
   return 0;
 }
