@@ -143,28 +143,54 @@ __global__ void __launch_bounds__(kJobThreads) ue_mha_fwd_kernel(const __nv_bflo
 
 // Backward of the attention: dctx bf16 [B*L, H*dk] → dqkv bf16 [B*L, 3*H*dk]. Probabilities are
 // recomputed from q, k and the saved (max, denominator).
+// dot of a register row with a shared-memory row read as float4 (all threads read the same row: broadcast)
+template <int DKP>
+__device__ __forceinline__ float dot_row(const float* reg, const float* srow) {
+  float s = 0.f;
+#pragma unroll
+  for (int d = 0; d < DKP; d += 4) {
+    const float4 k = *reinterpret_cast<const float4*>(srow + d);
+    s = fmaf(reg[d], k.x, s); s = fmaf(reg[d + 1], k.y, s); s = fmaf(reg[d + 2], k.z, s); s = fmaf(reg[d + 3], k.w, s);
+  }
+  return s;
+}
+template <int DKP>
+__device__ __forceinline__ void axpy_row(float* reg, float a, const float* srow) {
+#pragma unroll
+  for (int d = 0; d < DKP; d += 4) {
+    const float4 k = *reinterpret_cast<const float4*>(srow + d);
+    reg[d] = fmaf(a, k.x, reg[d]); reg[d + 1] = fmaf(a, k.y, reg[d + 1]);
+    reg[d + 2] = fmaf(a, k.z, reg[d + 2]); reg[d + 3] = fmaf(a, k.w, reg[d + 3]);
+  }
+}
+
 template <int DK>
 __global__ void __launch_bounds__(kJobThreads) ue_mha_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dctx,
                                                                  const float* __restrict__ stats, const int* __restrict__ his_ids,
                                                                  __nv_bfloat16* __restrict__ dqkv, int B, int L, int H, float scale,
                                                                  int use_mask) {
-  __shared__ float sQ[kMaxL][DK + 1];     // q * scale
-  __shared__ float sK[kMaxL][DK + 1];
-  __shared__ float sV[kMaxL][DK + 1];
-  __shared__ float sG[kMaxL][DK + 1];     // dctx
+  constexpr int DKP = (DK + 3) / 4 * 4;            // rows padded to 16 bytes: the hot loops read them as float4 broadcasts
+  __shared__ __align__(16) float sQ[kMaxL][DKP];   // q * scale
+  __shared__ __align__(16) float sK[kMaxL][DKP];
+  __shared__ __align__(16) float sV[kMaxL][DKP];
+  __shared__ __align__(16) float sG[kMaxL][DKP];   // dctx
   __shared__ float sMx[kMaxL], sZ[kMaxL], sDd[kMaxL], sMask[kMaxL];
   const int tid = threadIdx.x;
   const int job = blockIdx.x;
   const int b = job / H, h = job - b * H;
   const int ld = 3 * H * DK;
   const size_t row0 = (size_t)b * L;
-  for (int i = tid; i < L * DK; i += kJobThreads) {
-    const int r = i / DK, d = i - r * DK;
-    const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * DK + d;
-    sQ[r][d] = __bfloat162float(base[0]) * scale;
-    sK[r][d] = __bfloat162float(base[H * DK]);
-    sV[r][d] = __bfloat162float(base[2 * H * DK]);
-    sG[r][d] = __bfloat162float(dctx[(row0 + r) * (size_t)(H * DK) + h * DK + d]);
+  for (int i = tid; i < L * DKP; i += kJobThreads) {
+    const int r = i / DKP, d = i - r * DKP;
+    float q = 0.f, k = 0.f, v = 0.f, g = 0.f;
+    if (d < DK) {
+      const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * DK + d;
+      q = __bfloat162float(base[0]) * scale;
+      k = __bfloat162float(base[H * DK]);
+      v = __bfloat162float(base[2 * H * DK]);
+      g = __bfloat162float(dctx[(row0 + r) * (size_t)(H * DK) + h * DK + d]);
+    }
+    sQ[r][d] = q; sK[r][d] = k; sV[r][d] = v; sG[r][d] = g;
   }
   for (int j = tid; j < L; j += kJobThreads) {
     sMx[j] = stats[((size_t)job * L + j) * 2];
@@ -174,31 +200,22 @@ __global__ void __launch_bounds__(kJobThreads) ue_mha_bwd_kernel(const __nv_bflo
   __syncthreads();
   // pass 1 (thread = query i): Dd_i = sum_j P_ij dP_ij, then dQ_i = scale * sum_j dS_ij K_j
   for (int i = tid; i < L; i += kJobThreads) {
+    float q[DKP], g[DKP];
+#pragma unroll
+    for (int d = 0; d < DKP; ++d) { q[d] = sQ[i][d]; g[d] = sG[i][d]; }
     const float m = sMx[i], invz = 1.f / sZ[i];
     float dd = 0.f;
     for (int j = 0; j < L; ++j) {
-      float s = 0.f, dp = 0.f;
-#pragma unroll
-      for (int d = 0; d < DK; ++d) {
-        s = fmaf(sQ[i][d], sK[j][d], s);
-        dp = fmaf(sG[i][d], sV[j][d], dp);
-      }
+      const float s = dot_row<DKP>(q, sK[j]), dp = dot_row<DKP>(g, sV[j]);
       dd = fmaf(__expf(s - m) * sMask[j] * invz, dp, dd);
     }
     sDd[i] = dd;
-    float dq[DK];
+    float dq[DKP];
 #pragma unroll
-    for (int d = 0; d < DK; ++d) dq[d] = 0.f;
+    for (int d = 0; d < DKP; ++d) dq[d] = 0.f;
     for (int j = 0; j < L; ++j) {
-      float s = 0.f, dp = 0.f;
-#pragma unroll
-      for (int d = 0; d < DK; ++d) {
-        s = fmaf(sQ[i][d], sK[j][d], s);
-        dp = fmaf(sG[i][d], sV[j][d], dp);
-      }
-      const float ds = __expf(s - m) * sMask[j] * invz * (dp - dd);
-#pragma unroll
-      for (int d = 0; d < DK; ++d) dq[d] = fmaf(ds, sK[j][d], dq[d]);
+      const float s = dot_row<DKP>(q, sK[j]), dp = dot_row<DKP>(g, sV[j]);
+      axpy_row<DKP>(dq, __expf(s - m) * sMask[j] * invz * (dp - dd), sK[j]);
     }
     __nv_bfloat16* op = dqkv + (row0 + i) * ld + h * DK;
 #pragma unroll
@@ -208,24 +225,15 @@ __global__ void __launch_bounds__(kJobThreads) ue_mha_bwd_kernel(const __nv_bflo
   __syncthreads();
   // pass 2 (thread = key j): dV_j = sum_i P_ij dctx_i ; dK_j = sum_i dS_ij (q_i * scale)
   for (int j = tid; j < L; j += kJobThreads) {
-    float dk[DK], dv[DK];
+    float kj[DKP], vj[DKP], dk[DKP], dv[DKP];
 #pragma unroll
-    for (int d = 0; d < DK; ++d) { dk[d] = 0.f; dv[d] = 0.f; }
+    for (int d = 0; d < DKP; ++d) { kj[d] = sK[j][d]; vj[d] = sV[j][d]; dk[d] = 0.f; dv[d] = 0.f; }
     const float mk = sMask[j];
     for (int i = 0; i < L; ++i) {
-      float s = 0.f, dp = 0.f;
-#pragma unroll
-      for (int d = 0; d < DK; ++d) {
-        s = fmaf(sQ[i][d], sK[j][d], s);
-        dp = fmaf(sG[i][d], sV[j][d], dp);
-      }
+      const float s = dot_row<DKP>(kj, sQ[i]), dp = dot_row<DKP>(vj, sG[i]);
       const float pij = __expf(s - sMx[i]) * mk / sZ[i];
-      const float ds = pij * (dp - sDd[i]);
-#pragma unroll
-      for (int d = 0; d < DK; ++d) {
-        dv[d] = fmaf(pij, sG[i][d], dv[d]);
-        dk[d] = fmaf(ds, sQ[i][d], dk[d]);     // sQ already carries the 1/sqrt(dk) factor
-      }
+      axpy_row<DKP>(dv, pij, sG[i]);
+      axpy_row<DKP>(dk, pij * (dp - sDd[i]), sQ[i]);   // sQ already carries the 1/sqrt(dk) factor
     }
     __nv_bfloat16* op = dqkv + (row0 + j) * ld + h * DK;
 #pragma unroll
