@@ -389,8 +389,12 @@ class FusedStep:
         return u["loss"].clone()
 
     @torch.no_grad()
-    def scores(self, cand: torch.Tensor, his: torch.Tensor) -> torch.Tensor:
+    def scores(self, cand: torch.Tensor, his: torch.Tensor, chunk: int = 64) -> torch.Tensor:
+        """Inference scores ``[B, C]``. Large batches are processed ``chunk`` users at a time so the activation buffers
+        (sized for the worst case of every id being distinct) stay at a couple of fixed sizes."""
         B, C = cand.shape
+        if B > chunk:
+            return torch.cat([self.scores(cand[i:i + chunk], his[i:i + chunk], chunk) for i in range(0, B, chunk)])
         L = his.shape[1]
         with self._fork():
             self._pack_weights(False)
