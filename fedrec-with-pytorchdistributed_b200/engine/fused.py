@@ -35,27 +35,41 @@ class PackedTrunk:
 
     @torch.no_grad()
     def repack(self) -> None:
+        """(Re)fill the packed copies **in place**: captured CUDA graphs and in-flight steps hold these pointers, so a
+        weight change (load_state_dict, full-state FedAvg) must never move them."""
         b = self.bert
-        bf = torch.bfloat16
-        self.word = D.cast_bf16(b.embeddings.word_embeddings.weight.data)
-        self.pos = D.cast_bf16(b.embeddings.position_embeddings.weight.data)
-        self.emb_g = b.embeddings.LayerNorm.weight.data.float().contiguous()
-        self.emb_b = b.embeddings.LayerNorm.bias.data.float().contiguous()
-        self.layers = []
-        for blk in b.transformer.layer:
+        first = not hasattr(self, "layers")
+
+        def put(store, key, value_fp32, bf16):
+            value_fp32 = value_fp32.contiguous()
+            if first:
+                store[key] = D.cast_bf16(value_fp32) if bf16 else value_fp32.float().clone()
+            elif bf16:
+                D.cast_bf16(value_fp32, out=store[key])
+            else:
+                store[key].copy_(value_fp32)
+
+        if first:
+            self.emb, self.layers = {}, [dict() for _ in b.transformer.layer]
+        put(self.emb, "word", b.embeddings.word_embeddings.weight.data, True)
+        put(self.emb, "pos", b.embeddings.position_embeddings.weight.data, True)
+        put(self.emb, "g", b.embeddings.LayerNorm.weight.data, False)
+        put(self.emb, "b", b.embeddings.LayerNorm.bias.data, False)
+        self.word, self.pos, self.emb_g, self.emb_b = self.emb["word"], self.emb["pos"], self.emb["g"], self.emb["b"]
+        for blk, L in zip(b.transformer.layer, self.layers):
             a = blk.attention
-            wqkv = torch.cat([a.q_lin.weight.data, a.k_lin.weight.data, a.v_lin.weight.data], 0)
-            self.layers.append({
-                "wqkv": D.cast_bf16(wqkv),
-                "bqkv": torch.cat([a.q_lin.bias.data, a.k_lin.bias.data, a.v_lin.bias.data]).float().contiguous(),
-                "wo": D.cast_bf16(a.out_lin.weight.data), "bo": a.out_lin.bias.data.float().contiguous(),
-                "ln1_g": blk.sa_layer_norm.weight.data.float().contiguous(),
-                "ln1_b": blk.sa_layer_norm.bias.data.float().contiguous(),
-                "w1": D.cast_bf16(blk.ffn.lin1.weight.data), "b1": blk.ffn.lin1.bias.data.float().contiguous(),
-                "w2": D.cast_bf16(blk.ffn.lin2.weight.data), "b2": blk.ffn.lin2.bias.data.float().contiguous(),
-                "ln2_g": blk.output_layer_norm.weight.data.float().contiguous(),
-                "ln2_b": blk.output_layer_norm.bias.data.float().contiguous(),
-            })
+            put(L, "wqkv", torch.cat([a.q_lin.weight.data, a.k_lin.weight.data, a.v_lin.weight.data], 0), True)
+            put(L, "bqkv", torch.cat([a.q_lin.bias.data, a.k_lin.bias.data, a.v_lin.bias.data]), False)
+            put(L, "wo", a.out_lin.weight.data, True)
+            put(L, "bo", a.out_lin.bias.data, False)
+            put(L, "ln1_g", blk.sa_layer_norm.weight.data, False)
+            put(L, "ln1_b", blk.sa_layer_norm.bias.data, False)
+            put(L, "w1", blk.ffn.lin1.weight.data, True)
+            put(L, "b1", blk.ffn.lin1.bias.data, False)
+            put(L, "w2", blk.ffn.lin2.weight.data, True)
+            put(L, "b2", blk.ffn.lin2.bias.data, False)
+            put(L, "ln2_g", blk.output_layer_norm.weight.data, False)
+            put(L, "ln2_b", blk.output_layer_norm.bias.data, False)
         self.heads = b.config.n_heads
         self.dim = b.config.dim
         self.ffn = b.config.hidden_dim
@@ -335,7 +349,9 @@ class FusedStep:
         the dropout / noise streams so every replay draws fresh randomness."""
         if not (train and self.cfg.cuda_graph):
             return self._run_eager(cand, his, train)
-        key = (tuple(cand.shape), tuple(his.shape))
+        cfg = self.cfg      # everything a captured launch bakes in as a constant is part of the key
+        key = (tuple(cand.shape), tuple(his.shape), float(cfg.news_grad_noise), bool(cfg.mask_padding), bool(cfg.dedup),
+               bool(cfg.trunk_cache), float(self.model.user_encoder.dropout_rate))
         g = self._graphs.get(key)
         if g is None:
             g = self._capture(cand, his, key)

@@ -106,3 +106,27 @@ def test_fused_step_with_upstream_toy_shapes():
     assert float(la) == pytest.approx(float(lb), abs=5e-3)
     rel = float((a.flat.grad - b.flat.grad).norm() / b.flat.grad.norm())
     assert rel < 5e-2, rel
+
+
+def test_captured_graph_follows_trunk_weight_changes():
+    """load_state_dict / full-state FedAvg replace the frozen trunk's weights: the packed bf16 copies are refilled in
+    place, so the already captured CUDA graph computes with the new weights."""
+    a, b = _models()
+    g = torch.Generator(device=DEV).manual_seed(7)
+    cand = torch.randint(1, 600, (6, 5), device=DEV, generator=g, dtype=torch.int32)
+    his = torch.randint(0, 600, (6, 50), device=DEV, generator=g, dtype=torch.int32)
+    fused, oracle = TrainStep(a, impl="fused"), TrainStep(b, impl="torch")
+    l0 = float(fused.run(cand, his))                                    # captures the graph
+    sd = {k: v.clone() for k, v in a.state_dict().items()}
+    for k in sd:
+        if "DistillBert" in k and k.endswith("lin1.weight"):
+            sd[k] = sd[k] * 0.5
+        if "DistillBert" in k and "word_embeddings" in k:
+            sd[k] = sd[k] * 2.0
+    a.load_state_dict(sd)
+    b.load_state_dict(sd)
+    la, lb = fused.run(cand, his), oracle.run(cand, his)
+    assert float(la) == pytest.approx(float(lb), abs=5e-3)
+    assert abs(float(la) - l0) > 1e-6                                   # the change was visible at all
+    rel = float((a.flat.grad - b.flat.grad).norm() / b.flat.grad.norm())
+    assert rel < 5e-2, rel
