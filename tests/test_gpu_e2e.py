@@ -57,6 +57,7 @@ def test_fused_training_learns_planted_signal():
     data = make_synthetic_mind(num_news=2000, num_train=512, num_valid=128, title_len=30, seed=22, topics=4,
                                generic_frac=0.0, liked_topics=1)
     fl, fv, ft = _train(True, data, steps=600, lr=1e-4)
+    print("e2e learning:", float(fl[:50].mean()), float(fl[-50:].mean()), "train", ft, "valid", fv)
     assert torch.isfinite(fl).all()
     assert float(fl[-50:].mean()) < float(fl[:50].mean()) - 1e-3, (fl[:5], fl[-5:])   # the loss goes down
     assert ft[1] > 0.58 and fv[1] > 0.55, (ft, fv)                   # AUC clearly above chance on train and valid
