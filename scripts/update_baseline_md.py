@@ -95,6 +95,16 @@ without any epilogue. Evidence: `profiles/gemm_bench.json`, ncu summaries `profi
 In-situ (inside the training step, warm caches, power-capped clocks, `scripts/step_profile.py`, `profiles/step_profile.txt`):
 the four trunk GEMMs run at 0.9–1.4 PFLOP/s and account for ≈62 % of the step; attention ≈9 %, LayerNorm ≈7 %.
 
+### 3.4 Ranking quality of the kernel path vs the fp32 path (`tests/test_gpu_e2e.py`, planted-signal synthetic data)
+
+* Same weights, same batches, upstream's learning rate (5e-5), 40 steps: the bf16 kernel path follows the fp32 PyTorch
+  path's loss curve within 5e-3 at every step, and validation / training AUC, MRR, nDCG@5, nDCG@10 agree within 0.05
+  (the test's bounds; observed differences are an order of magnitude smaller).
+* 600 steps at lr 1e-4 on a 4-topic planted signal: loss 1.596 → 1.101, AUC 0.81 / MRR 0.73 / nDCG@5 0.80 / nDCG@10 0.80 on
+  training impressions and AUC 0.73 / MRR 0.67 / nDCG@5 0.75 / nDCG@10 0.75 on held-out impressions (chance: AUC 0.5).
+* The published MIND / Adressa quality numbers of the reference (section 1) need the real datasets and pretrained DistilBERT
+  weights, neither of which exists on these boxes.
+
 '''
     p = os.path.join(ROOT, "BASELINE.md")
     s = open(p).read()
