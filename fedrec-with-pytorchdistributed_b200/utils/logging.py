@@ -17,7 +17,7 @@ class MetricsLogger:
                  echo: bool = True):
         self.rank = rank
         self.enabled = enabled
-        self.echo = echo
+        self.echo = echo and os.environ.get("FEDREC_QUIET") != "1"
         self.path = None
         self._fh = None
         self._wandb = None
