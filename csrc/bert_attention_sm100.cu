@@ -13,7 +13,8 @@
 // The block-diagonal waste (x TP in MMA work) is irrelevant: the tile is latency-bound, not throughput-bound.
 // One CTA = 4 warps; thread r owns row r of the tile for the soft-max and the epilogue; lane 0 of warp 0 issues
 // the TMA loads (one job ahead of the math) and both MMAs. 80 KB of shared memory and 256 TMEM columns per CTA,
-// so two CTAs share an SM and hide each other's latencies. Reference: HF MultiHeadSelfAttention reached from
+// so two CTAs share an SM and hide each other's latencies. (Measured: a third CTA per SM, with O aliased onto S and
+// 24 KB of P, did not shorten the kernel, so the SM's issue/TMEM path rather than latency is the limit.) Reference: HF MultiHeadSelfAttention reached from
 // encoder.py:27.
 #include "sm100.cuh"
 #include <cuda.h>
@@ -26,6 +27,8 @@ int make_tmap_bf16_2d_box(CUtensorMap* out, const void* base, long long rows, lo
 
 constexpr int kAttTile = 128;
 constexpr int kAttHd = 64;
+constexpr int kAttPBlk = 16384;                // bytes of one 64-column block of P
+constexpr int kAttBar = 49152 + 32768;         // barriers follow Q, K, V (16 KB each) and P (32 KB)
 
 __device__ __forceinline__ uint64_t att_desc_k_sw128(uint32_t addr) { return make_smem_desc_sw128(addr); }
 __device__ __forceinline__ uint64_t att_desc_mn_sw128(uint32_t addr) {
@@ -61,11 +64,11 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   uint8_t* sK = smem + 16384;
   uint8_t* sV = smem + 32768;             // tokens x 64: MN-major SW128 for the second MMA
   uint8_t* sP = smem + 49152;             // 128 x 128 bf16 as two K-major SW128 blocks of 64 columns
-  uint64_t* bar_qk = reinterpret_cast<uint64_t*>(smem + 81920);    // Q and K of the next (tile, head) have landed
+  uint64_t* bar_qk = reinterpret_cast<uint64_t*>(smem + kAttBar);    // Q and K of the next (tile, head) have landed
   uint64_t* bar_v = bar_qk + 1;                                     // V of the next (tile, head) has landed
   uint64_t* bar_mma = bar_v + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mma + 1);
-  float* sKeyBias = reinterpret_cast<float*>(smem + 81920 + 64);  // [128] per key column: 0 or -inf, pre-scaled domain
+  float* sKeyBias = reinterpret_cast<float*>(smem + kAttBar + 64);  // [128] per key column: 0 or -inf, pre-scaled domain
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int T = p.T, heads = p.heads;
@@ -73,7 +76,6 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   const int num_tiles = (n_eff + TP - 1) / TP;
   const int hd_all = heads * kAttHd;
 
-  griddep_launch();                            // the out-projection GEMM may start its prologue
   if (tid == 0) {
     prefetch_tmap(&tmap_qkv);
     mbar_init(bar_qk, 1);
@@ -83,10 +85,10 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   }
   // off-diagonal blocks of P stay zero for the whole kernel
   {
-    const uint32_t prow = smem_u32(sP) + (uint32_t)tid * 128;
+    const uint32_t pz = smem_u32(sP) + (uint32_t)tid * 256;
 #pragma unroll
     for (int c = 0; c < 16; ++c)
-      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(prow + (uint32_t)(c >> 3) * 16384 + (uint32_t)(c & 7) * 16), "r"(0u) : "memory");
+      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(pz + (uint32_t)c * 16), "r"(0u) : "memory");
   }
   if (warp == 0) {
     __syncwarp();
@@ -96,6 +98,9 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  // The out-projection GEMM may start its prologue from here on. Not earlier: its CTAs allocate all 512 TMEM columns
+  // and then wait for this grid, so one that lands on this SM before our own allocation would deadlock both.
+  griddep_launch();
   const uint32_t tmem = *tmem_slot;
   const uint32_t tS = tmem, tO = tmem + 128;
   uint32_t ph_qk = 0, ph_v = 0, ph_mma = 0;
@@ -117,9 +122,14 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
     for (int t = 0; t < TP; ++t)
       tma_load_2d(sV + t * SLOT * 128, &tmap_qkv, bar_v, 2 * hd_all + h_ * kAttHd, (tile_ * TP + t) * T);
   };
-  if (tid == 0 && (int)blockIdx.x < num_tiles) {
-    load_qk(blockIdx.x, 0);
-    load_v(blockIdx.x, 0);
+  // Work unit = one (tile, head) job; every CTA takes a contiguous, balanced range of them so that the grid stays
+  // full when there are fewer tiles than CTA slots (tiles * heads / gridDim jobs each instead of whole tiles).
+  const long long total_jobs = (long long)num_tiles * heads;
+  const int job_begin = (int)(total_jobs * blockIdx.x / gridDim.x);
+  const int job_end = (int)(total_jobs * (blockIdx.x + 1) / gridDim.x);
+  if (tid == 0 && job_begin < job_end) {
+    load_qk(job_begin / heads, job_begin % heads);
+    load_v(job_begin / heads, job_begin % heads);
   }
 
   const int my_slot = tid / SLOT;                     // title slot of my row
@@ -128,11 +138,16 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   const uint32_t lane_base = ((uint32_t)(warp * 32) << 16);
   constexpr float kScaleLog2 = 0.125f * 1.4426950408889634f;     // 1/sqrt(64) * log2(e): soft-max in the exp2 domain
 
-  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-    const int title0 = tile * TP;
-    // key bias for the 128 key columns of this tile (key column tid and row tid belong to the same title slot)
-    bool my_uniform = false;
-    {
+  int cur_tile = -1;
+  bool my_uniform = false, row_ok = false;
+  size_t out_row = 0;
+  for (int job = job_begin; job < job_end; ++job) {
+    const int tile = job / heads, h = job - tile * heads;
+    if (tile != cur_tile) {
+      cur_tile = tile;
+      const int title0 = tile * TP;
+      // key bias for the 128 key columns of this tile (key column tid and row tid belong to the same title slot)
+      my_uniform = false;
       float bias = -INFINITY;
       if (my_tok < T && title0 + my_slot < n_eff) {
         const int item = p.items ? p.items[title0 + my_slot] : (title0 + my_slot);
@@ -142,18 +157,16 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
         my_uniform = mrow && !any;                    // fully masked title: HF's soft-max of a constant row = uniform
         bias = (!mrow || mrow[my_tok] != 0 || my_uniform) ? 0.f : -INFINITY;
       }
-      __syncthreads();                                // previous tile's readers are done with sKeyBias
-      sKeyBias[tid] = bias;
+      sKeyBias[tid] = bias;                           // the previous job ended with __syncthreads: no reader is left
+      __syncthreads();                                // sKeyBias is complete (every valid row of a title computed the same flag)
+      row_ok = my_tok < T && (title0 + my_slot) < n_eff;
+      out_row = (size_t)(title0 + my_slot) * T + my_tok;
     }
-    __syncthreads();                                  // sKeyBias is complete (every valid row of a title computed the same flag)
-    const bool row_ok = my_tok < T && (title0 + my_slot) < n_eff;
-    const size_t out_row = (size_t)(title0 + my_slot) * T + my_tok;
-
-    for (int h = 0; h < heads; ++h) {
-      // the job after this one (next head, or head 0 of this CTA's next tile)
-      const int nh = (h + 1 < heads) ? h + 1 : 0;
-      const int ntile = (h + 1 < heads) ? tile : tile + (int)gridDim.x;
-      const bool has_next = ntile < num_tiles;
+    {
+      // the job after this one
+      const int njob = job + 1;
+      const bool has_next = njob < job_end;
+      const int ntile = njob / heads, nh = njob - ntile * heads;
       mbar_wait(bar_qk, ph_qk);
       ph_qk ^= 1;
       if (tid == 0) {
@@ -204,7 +217,7 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
         }
         // 32 columns = 4 chunks of 16 bytes inside 64-column block; chunk index XOR (row % 8) = 128B swizzle
         const int cc = col0 + c * 32;
-        const uint32_t blk = prow + (uint32_t)(cc >> 6) * 16384;
+        const uint32_t blk = prow + (uint32_t)(cc >> 6) * kAttPBlk;
 #pragma unroll
         for (int q4 = 0; q4 < 4; ++q4) {
           const uint32_t chunk = (uint32_t)(((cc & 63) >> 3) + q4) ^ (uint32_t)(tid & 7);
@@ -223,7 +236,7 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
         const uint32_t pa = smem_u32(sP), v = smem_u32(sV);
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks)
-          umma_bf16_ss(tO, att_desc_k_sw128(pa + (ks >> 2) * 16384 + (ks & 3) * 32), att_desc_mn_sw128(v + ks * 2048), id2, ks > 0);
+          umma_bf16_ss(tO, att_desc_k_sw128(pa + (ks >> 2) * kAttPBlk + (ks & 3) * 32), att_desc_mn_sw128(v + ks * 2048), id2, ks > 0);
         umma_commit(bar_mma);
       }
       ph_v ^= 1;
@@ -281,15 +294,15 @@ FR_API int fr_bert_attention_tc(const void* qkv, const int* mask_table, const in
   AttParams p;
   p.mask_table = mask_table; p.items = items; p.count_dev = count_dev; p.out = (__nv_bfloat16*)out;
   p.n_items = n_items; p.T = T; p.heads = heads;
-  constexpr int smem = 81920 + 64 + 512 + 1024;
+  constexpr int smem = kAttBar + 64 + 512 + 1024;
   static bool attr_set = false;
   if (!attr_set) {
     FR_CHECK(cudaFuncSetAttribute(bert_attention_tc_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     FR_CHECK(cudaFuncSetAttribute(bert_attention_tc_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  int tiles = (n_items + TP - 1) / TP;
-  int grid = tiles < 2 * kNumSMs ? tiles : 2 * kNumSMs;
+  long long jobs = (long long)((n_items + TP - 1) / TP) * heads;      // (tile, head) jobs, split evenly over the CTAs
+  int grid = jobs < 2 * kNumSMs ? (int)jobs : 2 * kNumSMs;
   if (slot == 32) bert_attention_tc_kernel<32><<<grid, 128, smem, (cudaStream_t)stream>>>(tm, p);
   else bert_attention_tc_kernel<64><<<grid, 128, smem, (cudaStream_t)stream>>>(tm, p);
   FR_LAUNCH_CHECK();
