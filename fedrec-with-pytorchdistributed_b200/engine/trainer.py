@@ -71,11 +71,12 @@ def train_on_step(model, train_dl, optimizer=None, dp_enabled: bool = False, sig
 
 
 @torch.no_grad()
-def validate_impressions(step: TrainStep, model, valid_sam, nid2index, batch: int = 256):
+def validate_impressions(step: TrainStep, model, valid_sam, nid2index, batch: int = 256, last_only: bool = False):
     """Mean loss / AUC / MRR / nDCG@5 / nDCG@10 over validation impressions, computed on the device.
 
     Candidates per impression: the positive + the *last* ``npratio`` negatives (client.py:160). Upstream returns the last
-    sample's metrics only (client.py:171); means are reported here.
+    sample's metrics only, rounded to two decimals, next to the mean loss (client.py:171); means are reported here
+     unless ``last_only=True`` asks for the upstream numbers.
     """
     cfg = model.cfg
     L, K = cfg.max_his_len, cfg.npratio
@@ -97,6 +98,8 @@ def validate_impressions(step: TrainStep, model, valid_sam, nid2index, batch: in
     labels[:, 0] = 1
     loss = torch.nn.functional.cross_entropy(scores, torch.zeros(len(cands), dtype=torch.long, device=scores.device))
     m = batched_ranking_metrics(scores, labels)
+    if last_only:
+        return (float(loss),) + tuple(round(float(m[k][-1]), 2) for k in ("auc", "mrr", "ndcg5", "ndcg10"))
     return (float(loss), float(m["auc"].mean()), float(m["mrr"].mean()), float(m["ndcg5"].mean()),
             float(m["ndcg10"].mean()))
 
@@ -128,9 +131,9 @@ class Trainer:
         if ckpt.save_snapshot(self.snapshot_path, self.model, next_epoch=epoch + 1, rank=self.global_rank):
             print(f"Epoch {epoch} | Training snapshot saved at {self.snapshot_path}")
 
-    def validate(self, valid_sam, nid2index, news_index=None, device=None, batch: int = 256):
+    def validate(self, valid_sam, nid2index, news_index=None, device=None, batch: int = 256, last_only: bool = False):
         """Mean loss / AUC / MRR / nDCG@5 / nDCG@10 over validation impressions (see ``validate_impressions``)."""
-        return validate_impressions(self.step, self.model, valid_sam, nid2index, batch)
+        return validate_impressions(self.step, self.model, valid_sam, nid2index, batch, last_only)
 
     def train(self, max_epochs: int, valid_sam=None, nid2index=None, news_index=None, device=None,
               dp_enabled: bool = False, sigma: Optional[float] = None):

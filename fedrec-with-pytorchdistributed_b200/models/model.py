@@ -22,6 +22,8 @@ Reference defects that are *not* reproduced: gradient doubling i
 """
 from __future__ import annotations
 
+import time
+
 from typing import Dict, List, Optional, Tuple, Union
 
 import numpy as np
@@ -66,6 +68,7 @@ class UserModel(nn.Module):
         self.news_dataset = news_dataset                          # kept for signature parity (unused upstream too)
         self.criterion = nn.CrossEntropyLoss()
         self.cnt = 0
+        self.time = time.time()                                   # model.py:31 (never read upstream either)
         self.set_news_index(news_index)
         trainable = [(n, p) for n, p in self.named_parameters() if p.requires_grad]
         self.flat = FlatState(trainable, self.device, allocator=flat_allocator)

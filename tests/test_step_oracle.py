@@ -99,6 +99,11 @@ def test_training_moves_metrics(tiny_bert, tiny_data):
     v = tr.validate(tiny_data.train_sam, tiny_data.nid2index)
     assert float(loss) < first - 0.05
     assert v[1] > 0.7, v            # AUC on the training impressions
+    # upstream's return value: mean loss + the LAST sample's metrics rounded to 2 decimals (client.py:171)
+    last = tr.validate(tiny_data.train_sam, tiny_data.nid2index, last_only=True)
+    one = tr.validate(tiny_data.train_sam[-1:], tiny_data.nid2index)
+    assert abs(last[0] - v[0]) < 1e-6
+    assert last[1:] == tuple(round(x, 2) for x in one[1:])
 
 
 def test_train_on_step_api(tiny_bert, tiny_data):
