@@ -48,14 +48,14 @@ struct GemmParams {
 // 128 rows of A and half of the B tile, so the L2 → shared-memory traffic per FLOP drops by a third.
 template <int BN, bool TMA_EPI, int CG>
 struct Cfg {
-  static constexpr int kStages = CG == 2 ? (TMA_EPI ? 4 : 6)
+  static constexpr int kStages = CG == 2 ? (BN == 192 ? (TMA_EPI ? 5 : 7) : (TMA_EPI ? 4 : 6))
                                          : (TMA_EPI ? (BN >= 256 ? 3 : 4) : (BN >= 256 ? 4 : (BN >= 128 ? 6 : 8)));
   static constexpr int kABytes = BM * BK * 2;
   static constexpr int kBBytes = (BN / CG) * BK * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
-  static constexpr int kTmemCols = 2 * BN < 32 ? 32 : 2 * BN;   // BN in {64,128,256} → 128/256/512
-  static constexpr int kColsPerWarp = BN / 4 < 32 ? 32 : BN / 4;       // columns one epilogue warp owns
-  static constexpr int kColGroups = BN / kColsPerWarp;                 // 4 (BN >= 128) or 2 (BN = 64)
+  static constexpr int kTmemCols = BN == 192 ? 512 : (2 * BN < 32 ? 32 : 2 * BN);   // two accumulators, a power of two
+  static constexpr int kColsPerWarp = BN == 192 ? 64 : (BN / 4 < 32 ? 32 : BN / 4);  // columns one epilogue warp owns
+  static constexpr int kColGroups = BN / kColsPerWarp;                 // 4 (BN = 128, 256), 3 (BN = 192) or 2 (BN = 64)
   static constexpr int kBiasBytes = kEpiWarps * kColsPerWarp * 4;      // per-warp bias staging
   static constexpr int kBoxBytes = 4096;                               // per-warp output box: 32 rows x (64|32) bf16
   static constexpr int kStagingBytes = TMA_EPI ? kEpiWarps * kBoxBytes : 0;
@@ -519,7 +519,7 @@ static int sm_count() {
 using namespace fr;
 
 // out = epi(A · W^T + bias).  A [M,K] ld=lda, W [N,K] ld=ldw (both bf16, K-major), out bf16 or fp32 ld=ldo.
-// block_n: 0 = choose, else 64/128/256.  m_dev (optional, device int): effective M = min(M, *m_dev*m_scale).
+// block_n: 0 = choose, else 64/128/192/256 (192: CTA pairs only).  m_dev (optional, device int): effective M = min(M, *m_dev*m_scale).
 static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32,
                           int M, int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n,
                           const int* m_dev, int m_scale, int cta_group, int tma_epilogue, void* stream) {
@@ -537,13 +537,18 @@ static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const
       if (waste < best_waste) { best = bn; best_waste = waste; }
     }
     block_n = best;
+    // N = 768 (attention out-projection, FFN2): 4 x 192 columns quantise into waves better than 3 x 256
+    static const int env_bn768 = [] { const char* e = getenv("FEDREC_GEMM_BN768"); return e ? atoi(e) : 256; }();
+    if (N == 768 && !out_fp32 && M >= 4096 && env_bn768 == 192) block_n = 192;
   }
-  FR_REQUIRE(block_n == 64 || block_n == 128 || block_n == 256, "fr_gemm_bf16: block_n=%d", block_n);
+  FR_REQUIRE(block_n == 64 || block_n == 128 || block_n == 192 || block_n == 256, "fr_gemm_bf16: block_n=%d", block_n);
   // cta_group: 0 = choose. Pairs need the wide tile, a bf16 output and enough rows to fill the GPU with pairs.
   static const int env_cg = [] { const char* e = getenv("FEDREC_GEMM_CTA_GROUP"); return e ? atoi(e) : 0; }();
   if (cta_group == 0) cta_group = env_cg;
-  const bool pair_ok = !out_fp32 && block_n == 256;
-  if (cta_group == 0) cta_group = (pair_ok && M >= 4096) ? 2 : 1;
+  // 192-wide tiles exist for CTA pairs only (N = 768 = 4 x 192: six waves of narrow tiles instead of five of wide ones)
+  if (block_n == 192 && (out_fp32 || cta_group == 1)) block_n = 256;
+  const bool pair_ok = !out_fp32 && (block_n == 256 || block_n == 192);
+  if (cta_group == 0) cta_group = (pair_ok && (M >= 4096 || block_n == 192)) ? 2 : 1;
   if (cta_group == 2 && !pair_ok) cta_group = 1;
   FR_REQUIRE(cta_group == 1 || cta_group == 2, "fr_gemm_bf16: cta_group=%d", cta_group);
   Maps maps;
@@ -553,12 +558,12 @@ static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const
   // For single CTAs the staging boxes cost a pipeline stage, which only pays off when the epilogue dominates (short K).
   static const int env_epi = [] { const char* e = getenv("FEDREC_GEMM_EPI"); return !e ? 0 : (strcmp(e, "direct") == 0 ? -1 : 1); }();
   if (tma_epilogue == 0) tma_epilogue = env_epi;
-  bool tma_epi = !out_fp32 && block_n == 256 && K <= 1536;     // long K: the deeper pipeline wins (measured)
+  bool tma_epi = !out_fp32 && block_n >= 192 && K <= 1536;     // long K: the deeper pipeline wins (measured)
   if (tma_epilogue < 0) tma_epi = false;
-  if (tma_epilogue > 0) tma_epi = !out_fp32 && block_n == 256;
+  if (tma_epilogue > 0) tma_epi = !out_fp32 && block_n >= 192;
   maps.o = maps.a; maps.r = maps.a;
   if (tma_epi) {
-    const int kc = block_n / 4;
+    const int kc = block_n == 192 ? 64 : block_n / 4;
     const CUtensorMapSwizzle swz = kc == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
     if (int e = make_tmap_box_swz(&maps.o, out, M, N, ldo, 32, kc, swz)) return e;
     if (epi == EPI_BIAS_RESID)
@@ -577,6 +582,10 @@ static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const
     }
   }
   if (cta_group == 2) {
+    if (block_n == 192) {
+      if (tma_epi) return dispatch_epi<192, false, true, 2>(epi, maps, p, ctas, s);
+      return dispatch_epi<192, false, false, 2>(epi, maps, p, ctas, s);
+    }
     if (tma_epi) return dispatch_epi<256, false, true, 2>(epi, maps, p, ctas, s);
     return dispatch_epi<256, false, false, 2>(epi, maps, p, ctas, s);
   }

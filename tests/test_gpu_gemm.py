@@ -71,6 +71,15 @@ def test_kernel_variants(cta_group, tma_epilogue, M, N, K, epi):
     _check(M, N, K, epi, block_n=256, cta_group=cta_group, tma_epilogue=tma_epilogue)
 
 
+@pytest.mark.parametrize("tma_epilogue", [-1, 1])
+@pytest.mark.parametrize("M,N,K,epi", [(4500, 768, 768, "resid"), (5000, 768, 3072, "resid"), (4200, 3072, 768, "gelu"),
+                                       (300, 768, 768, "bias"), (4100, 400, 192, "tanh")])
+def test_narrow_pair_tile(tma_epilogue, M, N, K, epi):
+    """192-column tiles on CTA pairs (three of the four epilogue column groups active; N = 400 clips the last tile)."""
+    _check(M, N, K, epi, block_n=192, cta_group=2, tma_epilogue=tma_epilogue)
+    _check(6000, 768, 768, "resid", block_n=192, m_dev=133, m_scale=30, cta_group=2, tma_epilogue=tma_epilogue)
+
+
 @pytest.mark.parametrize("cta_group", [1, 2])
 def test_variants_with_device_side_m(cta_group):
     _check(6000, 768, 768, "resid", block_n=256, m_dev=133, m_scale=30, cta_group=cta_group, tma_epilogue=1)
