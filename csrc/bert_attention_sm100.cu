@@ -72,6 +72,9 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
 
   const int tid = threadIdx.x, warp = tid >> 5;
   const int T = p.T, heads = p.heads;
+  // Launched with the PDL attribute: the CTA may already be resident while the QKV GEMM drains (it cannot share an SM
+  // with a GEMM CTA: shared memory), and from here on that GEMM has completed.
+  griddep_wait();
   const int n_eff = p.count_dev ? min(p.n_items, *p.count_dev) : p.n_items;
   const int num_tiles = (n_eff + TP - 1) / TP;
   const int hd_all = heads * kAttHd;
@@ -303,8 +306,7 @@ FR_API int fr_bert_attention_tc(const void* qkv, const int* mask_table, const in
   }
   long long jobs = (long long)((n_items + TP - 1) / TP) * heads;      // (tile, head) jobs, split evenly over the CTAs
   int grid = jobs < 2 * kNumSMs ? (int)jobs : 2 * kNumSMs;
-  if (slot == 32) bert_attention_tc_kernel<32><<<grid, 128, smem, (cudaStream_t)stream>>>(tm, p);
-  else bert_attention_tc_kernel<64><<<grid, 128, smem, (cudaStream_t)stream>>>(tm, p);
-  FR_LAUNCH_CHECK();
+  if (slot == 32) FR_CHECK(launch_pdl(bert_attention_tc_kernel<32>, dim3(grid), dim3(128), smem, (cudaStream_t)stream, tm, p));
+  else FR_CHECK(launch_pdl(bert_attention_tc_kernel<64>, dim3(grid), dim3(128), smem, (cudaStream_t)stream, tm, p));
   return 0;
 }

@@ -122,7 +122,8 @@ __global__ void __launch_bounds__(512) layernorm_kernel(const __nv_bfloat16* __r
                                                         int rows_max, const int* __restrict__ count_dev, int rows_per_item,
                                                         float eps) {
   const int lane = threadIdx.x & 31;
-  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // a following GEMM may start its prologue
+  pdl_launch();                                      // a following GEMM may start its prologue
+  pdl_wait();                                        // launched with the PDL attribute: the producer has finished from here on
   int rows = rows_max;
   if (count_dev) rows = min(rows_max, *count_dev * rows_per_item);
   const int nwarps = gridDim.x * (blockDim.x >> 5);
@@ -239,63 +240,58 @@ __global__ void __launch_bounds__(kAttnWarps * 32) bert_attention_kernel(
 
 // ---------------------------------------------------------------------------------------------
 // Text-head pooling (forward). e = tanh(h·W1^T + b1) comes from the GEMM (tanh epilogue), bf16 [rows, Hq].
-// One warp per item: a_t = e_t·w2 + b2; alpha = exp(a - m) / (sum exp(a - m) + 1e-8 exp(-m));
-// pooled = sum_t alpha_t h_t  (bf16 [n, 768]); alpha is kept (fp32 [n, T]) for the backward.
+// One block (8 warps) per item, tokens dealt round-robin to the warps so a whole title's rows are in flight at once
+// (one warp per item left ~6 warps per SM and the kernel latency-bound):
+//   a_t = e_t·w2 + b2; alpha = exp(a - m) / (sum exp(a - m) + 1e-8 exp(-m));
+//   pooled = sum_t alpha_t h_t  (bf16 [n, 768]); alpha is kept (fp32 [n, T]) for the backward.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) text_pool_kernel(const __nv_bfloat16* __restrict__ hidden,
+constexpr int kPoolWarps = 8;
+__global__ void __launch_bounds__(kPoolWarps * 32) text_pool_kernel(const __nv_bfloat16* __restrict__ hidden,
                                                         const __nv_bfloat16* __restrict__ e, const float* __restrict__ w2,
                                                         const float* __restrict__ b2, const int* __restrict__ mask_table,
                                                         const int* __restrict__ items, const int* __restrict__ count_dev,
                                                         int n_items, int T, int Hq, __nv_bfloat16* __restrict__ pooled,
                                                         float* __restrict__ alpha_out) {
-  __shared__ float sA[4][kMaxT];
+  __shared__ float sA[kMaxT];
+  __shared__ __align__(16) float sPart[kPoolWarps][kHid];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_wait();
+  pdl_launch();
   const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
-  for (int n = blockIdx.x * 4 + w; n < n_eff; n += gridDim.x * 4) {
+  for (int n = blockIdx.x; n < n_eff; n += gridDim.x) {
     const size_t row0 = (size_t)n * T;
     const int item = items ? items[n] : n;
-    // logits a_t = e_t · w2 + b2, four rows per pass: 8 lanes share a row (16-byte loads), 3 shuffle steps per row
-    float mx = -INFINITY;
-    const int sub = lane & 7, rgrp = lane >> 3;
-    for (int t0 = 0; t0 < T; t0 += 4) {
-      const int t = t0 + rgrp;
+    // logits a_t = e_t · w2 + b2
+    for (int t = w; t < T; t += kPoolWarps) {
       float s = 0.f;
-      if (t < T) {
-        for (int c = sub * 8; c < Hq; c += 64) {
-          float ev[8];
-          load8(e + (row0 + t) * Hq + c, ev);
+      for (int c = lane * 8; c < Hq; c += 256) {
+        float ev[8];
+        load8(e + (row0 + t) * Hq + c, ev);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) s = fmaf(ev[i], w2[c + i], s);
-        }
+        for (int i = 0; i < 8; ++i) s = fmaf(ev[i], w2[c + i], s);
       }
-      s += __shfl_xor_sync(0xffffffffu, s, 4);
-      s += __shfl_xor_sync(0xffffffffu, s, 2);
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      s += b2[0];
-      if (t < T) {
-        if (sub == 0) sA[w][t] = s;
-        mx = fmaxf(mx, s);
-      }
+      s = warp_sum(s);
+      if (lane == 0) sA[t] = s + b2[0];
     }
-    mx = warp_max(mx);
-    __syncwarp();
-    float z = 0.f;
-    for (int t = lane; t < T; t += 32) {
-      const float mk = (mask_table && mask_table[(size_t)item * T + t] == 0) ? 0.f : 1.f;
-      const float ex = __expf(sA[w][t] - mx) * mk;
-      sA[w][t] = ex;
-      z += ex;
+    __syncthreads();
+    // every warp normalises redundantly: lane holds tokens lane and lane + 32 (T <= 64)
+    const int t0 = lane, t1 = lane + 32;
+    const float v0 = t0 < T ? sA[t0] : -INFINITY, v1 = t1 < T ? sA[t1] : -INFINITY;
+    const float mx = warp_max(fmaxf(v0, v1));
+    const float mk0 = (t0 < T && !(mask_table && mask_table[(size_t)item * T + t0] == 0)) ? 1.f : 0.f;
+    const float mk1 = (t1 < T && !(mask_table && mask_table[(size_t)item * T + t1] == 0)) ? 1.f : 0.f;
+    const float ex0 = t0 < T ? __expf(v0 - mx) * mk0 : 0.f, ex1 = t1 < T ? __expf(v1 - mx) * mk1 : 0.f;
+    const float invz = 1.f / (warp_sum(ex0 + ex1) + 1e-8f * __expf(-mx));
+    const float a0 = ex0 * invz, a1 = ex1 * invz;
+    if (w == 0 && alpha_out) {
+      if (t0 < T) alpha_out[row0 + t0] = a0;
+      if (t1 < T) alpha_out[row0 + t1] = a1;
     }
-    z = warp_sum(z) + 1e-8f * __expf(-mx);
-    __syncwarp();
-    const float invz = 1.f / z;
     float acc[kPerLane];
 #pragma unroll
     for (int i = 0; i < kPerLane; ++i) acc[i] = 0.f;
-#pragma unroll 4
-    for (int t = 0; t < T; ++t) {
-      const float a = sA[w][t] * invz;
-      if (lane == 0 && alpha_out) alpha_out[row0 + t] = a;
+    for (int t = w; t < T; t += kPoolWarps) {
+      const float a = __shfl_sync(0xffffffffu, t < 32 ? a0 : a1, t & 31);
       float hv[8];
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -305,8 +301,25 @@ __global__ void __launch_bounds__(128) text_pool_kernel(const __nv_bfloat16* __r
       }
     }
 #pragma unroll
-    for (int c = 0; c < 3; ++c) store8(pooled + (size_t)n * kHid + c * 256 + lane * 8, acc + c * 8);
-    __syncwarp();
+    for (int c = 0; c < 3; ++c) {
+      float4* dst = reinterpret_cast<float4*>(&sPart[w][c * 256 + lane * 8]);
+      dst[0] = make_float4(acc[c * 8], acc[c * 8 + 1], acc[c * 8 + 2], acc[c * 8 + 3]);
+      dst[1] = make_float4(acc[c * 8 + 4], acc[c * 8 + 5], acc[c * 8 + 6], acc[c * 8 + 7]);
+    }
+    __syncthreads();
+    if (threadIdx.x < kHid / 8) {
+      float o[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) o[i] = 0.f;
+#pragma unroll
+      for (int k = 0; k < kPoolWarps; ++k) {
+        const float4* src = reinterpret_cast<const float4*>(&sPart[k][threadIdx.x * 8]);
+        const float4 x = src[0], y = src[1];
+        o[0] += x.x; o[1] += x.y; o[2] += x.z; o[3] += x.w; o[4] += y.x; o[5] += y.y; o[6] += y.z; o[7] += y.w;
+      }
+      store8(pooled + (size_t)n * kHid + threadIdx.x * 8, o);
+    }
+    __syncthreads();                       // sA / sPart are reused by the next item
   }
 }
 
@@ -318,24 +331,32 @@ __global__ void __launch_bounds__(128) text_pool_kernel(const __nv_bfloat16* __r
 // [count*T, round_up(count*T, 64)) are zeroed: the weight-gradient GEMM reduces over whole 64-row blocks.
 // ---------------------------------------------------------------------------------------------
 constexpr int kMaxHq = 512;
-// stage 1, one warp per item: da[n*T + t] (fp32) and d_b2 += sum da
-__global__ void __launch_bounds__(128) text_pool_bwd_kernel(const __nv_bfloat16* __restrict__ hidden,
+// One block (8 warps) per item, tokens dealt round-robin to the warps:
+//   da[n*T + t] (fp32), d_b2 += sum da, then d_pre[r, c] = da[r] * w2[c] * (1 - e[r,c]^2) (bf16, the weight-gradient GEMM
+//   operand) for the item's T rows. Block 0 also writes zeros to the rows in [rows_eff, round_up(rows_eff, 64)).
+// The two column reductions that need every row (d_w2 = e^T·da, d_b1 = colsum(d_pre)) are separate launches
+// (colsum kernels in user_encoder.cu), so the training step can take them off its critical path.
+__global__ void __launch_bounds__(kPoolWarps * 32) text_pool_bwd_kernel(const __nv_bfloat16* __restrict__ hidden,
+                                                            const __nv_bfloat16* __restrict__ e,
                                                             const float* __restrict__ alpha,
                                                             const __nv_bfloat16* __restrict__ d_pooled,
-                                                            const int* __restrict__ count_dev, int n_items, int T,
-                                                            float* __restrict__ da_out, float* __restrict__ d_b2) {
-  __shared__ float sDa[4][kMaxT];
+                                                            const float* __restrict__ w2,
+                                                            const int* __restrict__ count_dev, int n_items, int T, int Hq,
+                                                            float* __restrict__ da_out, __nv_bfloat16* __restrict__ d_pre,
+                                                            float* __restrict__ d_b2) {
+  __shared__ float sS[kMaxT], sDa[kMaxT];
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  pdl_wait();
+  pdl_launch();
   const int n_eff = count_dev ? min(n_items, *count_dev) : n_items;
+  const int hq8 = Hq >> 3;
   float db2 = 0.f;
-  for (int n = blockIdx.x * 4 + w; n < n_eff; n += gridDim.x * 4) {
+  for (int n = blockIdx.x; n < n_eff; n += gridDim.x) {
     const size_t row0 = (size_t)n * T;
     float dp[kPerLane];
 #pragma unroll
     for (int c = 0; c < 3; ++c) load8(d_pooled + (size_t)n * kHid + c * 256 + lane * 8, dp + c * 8);
-    float dot = 0.f;
-#pragma unroll 2
-    for (int t = 0; t < T; ++t) {
+    for (int t = w; t < T; t += kPoolWarps) {
       float hv[8], s = 0.f;
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
@@ -344,76 +365,44 @@ __global__ void __launch_bounds__(128) text_pool_bwd_kernel(const __nv_bfloat16*
         for (int i = 0; i < 8; ++i) s = fmaf(dp[c * 8 + i], hv[i], s);
       }
       s = warp_sum(s);
-      if (lane == 0) sDa[w][t] = s;
-      dot = fmaf(alpha[row0 + t], s, dot);
+      if (lane == 0) sS[t] = s;
     }
-    __syncwarp();
-    for (int t = lane; t < T; t += 32) {
-      const float da = alpha[row0 + t] * (sDa[w][t] - dot);
-      da_out[row0 + t] = da;
-      db2 += da;
+    __syncthreads();
+    if (w == 0) {
+      const int t0 = lane, t1 = lane + 32;
+      const float a0 = t0 < T ? alpha[row0 + t0] : 0.f, a1 = t1 < T ? alpha[row0 + t1] : 0.f;
+      const float s0 = t0 < T ? sS[t0] : 0.f, s1 = t1 < T ? sS[t1] : 0.f;
+      const float dot = warp_sum(fmaf(a0, s0, a1 * s1));
+      const float da0 = a0 * (s0 - dot), da1 = a1 * (s1 - dot);
+      if (t0 < T) { da_out[row0 + t0] = da0; sDa[t0] = da0; }
+      if (t1 < T) { da_out[row0 + t1] = da1; sDa[t1] = da1; }
+      db2 += da0 + da1;
     }
-    __syncwarp();
+    __syncthreads();
+    for (int i = threadIdx.x; i < T * hq8; i += kPoolWarps * 32) {
+      const int t = i / hq8, c = (i - t * hq8) * 8;
+      float ev[8], out[8];
+      load8(e + (row0 + t) * Hq + c, ev);
+      const float d = sDa[t];
+      const float4 wa = *reinterpret_cast<const float4*>(w2 + c), wb = *reinterpret_cast<const float4*>(w2 + c + 4);
+      const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) out[k] = d * wv[k] * (1.f - ev[k] * ev[k]);
+      store8(d_pre + (row0 + t) * Hq + c, out);
+    }
+    __syncthreads();                       // sS / sDa are reused by the next item
   }
-  db2 = warp_sum(db2);
-  if (lane == 0 && db2 != 0.f) atomicAdd(d_b2, db2);
-}
-
-// stage 2, streaming over the rows: d_pre[r, c] = da[r] * w2[c] * (1 - e[r,c]^2) (bf16, the weight-gradient GEMM operand),
-// d_w2[c] += sum_r da[r] e[r,c], d_b1[c] += sum_r d_pre[r,c]. A thread owns 8 consecutive columns; a block owns a
-// contiguous range of rows. Rows in [rows_eff, round_up(rows_eff, 64)) are written as zeros.
-constexpr int kDpreRowLanes = 5;
-__global__ void __launch_bounds__(kDpreRowLanes * 64) text_dpre_kernel(const __nv_bfloat16* __restrict__ e,
-                                                                        const float* __restrict__ da,
-                                                                        const float* __restrict__ w2,
-                                                                        const int* __restrict__ count_dev, int rows_max,
-                                                                        int rows_per_item, int Hq, int rows_per_block,
-                                                                        __nv_bfloat16* __restrict__ d_pre,
-                                                                        float* __restrict__ d_w2, float* __restrict__ d_b1) {
-  __shared__ float sW2[kDpreRowLanes][64][8];
-  __shared__ float sB1[kDpreRowLanes][64][8];
-  const int cq = threadIdx.x & 63;                    // column chunk (8 columns)
-  const int rl = threadIdx.x >> 6;                    // row lane
-  const int rows_eff = count_dev ? min(rows_max, *count_dev * rows_per_item) : rows_max;
-  const int rows_pad = min(rows_max, (rows_eff + 63) / 64 * 64);
-  const int r0 = blockIdx.x * rows_per_block, r1 = min(rows_pad, r0 + rows_per_block);
-  const bool col_ok = cq * 8 < Hq;
-  float wv[8], aw[8], ab[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) { wv[i] = col_ok ? w2[cq * 8 + i] : 0.f; aw[i] = 0.f; ab[i] = 0.f; }
-  if (col_ok) {
-#pragma unroll 4
-    for (int r = r0 + rl; r < r1; r += kDpreRowLanes) {
-      float out[8];
-      if (r < rows_eff) {
-        float ev[8];
-        load8(e + (size_t)r * Hq + cq * 8, ev);
-        const float d = da[r];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          out[i] = d * wv[i] * (1.f - ev[i] * ev[i]);
-          aw[i] = fmaf(d, ev[i], aw[i]);
-          ab[i] += out[i];
-        }
-      } else {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) out[i] = 0.f;
-      }
-      store8(d_pre + (size_t)r * Hq + cq * 8, out);
-    }
+  if (w == 0) {
+    db2 = warp_sum(db2);
+    if (lane == 0 && db2 != 0.f) atomicAdd(d_b2, db2);
   }
-#pragma unroll
-  for (int i = 0; i < 8; ++i) { sW2[rl][cq][i] = aw[i]; sB1[rl][cq][i] = ab[i]; }
-  __syncthreads();
-  if (rl == 0 && col_ok) {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      float a = 0.f, b = 0.f;
-#pragma unroll
-      for (int k = 0; k < kDpreRowLanes; ++k) { a += sW2[k][cq][i]; b += sB1[k][cq][i]; }
-      if (a != 0.f) atomicAdd(d_w2 + cq * 8 + i, a);
-      if (b != 0.f) atomicAdd(d_b1 + cq * 8 + i, b);
-    }
+  if (blockIdx.x == 0) {
+    const long long rows_max = (long long)n_items * T, rows_eff = (long long)n_eff * T;
+    long long rows_pad = (rows_eff + 63) / 64 * 64;
+    if (rows_pad > rows_max) rows_pad = rows_max;
+    const float z[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (long long i = threadIdx.x; i < (rows_pad - rows_eff) * hq8; i += kPoolWarps * 32)
+      store8(d_pre + rows_eff * Hq + i * 8, z);
   }
 }
 
@@ -454,6 +443,8 @@ __global__ void __launch_bounds__(256) rows_copy_kernel(const uint4* __restrict_
 
 // fp32 → bf16 cast of a contiguous buffer (weight packing, activations entering a GEMM)
 __global__ void __launch_bounds__(256) cast_bf16_kernel(const float4* __restrict__ in, uint2* __restrict__ out, size_t n4) {
+  pdl_wait();
+  pdl_launch();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const float4 v = in[i];
     uint2 q;
@@ -492,9 +483,8 @@ FR_API int fr_layernorm_bf16(const void* in, void* out, const float* gamma, cons
   if (rows == 0) return 0;
   // 117 registers x 512 threads = one block per SM: exactly one wave of blocks, so gamma/beta are loaded once per SM and
   // no block waits for another to retire (measured: +0.8% step throughput over a 3x oversubscribed grid).
-  layernorm_kernel<<<grid_for(rows, 32, kNumSMs), 512, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)in, (__nv_bfloat16*)out, gamma, beta, rows, count_dev, rows_per_item, eps);
-  FR_LAUNCH_CHECK();
+  FR_CHECK(launch_pdl(layernorm_kernel, dim3(grid_for(rows, 32, kNumSMs)), dim3(512), 0, (cudaStream_t)stream,
+                      (const __nv_bfloat16*)in, (__nv_bfloat16*)out, gamma, beta, rows, count_dev, rows_per_item, eps));
   return 0;
 }
 
@@ -516,27 +506,35 @@ FR_API int fr_text_pool(const void* hidden, const void* e, const float* w2, cons
   FR_REQUIRE(hidden_dim == kHid, "fr_text_pool: hidden=%d (only %d is built)", hidden_dim, kHid);
   FR_REQUIRE(T >= 1 && T <= kMaxT && Hq % 8 == 0, "fr_text_pool: T=%d Hq=%d (Hq must be a multiple of 8)", T, Hq);
   if (n_items == 0) return 0;
-  text_pool_kernel<<<grid_for(n_items, 4, kNumSMs * 8), 128, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)hidden, (const __nv_bfloat16*)e, w2, b2, mask_table, items, count_dev, n_items, T, Hq,
-      (__nv_bfloat16*)pooled, alpha_out);
-  FR_LAUNCH_CHECK();
+  FR_CHECK(launch_pdl(text_pool_kernel, dim3(n_items < kNumSMs * 8 ? n_items : kNumSMs * 8), dim3(kPoolWarps * 32), 0,
+                      (cudaStream_t)stream, (const __nv_bfloat16*)hidden, (const __nv_bfloat16*)e, w2, b2, mask_table, items,
+                      count_dev, n_items, T, Hq, (__nv_bfloat16*)pooled, alpha_out));
   return 0;
 }
 
+namespace fr {
+int colsum_launch(const void* X, int is_bf16, const float* row_w, float* out, int M, int N, int ld, const int* m_dev,
+                  int m_scale, cudaStream_t s);   // user_encoder.cu
+}
+
+// d_w2 / d_b1 may both be null: the caller then runs the two column reductions itself (fr_colsum on d_pre for d_b1,
+// fr_colsum_weighted(e, da) for d_w2), e.g. on another stream.
 FR_API int fr_text_pool_bwd(const void* hidden, const void* e, const float* alpha, const void* d_pooled, const float* w2,
                             const int* count_dev, int n_items, int T, int Hq, int hidden_dim, void* d_pre, float* da_scratch,
                             float* d_w2, float* d_b2, float* d_b1, void* stream) {
   FR_REQUIRE(hidden_dim == kHid, "fr_text_pool_bwd: hidden=%d (only %d is built)", hidden_dim, kHid);
   FR_REQUIRE(T >= 1 && T <= kMaxT && Hq >= 8 && Hq <= kMaxHq && Hq % 8 == 0, "fr_text_pool_bwd: T=%d Hq=%d", T, Hq);
+  FR_REQUIRE(((uintptr_t)w2 & 15) == 0, "fr_text_pool_bwd: w2 must be 16-byte aligned");
   if (n_items == 0) return 0;
   cudaStream_t s = (cudaStream_t)stream;
-  text_pool_bwd_kernel<<<grid_for(n_items, 4, kNumSMs * 8), 128, 0, s>>>(
-      (const __nv_bfloat16*)hidden, alpha, (const __nv_bfloat16*)d_pooled, count_dev, n_items, T, da_scratch, d_b2);
+  FR_CHECK(launch_pdl(text_pool_bwd_kernel, dim3(n_items < kNumSMs * 8 ? n_items : kNumSMs * 8), dim3(kPoolWarps * 32), 0, s,
+                      (const __nv_bfloat16*)hidden, (const __nv_bfloat16*)e, alpha, (const __nv_bfloat16*)d_pooled, w2, count_dev,
+                      n_items, T, Hq, da_scratch, (__nv_bfloat16*)d_pre, d_b2));
   const int rows = n_items * T;
-  const int rows_per_block = 160;
-  text_dpre_kernel<<<(rows + rows_per_block - 1) / rows_per_block, kDpreRowLanes * 64, 0, s>>>(
-      (const __nv_bfloat16*)e, da_scratch, w2, count_dev, rows, T, Hq, rows_per_block, (__nv_bfloat16*)d_pre, d_w2, d_b1);
-  FR_LAUNCH_CHECK();
+  if (d_w2)
+    if (int err = colsum_launch(e, 1, da_scratch, d_w2, rows, Hq, Hq, count_dev, T, s)) return err;
+  if (d_b1)
+    if (int err = colsum_launch(d_pre, 1, nullptr, d_b1, rows, Hq, Hq, count_dev, T, s)) return err;
   return 0;
 }
 
@@ -570,7 +568,6 @@ FR_API int fr_cast_f32_to_bf16(const float* in, void* out, long long n, void* st
   const size_t n4 = (size_t)n / 4;
   int blocks = (int)((n4 + 255) / 256);
   if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;
-  cast_bf16_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((const float4*)in, (uint2*)out, n4);
-  FR_LAUNCH_CHECK();
+  FR_CHECK(launch_pdl(cast_bf16_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, (const float4*)in, (uint2*)out, n4));
   return 0;
 }

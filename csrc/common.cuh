@@ -37,6 +37,32 @@ void set_error(const char* fmt, ...);
 
 constexpr int kNumSMs = 148;
 
+// ---- programmatic dependent launch (PDL) --------------------------------------------------------------------------
+// A kernel launched through launch_pdl may become resident while the previous kernel of the stream is still draining;
+// it MUST call pdl_wait() before its first global-memory access (the wait returns once the previous grid has completed
+// and its writes are visible; it is a no-op for a plain launch). Every kernel of such a chain waits, so ordering stays
+// transitive. pdl_launch() lets the next kernel of the stream start its own launch early. FEDREC_PDL=0 turns the
+// attribute off (plain stream order).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_enabled();   // runtime.cu
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

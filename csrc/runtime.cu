@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include <stdarg.h>
 #include <string.h>
+#include <stdlib.h>
 
 namespace fr {
 static thread_local char g_err[1024] = "";
@@ -10,6 +11,10 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("FEDREC_PDL"); return !(e && atoi(e) == 0); }();
+  return on;
 }
 }  // namespace fr
 

@@ -38,6 +38,8 @@ __global__ void __launch_bounds__(256) ue_gather_dropout_kernel(const float* __r
                                                                 __nv_bfloat16* __restrict__ X, int rows, int D4, float p,
                                                                 unsigned long long seed,
                                                                 const unsigned long long* __restrict__ seed_dev) {
+  pdl_wait();      // may have been launched early (PDL): the producer has finished from here on
+  pdl_launch();
   if (seed_dev) seed += *seed_dev;            // per-replay salt when the step lives in a CUDA graph
   const Philox rng(seed);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
@@ -62,6 +64,8 @@ __global__ void __launch_bounds__(256) ue_scatter_dx_kernel(const float* __restr
                                                             unsigned long long seed, float noise_std,
                                                             unsigned long long noise_seed,
                                                             const unsigned long long* __restrict__ seed_dev) {
+  pdl_wait();      // may have been launched early (PDL): the producer has finished from here on
+  pdl_launch();
   if (seed_dev) { seed += *seed_dev; noise_seed += *seed_dev; }
   const Philox rng(seed), nrng(noise_seed);
   const float inv_keep = p > 0.f ? 1.f / (1.f - p) : 1.f;
@@ -91,6 +95,8 @@ template <int DK>
 __global__ void __launch_bounds__(kJobThreads) ue_mha_fwd_kernel(const __nv_bfloat16* __restrict__ qkv, const int* __restrict__ his_ids,
                                                                  __nv_bfloat16* __restrict__ ctx, float* __restrict__ stats,
                                                                  int B, int L, int H, float scale, int use_mask) {
+  pdl_wait();      // may have been launched early (PDL): the producer has finished from here on
+  pdl_launch();
   __shared__ float sK[kMaxL][DK + 1];
   __shared__ float sV[kMaxL][DK + 1];
   __shared__ float sM[kMaxL];
@@ -164,80 +170,127 @@ __device__ __forceinline__ void axpy_row(float* reg, float a, const float* srow)
   }
 }
 
+// One (user, head) job per block of 128 threads: thread (r, hf) = (tid & 63, tid >> 6) owns row r and one half of the
+// work of that row, so four warps share a job and nothing is computed twice:
+//   A  (r = query i, hf = half of the keys j): P_ij = exp(s_ij - m_i) mask_j / z_i and dP_ij = dctx_i · v_j → shared
+//      memory; partial Dd_i = sum_j P_ij dP_ij
+//   B1 (same split): dS_ij = P_ij (dP_ij - Dd_i), overwriting dP
+//   B2 (r = query i, hf = half of the head dims): dQ_i = scale * sum_j dS_ij K_j
+//   C  (r = key j,   hf = half of the head dims): dV_j = sum_i P_ij dctx_i ; dK_j = sum_i dS_ij (q_i * scale)
+// P and dS rows have an odd stride, so row-wise (thread = i) and column-wise (thread = j) accesses are conflict-free.
+constexpr int kBwdThreads = 128;
 template <int DK>
-__global__ void __launch_bounds__(kJobThreads) ue_mha_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dctx,
+__global__ void __launch_bounds__(kBwdThreads) ue_mha_bwd_kernel(const __nv_bfloat16* __restrict__ qkv, const __nv_bfloat16* __restrict__ dctx,
                                                                  const float* __restrict__ stats, const int* __restrict__ his_ids,
                                                                  __nv_bfloat16* __restrict__ dqkv, int B, int L, int H, float scale,
                                                                  int use_mask) {
+  pdl_wait();      // may have been launched early (PDL): the producer has finished from here on
+  pdl_launch();
   constexpr int DKP = (DK + 3) / 4 * 4;            // rows padded to 16 bytes: the hot loops read them as float4 broadcasts
-  __shared__ __align__(16) float sQ[kMaxL][DKP];   // q * scale
-  __shared__ __align__(16) float sK[kMaxL][DKP];
-  __shared__ __align__(16) float sV[kMaxL][DKP];
-  __shared__ __align__(16) float sG[kMaxL][DKP];   // dctx
-  __shared__ float sMx[kMaxL], sZ[kMaxL], sDd[kMaxL], sMask[kMaxL];
+  constexpr int DH = DK / 2;                       // head dims per thread in B2 / C
+  static_assert(DK % 4 == 0 && DH % 2 == 0, "head dim must be a multiple of 4");
+  extern __shared__ __align__(16) float smem_f[];
+  const int LP = L | 1;
+  float* sQ = smem_f;                              // [L][DKP] q * scale
+  float* sK = sQ + L * DKP;
+  float* sV = sK + L * DKP;
+  float* sG = sV + L * DKP;                        // dctx
+  float* sP = sG + L * DKP;                        // [L][LP]
+  float* sDS = sP + L * LP;                        // [L][LP] dP, then dS
+  float* sMx = sDS + L * LP;
+  float* sZ = sMx + L;
+  float* sMask = sZ + L;
+  float* sDd = sMask + L;                          // [2][L] partial Dd of the two key halves
   const int tid = threadIdx.x;
+  const int r = tid & 63, hf = tid >> 6;
   const int job = blockIdx.x;
   const int b = job / H, h = job - b * H;
   const int ld = 3 * H * DK;
   const size_t row0 = (size_t)b * L;
-  for (int i = tid; i < L * DKP; i += kJobThreads) {
-    const int r = i / DKP, d = i - r * DKP;
+  for (int i = tid; i < L * DKP; i += kBwdThreads) {
+    const int rr = i / DKP, d = i - rr * DKP;
     float q = 0.f, k = 0.f, v = 0.f, g = 0.f;
     if (d < DK) {
-      const __nv_bfloat16* base = qkv + (row0 + r) * ld + h * DK + d;
+      const __nv_bfloat16* base = qkv + (row0 + rr) * ld + h * DK + d;
       q = __bfloat162float(base[0]) * scale;
       k = __bfloat162float(base[H * DK]);
       v = __bfloat162float(base[2 * H * DK]);
-      g = __bfloat162float(dctx[(row0 + r) * (size_t)(H * DK) + h * DK + d]);
+      g = __bfloat162float(dctx[(row0 + rr) * (size_t)(H * DK) + h * DK + d]);
     }
-    sQ[r][d] = q; sK[r][d] = k; sV[r][d] = v; sG[r][d] = g;
+    sQ[i] = q; sK[i] = k; sV[i] = v; sG[i] = g;
   }
-  for (int j = tid; j < L; j += kJobThreads) {
+  for (int j = tid; j < L; j += kBwdThreads) {
     sMx[j] = stats[((size_t)job * L + j) * 2];
     sZ[j] = stats[((size_t)job * L + j) * 2 + 1];
     sMask[j] = (use_mask && his_ids[row0 + j] == 0) ? 0.f : 1.f;
   }
   __syncthreads();
-  // pass 1 (thread = query i): Dd_i = sum_j P_ij dP_ij, then dQ_i = scale * sum_j dS_ij K_j
-  for (int i = tid; i < L; i += kJobThreads) {
+  const int jh = (L + 1) / 2;
+  const int j0 = hf * jh, j1 = min(L, j0 + jh);
+  // ---- A ----
+  if (r < L) {
     float q[DKP], g[DKP];
 #pragma unroll
-    for (int d = 0; d < DKP; ++d) { q[d] = sQ[i][d]; g[d] = sG[i][d]; }
-    const float m = sMx[i], invz = 1.f / sZ[i];
+    for (int d = 0; d < DKP; ++d) { q[d] = sQ[r * DKP + d]; g[d] = sG[r * DKP + d]; }
+    const float m = sMx[r], invz = 1.f / sZ[r];
     float dd = 0.f;
-    for (int j = 0; j < L; ++j) {
-      const float s = dot_row<DKP>(q, sK[j]), dp = dot_row<DKP>(g, sV[j]);
-      dd = fmaf(__expf(s - m) * sMask[j] * invz, dp, dd);
+    for (int j = j0; j < j1; ++j) {
+      const float sc = dot_row<DKP>(q, sK + j * DKP), dp = dot_row<DKP>(g, sV + j * DKP);
+      const float pij = __expf(sc - m) * sMask[j] * invz;
+      sP[r * LP + j] = pij;
+      sDS[r * LP + j] = dp;
+      dd = fmaf(pij, dp, dd);
     }
-    sDd[i] = dd;
-    float dq[DKP];
-#pragma unroll
-    for (int d = 0; d < DKP; ++d) dq[d] = 0.f;
-    for (int j = 0; j < L; ++j) {
-      const float s = dot_row<DKP>(q, sK[j]), dp = dot_row<DKP>(g, sV[j]);
-      axpy_row<DKP>(dq, __expf(s - m) * sMask[j] * invz * (dp - dd), sK[j]);
-    }
-    __nv_bfloat16* op = dqkv + (row0 + i) * ld + h * DK;
-#pragma unroll
-    for (int d = 0; d < DK; d += 2)
-      *reinterpret_cast<__nv_bfloat162*>(op + d) = __floats2bfloat162_rn(dq[d] * scale, dq[d + 1] * scale);
+    sDd[hf * L + r] = dd;
   }
   __syncthreads();
-  // pass 2 (thread = key j): dV_j = sum_i P_ij dctx_i ; dK_j = sum_i dS_ij (q_i * scale)
-  for (int j = tid; j < L; j += kJobThreads) {
-    float kj[DKP], vj[DKP], dk[DKP], dv[DKP];
+  // ---- B1 ----
+  if (r < L) {
+    const float dd = sDd[r] + sDd[L + r];
+    for (int j = j0; j < j1; ++j) sDS[r * LP + j] = sP[r * LP + j] * (sDS[r * LP + j] - dd);
+  }
+  __syncthreads();
+  // ---- B2 ----
+  if (r < L) {
+    float dq[DH];
 #pragma unroll
-    for (int d = 0; d < DKP; ++d) { kj[d] = sK[j][d]; vj[d] = sV[j][d]; dk[d] = 0.f; dv[d] = 0.f; }
-    const float mk = sMask[j];
-    for (int i = 0; i < L; ++i) {
-      const float s = dot_row<DKP>(kj, sQ[i]), dp = dot_row<DKP>(vj, sG[i]);
-      const float pij = __expf(s - sMx[i]) * mk / sZ[i];
-      axpy_row<DKP>(dv, pij, sG[i]);
-      axpy_row<DKP>(dk, pij * (dp - sDd[i]), sQ[i]);   // sQ already carries the 1/sqrt(dk) factor
+    for (int d = 0; d < DH; ++d) dq[d] = 0.f;
+    for (int j = 0; j < L; ++j) {
+      const float ds = sDS[r * LP + j];
+      const float* kr = sK + j * DKP + hf * DH;
+#pragma unroll
+      for (int d = 0; d < DH; d += 2) {
+        const float2 k2 = *reinterpret_cast<const float2*>(kr + d);
+        dq[d] = fmaf(ds, k2.x, dq[d]);
+        dq[d + 1] = fmaf(ds, k2.y, dq[d + 1]);
+      }
     }
-    __nv_bfloat16* op = dqkv + (row0 + j) * ld + h * DK;
+    __nv_bfloat16* op = dqkv + (row0 + r) * ld + h * DK + hf * DH;
 #pragma unroll
-    for (int d = 0; d < DK; d += 2) {
+    for (int d = 0; d < DH; d += 2)
+      *reinterpret_cast<__nv_bfloat162*>(op + d) = __floats2bfloat162_rn(dq[d] * scale, dq[d + 1] * scale);
+  }
+  // ---- C ---- (reads only what A / B1 wrote: no barrier needed after B2)
+  if (r < L) {
+    float dk[DH], dv[DH];
+#pragma unroll
+    for (int d = 0; d < DH; ++d) { dk[d] = 0.f; dv[d] = 0.f; }
+    for (int i = 0; i < L; ++i) {
+      const float pij = sP[i * LP + r], ds = sDS[i * LP + r];
+      const float* gr = sG + i * DKP + hf * DH;
+      const float* qr = sQ + i * DKP + hf * DH;
+#pragma unroll
+      for (int d = 0; d < DH; d += 2) {
+        const float2 g2 = *reinterpret_cast<const float2*>(gr + d), q2 = *reinterpret_cast<const float2*>(qr + d);
+        dv[d] = fmaf(pij, g2.x, dv[d]);
+        dv[d + 1] = fmaf(pij, g2.y, dv[d + 1]);
+        dk[d] = fmaf(ds, q2.x, dk[d]);                  // sQ already carries the 1/sqrt(dk) factor
+        dk[d + 1] = fmaf(ds, q2.y, dk[d + 1]);
+      }
+    }
+    __nv_bfloat16* op = dqkv + (row0 + r) * ld + h * DK + hf * DH;
+#pragma unroll
+    for (int d = 0; d < DH; d += 2) {
       *reinterpret_cast<__nv_bfloat162*>(op + H * DK + d) = __floats2bfloat162_rn(dk[d], dk[d + 1]);
       *reinterpret_cast<__nv_bfloat162*>(op + 2 * H * DK + d) = __floats2bfloat162_rn(dv[d], dv[d + 1]);
     }
@@ -273,6 +326,8 @@ struct PoolScoreArgs {
 };
 
 __global__ void __launch_bounds__(kPoolThreads) ue_pool_score_kernel(const PoolScoreArgs a) {
+  pdl_wait();      // may have been launched early (PDL): the producer has finished from here on
+  pdl_launch();
   __shared__ float sA[kMaxL];          // logits → exp → alpha
   __shared__ float sU[512];            // user vector, later d_u
   __shared__ float sS[32];             // candidate logits / ds
@@ -399,10 +454,12 @@ __global__ void __launch_bounds__(kPoolThreads) ue_pool_score_kernel(const PoolS
   }
 }
 
-// out[n] += sum_m X[m, n]   (bias gradients). X [M, N] with leading dimension ld; rows limited by *m_dev * m_scale.
+// out[n] += sum_m w[m] X[m, n]   (w = 1 if row_w is null: bias gradients; with weights: a transposed GEMV).
+// X [M, N] with leading dimension ld; rows limited by *m_dev * m_scale.
 // A thread owns 8 (bf16) or 4 (fp32) consecutive columns = one 16-byte load per row; 8 row lanes per block.
 template <typename T, int VEC>
-__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ X, float* __restrict__ out, int M, int N, int ld,
+__global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ X, const float* __restrict__ row_w,
+                                                     float* __restrict__ out, int M, int N, int ld,
                                                      const int* __restrict__ m_dev, int m_scale) {
   if (m_dev) M = min(M, *m_dev * m_scale);
   const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
@@ -412,20 +469,33 @@ __global__ void __launch_bounds__(256) colsum_kernel(const T* __restrict__ X, fl
 #pragma unroll
   for (int i = 0; i < VEC; ++i) acc[i] = 0.f;
   if (col < N) {
-    for (int r = blockIdx.y * 8 + rl; r < M; r += gridDim.y * 8) {
-      const uint4 q = *reinterpret_cast<const uint4*>(X + (size_t)r * ld + col);
-      if (VEC == 8) {
-        const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q);
+    // four rows in flight per thread: the loop is a chain of dependent-free 16-byte loads, so latency is what costs
+    const int rstep = gridDim.y * 8;
+    for (int r = blockIdx.y * 8 + rl; r < M; r += 4 * rstep) {
+      uint4 q[4];
+      float wr[4];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const float2 f = __bfloat1622float2(h[i]);
-          acc[2 * i] += f.x;
-          acc[2 * i + 1] += f.y;
+      for (int u = 0; u < 4; ++u) {
+        const int ru = r + u * rstep;
+        const bool ok = ru < M;
+        q[u] = ok ? *reinterpret_cast<const uint4*>(X + (size_t)ru * ld + col) : make_uint4(0, 0, 0, 0);
+        wr[u] = ok ? (row_w ? row_w[ru] : 1.f) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (VEC == 8) {
+          const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&q[u]);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float2 f = __bfloat1622float2(h[i]);
+            acc[2 * i] = fmaf(wr[u], f.x, acc[2 * i]);
+            acc[2 * i + 1] = fmaf(wr[u], f.y, acc[2 * i + 1]);
+          }
+        } else {
+          const float* f = reinterpret_cast<const float*>(&q[u]);
+#pragma unroll
+          for (int i = 0; i < VEC; ++i) acc[i] = fmaf(wr[u], f[i], acc[i]);
         }
-      } else {
-        const float* f = reinterpret_cast<const float*>(&q);
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) acc[i] += f[i];
       }
     }
   }
@@ -479,7 +549,8 @@ FR_API int fr_ue_gather_dropout(const float* news_vecs, const int* inv_his, void
   const size_t total = (size_t)rows * (D / 4);
   int blocks = (int)((total + 255) / 256);
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-  ue_gather_dropout_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(news_vecs, inv_his, (__nv_bfloat16*)X, rows, D / 4, p, seed, seed_dev);
+  FR_CHECK(launch_pdl(ue_gather_dropout_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, news_vecs, inv_his,
+                      (__nv_bfloat16*)X, rows, D / 4, p, seed, seed_dev));
   FR_LAUNCH_CHECK();
   return 0;
 }
@@ -492,7 +563,8 @@ FR_API int fr_ue_scatter_dx(const float* dX, const int* inv_his, float* d_news, 
   const size_t total = (size_t)rows * (D / 4);
   int blocks = (int)((total + 255) / 256);
   if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
-  ue_scatter_dx_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(dX, inv_his, d_news, rows, D / 4, p, seed, noise_std, noise_seed, seed_dev);
+  FR_CHECK(launch_pdl(ue_scatter_dx_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, dX, inv_his, d_news, rows, D / 4, p,
+                      seed, noise_std, noise_seed, seed_dev));
   FR_LAUNCH_CHECK();
   return 0;
 }
@@ -506,7 +578,7 @@ FR_API int fr_ue_mha_fwd(const void* qkv, const int* his_ids, void* ctx, float* 
   const int blocks = B * H;
   const float scale = 1.f / sqrtf((float)dk);
   cudaStream_t s = (cudaStream_t)stream;
-#define FR_GO(DK) ue_mha_fwd_kernel<DK><<<blocks, kJobThreads, 0, s>>>((const __nv_bfloat16*)qkv, his_ids, (__nv_bfloat16*)ctx, stats, B, L, H, scale, use_mask)
+#define FR_GO(DK) FR_CHECK(launch_pdl(ue_mha_fwd_kernel<DK>, dim3(blocks), dim3(kJobThreads), 0, s, (const __nv_bfloat16*)qkv, his_ids, (__nv_bfloat16*)ctx, stats, B, L, H, scale, use_mask))
   if (dk == 20) FR_GO(20); else if (dk == 32) FR_GO(32); else FR_GO(16);
 #undef FR_GO
   FR_LAUNCH_CHECK();
@@ -521,7 +593,18 @@ FR_API int fr_ue_mha_bwd(const void* qkv, const void* dctx, const float* stats, 
   const int blocks = B * H;
   const float scale = 1.f / sqrtf((float)dk);
   cudaStream_t s = (cudaStream_t)stream;
-#define FR_GO(DK) ue_mha_bwd_kernel<DK><<<blocks, kJobThreads, 0, s>>>((const __nv_bfloat16*)qkv, (const __nv_bfloat16*)dctx, stats, his_ids, (__nv_bfloat16*)dqkv, B, L, H, scale, use_mask)
+  const int dkp = (dk + 3) / 4 * 4, lp = L | 1;
+  const size_t smem = sizeof(float) * ((size_t)4 * L * dkp + (size_t)2 * L * lp + (size_t)5 * L);
+#define FR_GO(DK)                                                                                                        \
+  do {                                                                                                                   \
+    static bool attr_set = false;                                                                                        \
+    if (!attr_set) {                                                                                                     \
+      FR_CHECK(cudaFuncSetAttribute(ue_mha_bwd_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024));    \
+      attr_set = true;                                                                                                   \
+    }                                                                                                                    \
+    FR_CHECK(launch_pdl(ue_mha_bwd_kernel<DK>, dim3(blocks), dim3(kBwdThreads), smem, s, (const __nv_bfloat16*)qkv,   \
+                        (const __nv_bfloat16*)dctx, stats, his_ids, (__nv_bfloat16*)dqkv, B, L, H, scale, use_mask));      \
+  } while (0)
   if (dk == 20) FR_GO(20); else if (dk == 32) FR_GO(32); else FR_GO(16);
 #undef FR_GO
   FR_LAUNCH_CHECK();
@@ -545,13 +628,14 @@ FR_API int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, con
   a.d_ctx_pool = (__nv_bfloat16*)d_ctx_pool; a.d_pre = (__nv_bfloat16*)d_pre; a.d_w2 = d_w2; a.d_b2 = d_b2; a.d_news = d_news;
   a.B = B; a.L = L; a.C = C; a.D = D; a.Q = Q; a.use_mask = use_mask; a.train = train; a.noise_std = noise_std;
   a.noise_seed = noise_seed; a.seed_dev = seed_dev;
-  ue_pool_score_kernel<<<B, kPoolThreads, 0, s>>>(a);
+  FR_CHECK(launch_pdl(ue_pool_score_kernel, dim3(B), dim3(kPoolThreads), 0, s, a));
   FR_LAUNCH_CHECK();
   return 0;
 }
 
-FR_API int fr_colsum(const void* X, int is_bf16, float* out, int M, int N, int ld, const int* m_dev, int m_scale,
-                     void* stream) {
+namespace fr {
+int colsum_launch(const void* X, int is_bf16, const float* row_w, float* out, int M, int N, int ld, const int* m_dev,
+                  int m_scale, cudaStream_t s) {
   if (M == 0 || N == 0) return 0;
   const int vec = is_bf16 ? 8 : 4;
   FR_REQUIRE(N % vec == 0 && ld % vec == 0 && ((uintptr_t)X & 15) == 0, "fr_colsum: N=%d, ld=%d must be multiples of %d and X 16-byte aligned", N, ld, vec);
@@ -559,10 +643,23 @@ FR_API int fr_colsum(const void* X, int is_bf16, float* out, int M, int N, int l
   if (rows_blocks > 128) rows_blocks = 128;
   if (rows_blocks < 1) rows_blocks = 1;
   dim3 grid((N / vec + 31) / 32, rows_blocks);
-  if (is_bf16) colsum_kernel<__nv_bfloat16, 8><<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)X, out, M, N, ld, m_dev, m_scale);
-  else colsum_kernel<float, 4><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)X, out, M, N, ld, m_dev, m_scale);
+  if (is_bf16) colsum_kernel<__nv_bfloat16, 8><<<grid, 256, 0, s>>>((const __nv_bfloat16*)X, row_w, out, M, N, ld, m_dev, m_scale);
+  else colsum_kernel<float, 4><<<grid, 256, 0, s>>>((const float*)X, row_w, out, M, N, ld, m_dev, m_scale);
   FR_LAUNCH_CHECK();
   return 0;
+}
+}  // namespace fr
+
+FR_API int fr_colsum(const void* X, int is_bf16, float* out, int M, int N, int ld, const int* m_dev, int m_scale,
+                     void* stream) {
+  return colsum_launch(X, is_bf16, nullptr, out, M, N, ld, m_dev, m_scale, (cudaStream_t)stream);
+}
+
+// out[n] += sum_m row_w[m] * X[m, n]  (row_w fp32 [M]); same row limit as fr_colsum.
+FR_API int fr_colsum_weighted(const void* X, int is_bf16, const float* row_w, float* out, int M, int N, int ld,
+                              const int* m_dev, int m_scale, void* stream) {
+  FR_REQUIRE(row_w != nullptr, "fr_colsum_weighted: row_w is null");
+  return colsum_launch(X, is_bf16, row_w, out, M, N, ld, m_dev, m_scale, (cudaStream_t)stream);
 }
 
 FR_API int fr_transpose_cast(const float* in, void* out, int R, int Ccols, int ld_out, void* stream) {

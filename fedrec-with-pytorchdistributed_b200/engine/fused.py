@@ -336,9 +336,11 @@ class FusedStep:
             D.colsum(b["d_news"], g("text_encoder.fc.bias"), m_dev=count, m_scale=1)
         D.linear_bf16(b["d_news_bf"], pk["t_wfcT"], None, "bias", out=b["d_pooled"], m_dev=count, m_scale=1)
         D.text_pool_bwd(b["x"], b["e"], b["alpha"], b["d_pooled"], aa.att_fc2.weight.data.view(-1), count, K, T,
-                        b["d_pre"], b["da"], g("text_encoder.additive_attention.att_fc2.weight").view(-1),
-                        g("text_encoder.additive_attention.att_fc2.bias"),
-                        g("text_encoder.additive_attention.att_fc1.bias"))
+                        b["d_pre"], b["da"], None, g("text_encoder.additive_attention.att_fc2.bias"), None)
+        with self._fork():                                   # needs da, d_pre: the two reductions over all rows
+            D.colsum_weighted(b["e"], b["da"], g("text_encoder.additive_attention.att_fc2.weight").view(-1),
+                              m_dev=count, m_scale=T)
+            D.colsum(b["d_pre"], g("text_encoder.additive_attention.att_fc1.bias"), m_dev=count, m_scale=T)
         D.gemm_grad(b["d_pre"], b["x"], g("text_encoder.additive_attention.att_fc1.weight"), k_dev=count, k_scale=T)
         self._join()                                         # every gradient is in the flat buffer
 

@@ -40,6 +40,7 @@ SIGNATURES = {
     "fr_ue_mha_bwd": (I, [P, P, P, P, P, I, I, I, I, I, P]),
     "fr_ue_pool_score": (I, [P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, F, c_ulonglong, P, P]),
     "fr_colsum": (I, [P, I, P, I, I, I, P, I, P]),
+    "fr_colsum_weighted": (I, [P, I, P, P, I, I, I, P, I, P]),
     "fr_transpose_cast": (I, [P, P, I, I, I, P]),
     # gemm_grad_sm100.cu
     "fr_gemm_grad_bf16": (I, [P, P, P, I, I, I, I, I, I, P, I, I, P]),

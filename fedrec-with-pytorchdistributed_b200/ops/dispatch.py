@@ -291,6 +291,17 @@ def colsum(X, out, m_dev=None, m_scale=1):
     return out
 
 
+def colsum_weighted(X, row_w, out, m_dev=None, m_scale=1):
+    """``out[n] += sum_m row_w[m] * X[m, n]`` (X bf16 or fp32, row_w fp32)."""
+    lib = require_native()
+    assert X.stride(1) == 1 and out.dtype == torch.float32 and row_w.dtype == torch.float32
+    check(lib.fr_colsum_weighted(X.data_ptr(), 1 if X.dtype == torch.bfloat16 else 0, row_w.data_ptr(), out.data_ptr(),
+                                 X.shape[0], X.shape[1], X.stride(0), _p(m_dev), m_scale, stream_ptr(X.device)),
+          "fr_colsum_weighted")
+    count_launches(1)
+    return out
+
+
 def transpose_cast(w: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``out[c, r] = bf16(w[r, c])`` for a contiguous fp32 matrix."""
     lib = require_native()
@@ -315,12 +326,13 @@ def gemm_grad(A: torch.Tensor, B: torch.Tensor, out: torch.Tensor, k_dev=None, k
 
 
 def text_pool_bwd(hidden, e, alpha, d_pooled, w2, count, n_items, T, d_pre, da_scratch, d_w2, d_b2, d_b1):
+    """``d_w2`` / ``d_b1`` may be None: run ``colsum_weighted(e, da_scratch, d_w2)`` and ``colsum(d_pre, d_b1)`` yourself."""
     lib = require_native()
     check(lib.fr_text_pool_bwd(hidden.data_ptr(), e.data_ptr(), alpha.data_ptr(), d_pooled.data_ptr(), w2.data_ptr(),
                                _p(count), n_items, T, e.shape[1], hidden.shape[1], d_pre.data_ptr(),
-                               da_scratch.data_ptr(), d_w2.data_ptr(), d_b2.data_ptr(), d_b1.data_ptr(),
+                               da_scratch.data_ptr(), _p(d_w2), d_b2.data_ptr(), _p(d_b1),
                                stream_ptr(hidden.device)), "fr_text_pool_bwd")
-    count_launches(2)
+    count_launches(1 + (d_w2 is not None) + (d_b1 is not None))
     return d_pre
 
 

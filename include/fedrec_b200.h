@@ -139,6 +139,10 @@ int fr_ue_pool_score(const void* ctx, const void* e, const float* w2, const floa
 
 /* out[n] += sum_m X[m,n] (bias gradients); X bf16 or fp32 with leading dimension ld. */
 int fr_colsum(const void* X, int is_bf16, float* out, int M, int N, int ld, const int* m_dev, int m_scale, void* stream);
+/* out[n] += sum_m row_w[m] * X[m, n] (row_w fp32 [M]): the transposed GEMV behind d_w2 = e^T · da of the text head
+ * (autograd of attention.py:18 upstream). */
+int fr_colsum_weighted(const void* X, int is_bf16, const float* row_w, float* out, int M, int N, int ld, const int* m_dev,
+                       int m_scale, void* stream);
 /* out[c,r] = bf16(in[r,c]): K-major weight copies for the data-gradient GEMMs. */
 int fr_transpose_cast(const float* in, void* out, int R, int Ccols, int ld_out, void* stream);
 
