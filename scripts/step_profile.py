@@ -1,6 +1,11 @@
-"""In-situ per-kernel device time of one training step (warm caches, real clocks) via the PyTorch profiler (CUPTI)."""
+"""In-situ per-kernel device time of one training step (warm caches, real clocks) via the PyTorch profiler (CUPTI).
+
+Runs with FEDREC_PDL=0: with programmatic dependent launch a kernel becomes resident while its predecessor drains and its
+recorded duration then includes that wait, so the per-kernel times would no longer be exclusive (or add up)."""
 import os
 import sys
+
+os.environ.setdefault("FEDREC_PDL", "0")
 
 import numpy as np
 import torch
