@@ -196,8 +196,11 @@ FR_API int fr_gemm_grad_bf16(const void* A, const void* B, float* out, int M1, i
   const int tiles = ((M1 + GBM - 1) / GBM) * ((N1 + BN - 1) / BN);
   const int kb_total = (K + GBK - 1) / GBK;
   if (splits <= 0) {
-    splits = (2 * kNumSMs + tiles - 1) / tiles;
-    if (splits > kb_total) splits = kb_total;
+    // One wave of CTAs (197 KB of shared memory = one CTA per SM): measured on the step's shapes
+    // (scripts/bench_gemm_grad.py), 9 tiles x 16 splits takes 30.7 us where two waves (33 splits) take 39.9 us, since
+    // every CTA pays the pipeline fill and a 128 KB red.global epilogue. At least four k-blocks per split.
+    splits = kNumSMs / tiles;
+    if (splits > kb_total / 4) splits = kb_total / 4;
     if (splits < 1) splits = 1;
   }
   GradParams p;
