@@ -48,3 +48,27 @@ def test_ctypes_signatures_match_header_arity():
     for name, (_res, argtypes) in SIGNATURES.items():
         assert name in decls, name
         assert decls[name] == len(argtypes), (name, decls[name], len(argtypes))
+
+
+def build_c_demo():
+    """Compile and link examples/c_abi_demo.c as C99 against the header and the in-tree library; returns the binary path."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    lib_path = native.build()
+    lib_dir = os.path.dirname(lib_path)
+    out_dir = os.path.join(root, "build")
+    os.makedirs(out_dir, exist_ok=True)
+    exe = os.path.join(out_dir, "c_abi_demo")
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    cmd = ["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(root, "include"), "-I", os.path.join(cuda, "include"),
+           os.path.join(root, "examples", "c_abi_demo.c"), "-o", exe, "-L", lib_dir, "-lfedrec_b200",
+           "-L", os.path.join(cuda, "lib64"), "-lcudart", "-lm", f"-Wl,-rpath,{lib_dir}",
+           f"-Wl,-rpath,{os.path.join(cuda, 'lib64')}"]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return exe
+
+
+def test_header_is_valid_c_and_links_from_a_c_host():
+    """The public header compiles as C99 and a C program links against the library (run on a GPU: test_gpu_small_ops)."""
+    exe = build_c_demo()
+    assert os.path.exists(exe)

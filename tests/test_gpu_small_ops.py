@@ -97,3 +97,12 @@ def test_clip_and_noise(dev):
     z3 = torch.zeros(n, device=dev)
     ops.clip_noise_(z3, clip=0.0, noise_std=0.1, seed=99, stream_id=4)
     assert abs(float((z * z3).mean())) < 1e-4                     # another client's stream is independent
+
+
+def test_c_host_program_runs():
+    """examples/c_abi_demo.c: a plain C host drives the tcgen05 GEMM and the no-allocation de-dup through the C ABI."""
+    import subprocess
+    from test_build import build_c_demo
+    r = subprocess.run([build_c_demo()], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "c_abi_demo: OK" in r.stdout
