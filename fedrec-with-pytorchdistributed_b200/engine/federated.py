@@ -21,9 +21,7 @@ shard, runs ``local_steps`` fused steps, and then one aggregation kernel runs:
 """
 from __future__ import annotations
 
-import math
 import os
-import time
 from typing import List, Optional
 
 import torch

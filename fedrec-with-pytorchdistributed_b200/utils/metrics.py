@@ -11,7 +11,7 @@ on the device (one sort per metric), which is what ``Trainer.validate`` uses.
 """
 from __future__ import annotations
 
-from typing import Dict, Sequence, Tuple
+from typing import Dict, Tuple
 
 import numpy as np
 import torch

@@ -1,7 +1,17 @@
-import os, sys, time
-import numpy as np, torch
-sys.path.insert(0, '.')
-import bench
+"""What the per-step loop costs around the captured graph: full loop vs graph + Adam vs graph only vs the input copies alone.
+
+Device time from CUDA events and host enqueue time per step, no profiler attached (scripts/step_gaps.py shows two large
+gaps before each graph replay; this script shows they are the profiler's launch overhead, not part of a normal run).
+"""
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import bench  # noqa: E402
 from fedrec_b200.config import FedRecConfig
 from fedrec_b200.engine import TrainStep
 from fedrec_b200.models import UserModel

@@ -1,5 +1,4 @@
 """Rewrite section 3 of BASELINE.md from the evidence under profiles/ (run after copying fresh JSON there)."""
-import glob
 import json
 import os
 import subprocess
