@@ -112,6 +112,8 @@ def clip_noise_(x: torch.Tensor, clip: float, noise_std: float, seed: int = 0, s
     if clip <= 0 and noise_std <= 0:
         return x
     if not x.is_cuda:
+        if generator is None and noise_std > 0:      # same contract as the kernel: the noise is a function of (seed, stream)
+            generator = torch.Generator().manual_seed((int(seed) * 1000003 + int(stream_id) * 7919 + 12345) & (2 ** 63 - 1))
         return ref.clip_noise_(x, clip, noise_std, generator)
     lib = require_native()
     sq = grad_sq_norm(x) if clip > 0 else None
