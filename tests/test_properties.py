@@ -6,10 +6,10 @@ from hypothesis import given, settings, strategies as st
 from fedrec_b200.ops import reference as ref
 from fedrec_b200.utils import metrics as M
 
+# scores on a grid (divided by 10000 in the test): no ties, and none created by an affine map
 labels_scores = st.integers(2, 30).flatmap(
     lambda n: st.tuples(st.lists(st.integers(0, 1), min_size=n, max_size=n),
-                        st.lists(st.integers(0, 10000), min_size=n, max_size=n, unique=True)))   # scores on a grid: no ties, and
-#                                                                                   none created by an affine map
+                        st.lists(st.integers(0, 10000), min_size=n, max_size=n, unique=True)))
 
 
 @settings(max_examples=60, deadline=None)
