@@ -150,7 +150,8 @@ def run_ours(args):
     cfg = FedRecConfig(mode=args.mode, local_steps=args.local_steps, average_frozen=args.average_frozen, batch_size=B_USERS, max_his_len=HIS_LEN, npratio=NPRATIO, title_len=TITLE_LEN,
                        num_news=NUM_NEWS, clip_norm=CLIP, noise_multiplier=SIGMA, synthetic=True, snapshot_path="",
                        log_dir="", transport=args.transport, num_train=8, num_valid=1, seed=1234,
-                       trunk_cache=args.trunk_cache)
+                       trunk_cache=args.trunk_cache,
+                       ln_fold={"on": True, "off": False}.get(args.ln_fold, FedRecConfig().ln_fold))
     news_index = synthetic_news_index(np)
     runner = FederatedRunner(cfg, news_index=news_index, nid2index={"<unk>": 0}, train_sam=[], valid_sam=[])
     dev = runner.device
@@ -212,7 +213,8 @@ def run_ours(args):
     e2e_ms = t0.elapsed_time(t1) / args.steps
     h2d = cand_pin[0].numel() * 4 + his_pin[0].numel() * 4
     finish(args, "ours", rank, world, ms, e2e_ms, h2d, 4, launches, clocks,
-           {"transport": runner.grad_agg.transport, "step_impl": runner.step.impl, "last_loss": host_loss,
+           {"transport": runner.grad_agg.transport, "step_impl": runner.step.impl, "ln_fold": bool(cfg.ln_fold),
+            "last_loss": host_loss,
             "peer_heap": (f"{runner.symm.backend}{'+nvls-multimem' if runner.symm.mc_ptr else ''}" if runner.symm else "none"),
             **({"trunk_cache": "ON — trunk outputs cached across steps; not comparable with the headline number"}
                if args.trunk_cache else {}),
@@ -296,6 +298,8 @@ def main():
                     help="grad_avg = BASELINE.json configs 2/4 (default, the headline); param_avg = config 3")
     ap.add_argument("--local_steps", type=int, default=5)
     ap.add_argument("--average_frozen", action="store_true")
+    ap.add_argument("--ln_fold", choices=["default", "on", "off"], default="default",
+                    help="LayerNorm folded into the trunk GEMM epilogues (same arithmetic, fewer kernels)")
     ap.add_argument("--trunk_cache", action="store_true",
                     help="NOT the headline: keep trunk outputs of seen news resident in HBM (skips DistilBERT work for repeats)")
     args = ap.parse_args()

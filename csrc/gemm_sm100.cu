@@ -42,11 +42,21 @@ struct GemmParams {
   int m_scale;
   int M, N, K;
   int ldo, ldr;
+  // LayerNorm folding (FOLD kernels only; every pointer optional). Row statistics are (sum, sum of squares) pairs, one
+  // per 64-column slice of the row they describe.
+  const float* a_stats;       // [M, K/64, 2] of the rows of A: out = rstd*(A·W'^T) - rstd*mu*col_c + bias  (W' = W∘gamma)
+  const float* col_c;         // [N]   c_n = sum_k W'_nk
+  const float* r_stats;       // [M, N/64, 2] of the residual rows: the residual is LayerNorm(resid) computed on the fly
+  const float* r_gamma;       // [N]
+  const float* r_beta;        // [N]
+  float* stats_out;           // [M, N/64, 2] = (sum, sum of squares) of every 64-column slice of the output rows
+  float ln_eps;
+  int a_dim, r_dim;           // widths the two statistics were taken over
 };
 
 // CG = 1: one CTA per 128 x BN tile. CG = 2: a CTA pair (cta_group::2) per 256 x BN tile; each CTA stages its own
 // 128 rows of A and half of the B tile, so the L2 → shared-memory traffic per FLOP drops by a third.
-template <int BN, bool TMA_EPI, int CG>
+template <int BN, bool TMA_EPI, int CG, bool FOLD = false>
 struct Cfg {
   static constexpr int kStages = CG == 2 ? (BN == 192 ? (TMA_EPI ? 5 : 7) : (TMA_EPI ? 4 : 6))
                                          : (TMA_EPI ? (BN >= 256 ? 3 : 4) : (BN >= 256 ? 4 : (BN >= 128 ? 6 : 8)));
@@ -56,7 +66,8 @@ struct Cfg {
   static constexpr int kTmemCols = BN == 192 ? 512 : (2 * BN < 32 ? 32 : 2 * BN);   // two accumulators, a power of two
   static constexpr int kColsPerWarp = BN == 192 ? 64 : (BN / 4 < 32 ? 32 : BN / 4);  // columns one epilogue warp owns
   static constexpr int kColGroups = BN / kColsPerWarp;                 // 4 (BN = 128, 256), 3 (BN = 192) or 2 (BN = 64)
-  static constexpr int kBiasBytes = kEpiWarps * kColsPerWarp * 4;      // per-warp bias staging
+  static constexpr int kVecs = FOLD ? 4 : 1;                           // per-column vectors staged per warp: bias (+ c, gamma, beta)
+  static constexpr int kBiasBytes = kVecs * kEpiWarps * kColsPerWarp * 4;
   static constexpr int kBoxBytes = 4096;                               // per-warp output box: 32 rows x (64|32) bf16
   static constexpr int kStagingBytes = TMA_EPI ? kEpiWarps * kBoxBytes : 0;
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/ + kBiasBytes;
@@ -90,12 +101,12 @@ __device__ __forceinline__ uint32_t box_off(int r, int j) {
   return (uint32_t)(r * 64 + ((j ^ ((r >> 1) & 3)) << 4));                       // SWIZZLE_64B
 }
 
-template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG>
+template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG, bool FOLD = false>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_r,
                     const GemmParams p) {
-  using C = Cfg<BN, TMA_EPI, CG>;
+  using C = Cfg<BN, TMA_EPI, CG, FOLD>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
@@ -227,6 +238,9 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     constexpr int kCols = C::kColsPerWarp;
     const bool active = cgroup < C::kColGroups;
     float* my_bias = bias_stage + ew * kCols;
+    float* my_c = bias_stage + (kEpiWarps + ew) * kCols;          // FOLD only: the three extra per-column vectors
+    float* my_g = bias_stage + (2 * kEpiWarps + ew) * kCols;
+    float* my_be = bias_stage + (3 * kEpiWarps + ew) * kCols;
     uint8_t* my_box = staging + (TMA_EPI ? ew * C::kBoxBytes : 0);
     const uint32_t box_u32 = smem_u32(my_box);
     uint32_t rphase = 0;
@@ -254,6 +268,15 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         __syncwarp();
 #pragma unroll
         for (int j = lane; j < kCols; j += 32) my_bias[j] = (p.bias && wcol0 + j < p.N) ? __ldg(p.bias + wcol0 + j) : 0.f;
+        if constexpr (FOLD) {
+#pragma unroll
+          for (int j = lane; j < kCols; j += 32) {
+            const bool ok = wcol0 + j < p.N;
+            my_c[j] = (p.col_c && ok) ? __ldg(p.col_c + wcol0 + j) : 0.f;
+            my_g[j] = (p.r_gamma && ok) ? __ldg(p.r_gamma + wcol0 + j) : 1.f;
+            my_be[j] = (p.r_beta && ok) ? __ldg(p.r_beta + wcol0 + j) : 0.f;
+          }
+        }
         if (TMA_EPI && lane == 0) {
           tma_store_wait_read<0>();
           if (EPI == EPI_BIAS_RESID) {
@@ -269,6 +292,43 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
         for (int q = 0; q < kCols / 8; ++q)
           rres[q] = (row_ok && wcol0 + q * 8 < p.N) ? __ldg(rp + q) : make_uint4(0, 0, 0, 0);
+      }
+      // FOLD: per-row LayerNorm scalars (this thread owns row `row`), fetched while the MMAs run
+      float ra = 1.f, rb = 0.f;            // out = ra * acc + rb * c[col] + bias[col]
+      float rr = 1.f, rm = 0.f;            // residual = (resid - rm) * rr * gamma[col] + beta[col]
+      float st_s = 0.f, st_q = 0.f;        // running (sum, sum of squares) of this thread's output row
+      if constexpr (FOLD) {
+        if (work && row_ok) {
+          // A row's statistics arrive as one (sum, sum of squares) pair per 64-column slice of the producer's output
+          // (written without atomics, see below) and are added here in a fixed order: bit-reproducible.
+          if (p.a_stats) {
+            const int ns = p.a_dim >> 6;
+            const float2* sp = reinterpret_cast<const float2*>(p.a_stats) + (size_t)row * ns;
+            float sum = 0.f, sq = 0.f;
+            for (int k = 0; k < ns; ++k) {
+              const float2 t = __ldg(sp + k);
+              sum += t.x;
+              sq += t.y;
+            }
+            const float inv_n = 1.f / (float)p.a_dim;
+            const float mu = sum * inv_n;
+            ra = rsqrtf(fmaxf(fmaf(sq, inv_n, -mu * mu), 0.f) + p.ln_eps);
+            rb = -ra * mu;
+          }
+          if (p.r_stats) {
+            const int ns = p.r_dim >> 6;
+            const float2* sp = reinterpret_cast<const float2*>(p.r_stats) + (size_t)row * ns;
+            float sum = 0.f, sq = 0.f;
+            for (int k = 0; k < ns; ++k) {
+              const float2 t = __ldg(sp + k);
+              sum += t.x;
+              sq += t.y;
+            }
+            const float inv_n = 1.f / (float)p.r_dim;
+            rm = sum * inv_n;
+            rr = rsqrtf(fmaxf(fmaf(sq, inv_n, -rm * rm), 0.f) + p.ln_eps);
+          }
+        }
       }
       mbar_wait(&tmem_full[acc], acc_phase);
       tc_fence_after();
@@ -299,7 +359,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           tmem_ld_wait();
           float v[32];
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) + my_bias[cc + j];
+          for (int j = 0; j < 32; ++j) {
+            if (FOLD) v[j] = fmaf(ra, __uint_as_float(r[j]), fmaf(rb, my_c[cc + j], my_bias[cc + j]));
+            else v[j] = __uint_as_float(r[j]) + my_bias[cc + j];
+          }
           const int ncols = min(32, p.N - col0);       // multiple of 8 (N % 8 == 0)
           if (EPI == EPI_BIAS_RESID) {
 #pragma unroll
@@ -308,8 +371,25 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
 #pragma unroll
               for (int t = 0; t < 4; ++t) {
                 const float2 f = __bfloat1622float2(h[t]);
-                v[q * 8 + 2 * t] += f.x;
-                v[q * 8 + 2 * t + 1] += f.y;
+                if (FOLD) {
+                  const int c = cc + q * 8 + 2 * t;
+                  v[q * 8 + 2 * t] += fmaf((f.x - rm) * rr, my_g[c], my_be[c]);
+                  v[q * 8 + 2 * t + 1] += fmaf((f.y - rm) * rr, my_g[c + 1], my_be[c + 1]);
+                } else {
+                  v[q * 8 + 2 * t] += f.x;
+                  v[q * 8 + 2 * t + 1] += f.y;
+                }
+              }
+            }
+          }
+          if constexpr (FOLD) {
+            if (p.stats_out) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                if (j < ncols) {
+                  st_s += v[j];
+                  st_q = fmaf(v[j], v[j], st_q);
+                }
               }
             }
           }
@@ -352,6 +432,11 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         tc_fence_before();
         __syncwarp();
         if (lane == 0) release_acc(acc);
+        if constexpr (FOLD) {
+          static_assert(!FOLD || kCols == 64, "row statistics are kept per 64-column slice");
+          if (p.stats_out && row_ok)       // this warp's 64 columns are slice wcol0 / 64 of the row: a plain store
+            reinterpret_cast<float2*>(p.stats_out)[(size_t)row * (p.N >> 6) + (wcol0 >> 6)] = make_float2(st_s, st_q);
+        }
         if (TMA_EPI) {
           if (box_full) {
 #pragma unroll
@@ -441,10 +526,10 @@ int make_tmap_bf16_2d_box(CUtensorMap* out, const void* base, long long rows, lo
 
 struct Maps { CUtensorMap a, b, o, r; };
 
-template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG>
+template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG, bool FOLD = false>
 static int launch(const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t s) {
-  auto kern = gemm_bf16_tn_kernel<BN, EPI, OUT_F32, TMA_EPI, CG>;
-  using C = Cfg<BN, TMA_EPI, CG>;
+  auto kern = gemm_bf16_tn_kernel<BN, EPI, OUT_F32, TMA_EPI, CG, FOLD>;
+  using C = Cfg<BN, TMA_EPI, CG, FOLD>;
   static bool attr_set = false;   // per instantiation
   if (!attr_set) {
     FR_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -488,6 +573,18 @@ static int dispatch_epi(int epi, const Maps& m, const GemmParams& p, int max_cta
   return -1;
 }
 
+// LayerNorm-folding variants: the 256-wide tile, bf16 output, three of the epilogues.
+template <bool TMA_EPI, int CG>
+static int dispatch_fold(int epi, const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t s) {
+  switch (epi) {
+    case EPI_BIAS: return launch<256, EPI_BIAS, false, TMA_EPI, CG, true>(m, p, max_ctas, s);
+    case EPI_BIAS_GELU: return launch<256, EPI_BIAS_GELU, false, TMA_EPI, CG, true>(m, p, max_ctas, s);
+    case EPI_BIAS_RESID: return launch<256, EPI_BIAS_RESID, false, TMA_EPI, CG, true>(m, p, max_ctas, s);
+  }
+  fr::set_error("fr_gemm_bf16_fold: epilogue %d has no LayerNorm-folding variant (bias, gelu, resid only)", epi);
+  return -1;
+}
+
 // generic 2D bf16 map with an explicit swizzle mode (epilogue boxes)
 static int make_tmap_box_swz(CUtensorMap* out, const void* base, long long rows, long long cols, long long ld, int box_rows,
                              int box_cols, CUtensorMapSwizzle swz) {
@@ -520,9 +617,15 @@ using namespace fr;
 
 // out = epi(A · W^T + bias).  A [M,K] ld=lda, W [N,K] ld=ldw (both bf16, K-major), out bf16 or fp32 ld=ldo.
 // block_n: 0 = choose, else 64/128/192/256 (192: CTA pairs only).  m_dev (optional, device int): effective M = min(M, *m_dev*m_scale).
+struct FoldArgs {
+  const float* a_stats; const float* col_c; const float* r_stats; const float* r_gamma; const float* r_beta;
+  float* stats_out; float ln_eps;
+};
+
 static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const void* resid, void* out, int out_fp32,
                           int M, int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n,
-                          const int* m_dev, int m_scale, int cta_group, int tma_epilogue, void* stream) {
+                          const int* m_dev, int m_scale, int cta_group, int tma_epilogue, void* stream,
+                          const FoldArgs* fold = nullptr) {
   FR_REQUIRE(M >= 1 && N >= 8 && K >= 8, "fr_gemm_bf16: bad shape M=%d N=%d K=%d", M, N, K);
   FR_REQUIRE(N % 8 == 0 && K % 8 == 0, "fr_gemm_bf16: N=%d and K=%d must be multiples of 8", N, K);
   FR_REQUIRE(ldo % 8 == 0 && ((uintptr_t)out & 15) == 0, "fr_gemm_bf16: out must be 16-byte aligned, ldo %% 8 == 0");
@@ -537,6 +640,7 @@ static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const
       if (waste < best_waste) { best = bn; best_waste = waste; }
     }
     block_n = best;
+    if (fold) block_n = 256;
     // N = 768 (attention out-projection, FFN2): 4 x 192 columns quantise into waves better than 3 x 256
     static const int env_bn768 = [] { const char* e = getenv("FEDREC_GEMM_BN768"); return e ? atoi(e) : 256; }();
     if (N == 768 && !out_fp32 && M >= 4096 && env_bn768 == 192) block_n = 192;
@@ -572,8 +676,23 @@ static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const
   GemmParams p;
   p.bias = bias; p.resid = (const __nv_bfloat16*)resid; p.out = out; p.m_dev = m_dev; p.m_scale = m_scale;
   p.M = M; p.N = N; p.K = K; p.ldo = ldo; p.ldr = ldr;
+  p.a_stats = nullptr; p.col_c = nullptr; p.r_stats = nullptr; p.r_gamma = nullptr; p.r_beta = nullptr; p.stats_out = nullptr;
+  p.ln_eps = 0.f; p.a_dim = K; p.r_dim = N;
   cudaStream_t s = (cudaStream_t)stream;
   const int ctas = sm_count();
+  if (fold) {
+    FR_REQUIRE(!out_fp32 && block_n == 256, "fr_gemm_bf16_fold: bf16 output and the 256-wide tile only (block_n=%d)", block_n);
+    FR_REQUIRE(!fold->a_stats || fold->col_c, "fr_gemm_bf16_fold: a_stats needs col_c");
+    FR_REQUIRE(!fold->r_stats || (fold->r_gamma && fold->r_beta && epi == EPI_BIAS_RESID),
+               "fr_gemm_bf16_fold: r_stats needs r_gamma, r_beta and the residual epilogue");
+    FR_REQUIRE(!fold->stats_out || epi == EPI_BIAS_RESID, "fr_gemm_bf16_fold: stats_out is built for the residual epilogue");
+    FR_REQUIRE((!fold->a_stats || K % 64 == 0) && ((!fold->r_stats && !fold->stats_out) || N % 64 == 0),
+               "fr_gemm_bf16_fold: row statistics are kept per 64 columns (K=%d, N=%d)", K, N);
+    p.a_stats = fold->a_stats; p.col_c = fold->col_c; p.r_stats = fold->r_stats; p.r_gamma = fold->r_gamma;
+    p.r_beta = fold->r_beta; p.stats_out = fold->stats_out; p.ln_eps = fold->ln_eps;
+    if (cta_group == 2) return tma_epi ? dispatch_fold<true, 2>(epi, maps, p, ctas, s) : dispatch_fold<false, 2>(epi, maps, p, ctas, s);
+    return tma_epi ? dispatch_fold<true, 1>(epi, maps, p, ctas, s) : dispatch_fold<false, 1>(epi, maps, p, ctas, s);
+  }
   if (out_fp32) {
     switch (block_n) {
       case 64: return dispatch_epi<64, true, false>(epi, maps, p, ctas, s);
@@ -611,4 +730,20 @@ FR_API int fr_gemm_bf16_ex(const void* A, const void* W, const float* bias, cons
                            const int* m_dev, int m_scale, int cta_group, int tma_epilogue, void* stream) {
   return gemm_bf16_impl(A, W, bias, resid, out, out_fp32, M, N, K, lda, ldw, ldo, ldr, epi, block_n, m_dev, m_scale,
                         cta_group, tma_epilogue, stream);
+}
+
+// fr_gemm_bf16 with LayerNorm folded around it (frozen-weight trunks; all extra pointers optional, 256-wide tile):
+//   Row statistics are (sum, sum of squares) per 64-column slice: a_stats [M, K/64, 2], r_stats / stats_out [M, N/64, 2];
+//   the producer stores its slices (no atomics, nothing to zero) and the consumer adds them in a fixed order.
+//   a_stats + col_c [N]:
+//       out = rstd_A * (A · W^T) - rstd_A * mu_A * col_c + bias      = LayerNorm_gamma,beta(A) · W0^T + b0
+//       when W = W0∘gamma, col_c = rowsum(W), bias = b0 + W0·beta.
+//   r_stats + r_gamma, r_beta [N] (residual epilogue): the residual added is LayerNorm(resid) computed on the fly.
+//   stats_out (residual epilogue): statistics of every output row, for the next consumer.
+FR_API int fr_gemm_bf16_fold(const void* A, const void* W, const float* bias, const void* resid, void* out, int M, int N,
+                             int K, int lda, int ldw, int ldo, int ldr, int epi, const int* m_dev, int m_scale,
+                             const float* a_stats, const float* col_c, const float* r_stats, const float* r_gamma,
+                             const float* r_beta, float* stats_out, float ln_eps, void* stream) {
+  FoldArgs f{a_stats, col_c, r_stats, r_gamma, r_beta, stats_out, ln_eps};
+  return gemm_bf16_impl(A, W, bias, resid, out, 0, M, N, K, lda, ldw, ldo, ldr, epi, 0, m_dev, m_scale, 0, 0, stream, &f);
 }

@@ -75,6 +75,7 @@ class FedRecConfig:
     trunk_dropout_in_update: bool = False  # model.py:73 runs DistilBERT in train() for the 2nd pass
     cuda_graph: bool = True
     trunk_cache: bool = False      # keep the frozen trunk's hidden states of every news item seen resident in HBM
+    ln_fold: bool = True           # fold 11 of the trunk's 12 LayerNorms into the neighbouring GEMM epilogues (exact algebra)
     seed: int = 1234
     snapshot_path: str = "snapshot.pt"
     log_dir: str = "logs"

@@ -70,6 +70,22 @@ class PackedTrunk:
             put(L, "b2", blk.ffn.lin2.bias.data, False)
             put(L, "ln2_g", blk.output_layer_norm.weight.data, False)
             put(L, "ln2_b", blk.output_layer_norm.bias.data, False)
+        # LayerNorm folding (cfg.ln_fold): LN(x)·W^T + b = rstd*(x·(W∘gamma)^T) - rstd*mu*c + (b + W·beta), c = rowsum(W∘gamma)
+        # taken from the bf16-rounded product, so a constant row cancels exactly. FFN1 consumes sa_layer_norm of its own
+        # block; the QKV projection of block l >= 1 consumes output_layer_norm of block l-1.
+        prev = None
+        for blk, L in zip(b.transformer.layer, self.layers):
+            def fold(key_w, key_c, key_b, w, bias, ln):
+                wf = (w.float() * ln.weight.data.float()[None, :]).bfloat16()
+                put(L, key_w, wf.float(), True)
+                put(L, key_c, wf.float().sum(1), False)
+                put(L, key_b, bias.float() + w.float() @ ln.bias.data.float(), False)
+            fold("w1f", "c1", "b1f", blk.ffn.lin1.weight.data, blk.ffn.lin1.bias.data, blk.sa_layer_norm)
+            if prev is not None:
+                a = blk.attention
+                fold("wqkvf", "cqkv", "bqkvf", torch.cat([a.q_lin.weight.data, a.k_lin.weight.data, a.v_lin.weight.data], 0),
+                     torch.cat([a.q_lin.bias.data, a.k_lin.bias.data, a.v_lin.bias.data]), prev.output_layer_norm)
+            prev = blk
         self.heads = b.config.n_heads
         self.dim = b.config.dim
         self.ffn = b.config.hidden_dim
@@ -182,6 +198,8 @@ class FusedStep:
         z = lambda *s, dt=bf: torch.zeros(*s, device=dev, dtype=dt)  # noqa: E731
         hq = self.model.text_encoder.additive_attention.att_fc1.out_features
         b = {"x": z(R, dim), "y": z(R, dim), "ctx": z(R, dim), "qkv": z(R, 3 * dim), "ffn": z(R, ffn),
+             "y2": z(R, dim) if self.cfg.ln_fold else None,
+             "stats": z(2 * len(self.trunk.layers), R, dim // 64, 2, dt=torch.float32) if self.cfg.ln_fold else None,
              "e": z(R, hq), "pooled": z(K, dim), "alpha": z(R, dt=torch.float32),
              "news_vecs": z(K, self.cfg.news_dim, dt=torch.float32),
              # backward
@@ -215,7 +233,9 @@ class FusedStep:
             D.cache_select(uniq, count, K, cache["valid"], b["miss"], b["miss_count"])
             uniq, count = b["miss"], b["miss_count"]
         D.bert_embed_ln(m.news_tokens, uniq, count, K, T, tr.word, tr.pos, tr.emb_g, tr.emb_b, x)
-        for L in tr.layers:
+        if self.cfg.ln_fold:
+            self._trunk_folded(b, uniq, count, K, T)
+        for L in ([] if self.cfg.ln_fold else tr.layers):
             D.linear_bf16(x, L["wqkv"], L["bqkv"], "bias", out=qkv, m_dev=count, m_scale=T)
             D.bert_attention(qkv, m.news_mask, uniq, count, K, T, tr.heads, ctx)
             D.linear_bf16(ctx, L["wo"], L["bo"], "resid", resid=x, out=y, m_dev=count, m_scale=T)
@@ -237,6 +257,34 @@ class FusedStep:
                     b["pooled"], b["alpha"])
         D.linear_bf16(b["pooled"], pk["t_wfc"], te.fc.bias.data, "bias", out=b["news_vecs"], m_dev=count, m_scale=1)
         return b
+
+    def _trunk_folded(self, b, uniq, count, K: int, T: int) -> None:
+        """The six blocks with every LayerNorm but the last folded into the GEMMs around it (GEMM notes).
+
+        ``y`` / ``y2`` hold the *un-normalised* block outputs; their row statistics travel in ``stats`` (one (sum, sum of
+        squares) pair per 64-column slice, stored by the residual epilogues without atomics, so the step stays
+        bit-reproducible) and each consumer applies the normalisation in its own epilogue."""
+        m, tr = self.model, self.trunk
+        x, y1, y2, ctx, qkv, ffn, st = b["x"], b["y"], b["y2"], b["ctx"], b["qkv"], b["ffn"], b["stats"]
+        kw = dict(m_dev=count, m_scale=T)
+        n = len(tr.layers)
+        for l, L in enumerate(tr.layers):
+            st1, st2 = st[2 * l], st[2 * l + 1]
+            if l == 0:
+                D.linear_bf16(x, L["wqkv"], L["bqkv"], "bias", out=qkv, **kw)
+                D.bert_attention(qkv, m.news_mask, uniq, count, K, T, tr.heads, ctx)
+                D.linear_bf16_fold(ctx, L["wo"], L["bo"], "resid", y1, resid=x, stats_out=st1, **kw)
+            else:
+                P, pst = tr.layers[l - 1], st[2 * l - 1]
+                D.linear_bf16_fold(y2, L["wqkvf"], L["bqkvf"], "bias", qkv, a_stats=pst, col_c=L["cqkv"], **kw)
+                D.bert_attention(qkv, m.news_mask, uniq, count, K, T, tr.heads, ctx)
+                D.linear_bf16_fold(ctx, L["wo"], L["bo"], "resid", y1, resid=y2, r_stats=pst, r_gamma=P["ln2_g"],
+                                   r_beta=P["ln2_b"], stats_out=st1, **kw)
+            D.linear_bf16_fold(y1, L["w1f"], L["b1f"], "gelu", ffn, a_stats=st1, col_c=L["c1"], **kw)
+            D.linear_bf16_fold(ffn, L["w2"], L["b2"], "resid", y2, resid=y1, r_stats=st1, r_gamma=L["ln1_g"],
+                               r_beta=L["ln1_b"], stats_out=st2 if l + 1 < n else None, **kw)
+        last = tr.layers[-1]
+        D.layernorm_bf16(y2, last["ln2_g"], last["ln2_b"], out=x, count=count, rows_per_item=T)
 
     def _ids(self, cand, his):
         ids = torch.cat([his.reshape(-1), cand.reshape(-1)]).to(torch.int32)
@@ -353,7 +401,7 @@ class FusedStep:
             return self._run_eager(cand, his, train)
         cfg = self.cfg      # everything a captured launch bakes in as a constant is part of the key
         key = (tuple(cand.shape), tuple(his.shape), float(cfg.news_grad_noise), bool(cfg.mask_padding), bool(cfg.dedup),
-               bool(cfg.trunk_cache), float(self.model.user_encoder.dropout_rate))
+               bool(cfg.trunk_cache), bool(cfg.ln_fold), float(self.model.user_encoder.dropout_rate))
         g = self._graphs.get(key)
         if g is None:
             g = self._capture(cand, his, key)

@@ -57,4 +57,5 @@ SIGNATURES = {
     # gemm_sm100.cu
     "fr_gemm_bf16": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, I, P]),
     "fr_gemm_bf16_ex": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, I, I, I, P]),
+    "fr_gemm_bf16_fold": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, P, I, P, P, P, P, P, P, F, P]),
 }

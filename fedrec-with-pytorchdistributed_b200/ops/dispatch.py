@@ -178,6 +178,33 @@ def linear_bf16(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] =
     return out
 
 
+def linear_bf16_fold(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], epi: str, out: torch.Tensor,
+                     resid: Optional[torch.Tensor] = None, m_dev: Optional[torch.Tensor] = None, m_scale: int = 1,
+                     a_stats: Optional[torch.Tensor] = None, col_c: Optional[torch.Tensor] = None,
+                     r_stats: Optional[torch.Tensor] = None, r_gamma: Optional[torch.Tensor] = None,
+                     r_beta: Optional[torch.Tensor] = None, stats_out: Optional[torch.Tensor] = None,
+                     ln_eps: float = 1e-12) -> torch.Tensor:
+    """``linear_bf16`` with LayerNorm folded around it (see ``fr_gemm_bf16_fold`` in the header).
+
+    ``a_stats``/``col_c``: the input is an un-normalised tensor whose LayerNorm is applied algebraically (``w`` must
+    already be scaled by gamma). ``r_stats``/``r_gamma``/``r_beta``: the residual is normalised on the fly.
+    Statistics tensors are ``[M, width // 64, 2]`` fp32: a (sum, sum of squares) pair per 64-column slice of the row they
+    describe; ``stats_out`` is written (not accumulated), so it needs no zeroing."""
+    assert x.is_cuda and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and out.dtype == torch.bfloat16
+    assert x.stride(1) == 1 and w.stride(1) == 1 and out.stride(1) == 1
+    for t in (a_stats, r_stats, stats_out):
+        assert t is None or (t.dtype == torch.float32 and t.is_contiguous() and t.shape[-1] == 2)
+    lib = require_native()
+    M, K = x.shape
+    N = w.shape[0]
+    check(lib.fr_gemm_bf16_fold(x.data_ptr(), w.data_ptr(), _p(bias), _p(resid), out.data_ptr(), M, N, K, x.stride(0),
+                                w.stride(0), out.stride(0), resid.stride(0) if resid is not None else 0, _EPI[epi],
+                                _p(m_dev), m_scale, _p(a_stats), _p(col_c), _p(r_stats), _p(r_gamma), _p(r_beta),
+                                _p(stats_out), float(ln_eps), stream_ptr(x.device)), "fr_gemm_bf16_fold")
+    count_launches(1)
+    return out
+
+
 # ---- DistilBERT trunk / text head pieces (CUDA only; the CPU path is the nn.Module code) -------------
 def bert_embed_ln(tokens, items, count, n_items, T, word, pos, gamma, beta, out, eps=1e-12):
     lib = require_native()

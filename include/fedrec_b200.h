@@ -197,6 +197,22 @@ int fr_gemm_bf16_ex(const void* A, const void* W, const float* bias, const void*
                     int N, int K, int lda, int ldw, int ldo, int ldr, int epi, int block_n, const int* m_dev,
                     int m_scale, int cta_group, int tma_epilogue, void* stream);
 
+/* fr_gemm_bf16 with LayerNorm folded around it, for trunks whose weights are frozen (HF DistilBERT's sa_layer_norm /
+ * output_layer_norm reached from encoder.py:27): the normalisation never runs as a kernel of its own. 256-wide tile,
+ * bf16 output, epi in {bias, gelu, resid}; every extra pointer is optional.
+ *   Row statistics are (sum, sum of squares) pairs, one per 64-column slice of the row: a_stats [M, K/64, 2],
+ *   r_stats and stats_out [M, N/64, 2]. The producer stores its slices (no atomics, nothing to zero beforehand), the
+ *   consumer adds them in a fixed order, so results are bit-reproducible.
+ *   a_stats + col_c [N]:
+ *       out = rstd*(A·W^T) - rstd*mu*col_c + bias  ==  LayerNorm(A)·W0^T + b0   for  W = W0∘gamma, col_c = rowsum(W),
+ *       bias = b0 + W0·beta.
+ *   r_stats, r_gamma [N], r_beta [N] (resid epilogue): adds LayerNorm(resid) instead of resid.
+ *   stats_out (resid epilogue): statistics of each output row. */
+int fr_gemm_bf16_fold(const void* A, const void* W, const float* bias, const void* resid, void* out, int M, int N, int K,
+                      int lda, int ldw, int ldo, int ldr, int epi, const int* m_dev, int m_scale, const float* a_stats,
+                      const float* col_c, const float* r_stats, const float* r_gamma, const float* r_beta,
+                      float* stats_out, float ln_eps, void* stream);
+
 /* out[M1,N1] (fp32) += A[K,M1]^T · B[K,N1]: weight gradients dW = dY^T X on tcgen05 with MN-major operands and
  * split-K (csrc/gemm_grad_sm100.cu). K_eff = min(K, *k_dev * k_scale); rows of A in [K_eff, round_up(K_eff,64))
  * must be zero. Replaces the autograd weight-gradient GEMMs of every trainable nn.Linear. */
