@@ -55,6 +55,10 @@ Our arm additionally clips (C=2) and adds LDP noise (σ=0.05) inside the aggrega
   one `fr_param_average` kernel): {pa['value']:,.0f} impressions/s on eight GPUs.
 * With NCCL as the aggregation transport instead of the fused kernels the same run is
   {last_json(os.path.join(P, 'r1_bench_ours_8_nccl.json'))['value']:,.0f} impressions/s.
+* The table rows for 2, 4 and 8 GPUs and the 100-step one-GPU row were taken before the LayerNorm folding landed
+  (DESIGN §3, GEMM notes); `r1_bench_ours_1_lnfold.json` is the final build (60 steps). Same-box A/B of the final build:
+  17,832 impressions/s with the folding, 17,271 without (`bench.py --ln_fold on|off`); best single run 18,054.
+  Run-to-run spread between boxes under the power cap is about ±2 %.
 * `sw_power_cap` is the only throttle reason seen (normal for dense tensor work on a 1 kW part; SM clock ≈1.8 GHz under
   load); no thermal or hardware slowdown.
 * Not the headline, reported separately: with the opt-in trunk-output cache (`--trunk_cache`, hidden states of news seen before
