@@ -223,7 +223,7 @@ class FusedStep:
             with self._fork():
                 self._pack_weights(train=False)
         T = m.news_tokens.shape[1]
-        x, y, ctx, qkv, ffn = b["x"], b["y"], b["ctx"], b["qkv"], b["ffn"]
+        x = b["x"]
         want_uniq, want_count = uniq, count
         cache = self._trunk_cache() if self.cfg.trunk_cache else None
         if cache is not None:
@@ -235,14 +235,8 @@ class FusedStep:
         D.bert_embed_ln(m.news_tokens, uniq, count, K, T, tr.word, tr.pos, tr.emb_g, tr.emb_b, x)
         if self.cfg.ln_fold:
             self._trunk_folded(b, uniq, count, K, T)
-        for L in ([] if self.cfg.ln_fold else tr.layers):
-            D.linear_bf16(x, L["wqkv"], L["bqkv"], "bias", out=qkv, m_dev=count, m_scale=T)
-            D.bert_attention(qkv, m.news_mask, uniq, count, K, T, tr.heads, ctx)
-            D.linear_bf16(ctx, L["wo"], L["bo"], "resid", resid=x, out=y, m_dev=count, m_scale=T)
-            D.layernorm_bf16(y, L["ln1_g"], L["ln1_b"], out=x, count=count, rows_per_item=T)
-            D.linear_bf16(x, L["w1"], L["b1"], "gelu", out=ffn, m_dev=count, m_scale=T)
-            D.linear_bf16(ffn, L["w2"], L["b2"], "resid", resid=x, out=y, m_dev=count, m_scale=T)
-            D.layernorm_bf16(y, L["ln2_g"], L["ln2_b"], out=x, count=count, rows_per_item=T)
+        else:
+            self._trunk_plain(b, uniq, count, K, T)
         if cache is not None:
             D.rows_copy(x, None, cache["hidden"], uniq, count, K, T, valid=cache["valid"])      # new items → cache
             uniq, count = want_uniq, (want_count if want_count is not None else b["full_count"])
@@ -257,6 +251,19 @@ class FusedStep:
                     b["pooled"], b["alpha"])
         D.linear_bf16(b["pooled"], pk["t_wfc"], te.fc.bias.data, "bias", out=b["news_vecs"], m_dev=count, m_scale=1)
         return b
+
+    def _trunk_plain(self, b, uniq, count, K: int, T: int) -> None:
+        """The six blocks with LayerNorm as a kernel of its own (``--ln_fold false``); ``x`` holds the block input / output."""
+        m, tr = self.model, self.trunk
+        x, y, ctx, qkv, ffn = b["x"], b["y"], b["ctx"], b["qkv"], b["ffn"]
+        for L in tr.layers:
+            D.linear_bf16(x, L["wqkv"], L["bqkv"], "bias", out=qkv, m_dev=count, m_scale=T)
+            D.bert_attention(qkv, m.news_mask, uniq, count, K, T, tr.heads, ctx)
+            D.linear_bf16(ctx, L["wo"], L["bo"], "resid", resid=x, out=y, m_dev=count, m_scale=T)
+            D.layernorm_bf16(y, L["ln1_g"], L["ln1_b"], out=x, count=count, rows_per_item=T)
+            D.linear_bf16(x, L["w1"], L["b1"], "gelu", out=ffn, m_dev=count, m_scale=T)
+            D.linear_bf16(ffn, L["w2"], L["b2"], "resid", resid=x, out=y, m_dev=count, m_scale=T)
+            D.layernorm_bf16(y, L["ln2_g"], L["ln2_b"], out=x, count=count, rows_per_item=T)
 
     def _trunk_folded(self, b, uniq, count, K: int, T: int) -> None:
         """The six blocks with every LayerNorm but the last folded into the GEMMs around it (GEMM notes).
