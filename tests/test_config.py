@@ -19,3 +19,10 @@ def test_options_and_flags(monkeypatch):
     assert cfg.client_weights == [1.0, 2.0, 3.0] and cfg.lr == 0.001
     with pytest.raises(SystemExit):
         FedRecConfig.from_argv(["--bogus", "1"], [])
+
+
+def test_kernel_switches(monkeypatch):
+    assert FedRecConfig().ln_fold and FedRecConfig().cuda_graph            # the fast paths are the defaults
+    assert not FedRecConfig.from_argv(["--ln_fold", "false"], []).ln_fold
+    monkeypatch.setenv("FEDREC_LN_FOLD", "0")
+    assert not FedRecConfig.from_env().ln_fold
