@@ -76,10 +76,10 @@ class PackedTrunk:
         prev = None
         for blk, L in zip(b.transformer.layer, self.layers):
             def fold(key_w, key_c, key_b, w, bias, ln):
-                wf = (w.float() * ln.weight.data.float()[None, :]).bfloat16()
+                wf, c, bf = ops.reference.fold_layernorm(w, bias, ln.weight.data, ln.bias.data)
                 put(L, key_w, wf.float(), True)
-                put(L, key_c, wf.float().sum(1), False)
-                put(L, key_b, bias.float() + w.float() @ ln.bias.data.float(), False)
+                put(L, key_c, c, False)
+                put(L, key_b, bf, False)
             fold("w1f", "c1", "b1f", blk.ffn.lin1.weight.data, blk.ffn.lin1.bias.data, blk.sa_layer_norm)
             if prev is not None:
                 a = blk.attention

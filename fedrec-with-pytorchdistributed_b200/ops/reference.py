@@ -102,3 +102,25 @@ def additive_pool(x, w1, b1, w2, b2, mask: Optional[torch.Tensor] = None):
     pm = mask[:, :, None].to(al.dtype) if mask is not None else None
     al = exp_normalise(al, 1, pm)
     return (x * al).sum(1)
+
+
+def fold_layernorm(w: torch.Tensor, bias: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor
+                   ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Weights of ``Linear(LayerNorm(x))`` rewritten so that the normalisation can be applied *after* the matmul:
+
+        LN(x)·Wᵀ + b  =  rstd ⊙ (x·W'ᵀ)  −  (rstd·μ) ⊙ c  +  b'        (μ, rstd = row statistics of x)
+
+    with ``W' = W∘γ`` (returned in bf16, the GEMM operand), ``c = rowsum(W')`` taken from the *rounded* W' so that a
+    constant row cancels exactly, and ``b' = b + W·β``. Used by ``engine.fused.PackedTrunk`` for ``fr_gemm_bf16_fold``."""
+    wf = (w.float() * gamma.float()[None, :]).bfloat16()
+    return wf, wf.float().sum(1), bias.float() + w.float() @ beta.float()
+
+
+def linear_after_layernorm_folded(x: torch.Tensor, wf: torch.Tensor, c: torch.Tensor, bf: torch.Tensor,
+                                  eps: float = 1e-12) -> torch.Tensor:
+    """fp32 statement of what the folded GEMM epilogue computes from the un-normalised ``x`` (oracle for the kernel)."""
+    xf = x.float()
+    mu = xf.mean(1, keepdim=True)
+    rstd = torch.rsqrt((xf * xf).mean(1, keepdim=True) - mu * mu + eps)
+    return rstd * (xf @ wf.float().t()) - (rstd * mu) * c[None, :] + bf[None, :]
+
