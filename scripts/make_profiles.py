@@ -22,6 +22,10 @@ WORK = {
     "gemm_ffn2": (2.0 * M * 768 * 3072, M * 3072 * 2 + 768 * 3072 * 2 + 2 * M * 768 * 2, f"M={M} N=768 K=3072 bias+residual"),
     "gemm_qkv": (2.0 * M * 2304 * 768, M * 768 * 2 + 2304 * 768 * 2 + M * 2304 * 2, f"M={M} N=2304 K=768 bias"),
     "gemm_out": (2.0 * M * 768 * 768, M * 768 * 2 * 3 + 768 * 768 * 2, f"M={M} N=768 K=768 bias+residual"),
+    "gemm_fold_ffn1": (2.0 * M * 3072 * 768, M * 768 * 2 + 3072 * 768 * 2 + M * 3072 * 2 + M * 96, f"M={M} N=3072 K=768 LN(A) folded + bias + GELU"),
+    "gemm_fold_ffn2": (2.0 * M * 768 * 3072, M * 3072 * 2 + 768 * 3072 * 2 + 2 * M * 768 * 2 + 2 * M * 96, f"M={M} N=768 K=3072 bias + LN(residual) + row stats"),
+    "gemm_fold_qkv": (2.0 * M * 2304 * 768, M * 768 * 2 + 2304 * 768 * 2 + M * 2304 * 2 + M * 96, f"M={M} N=2304 K=768 LN(A) folded + bias"),
+    "gemm_fold_out": (2.0 * M * 768 * 768, M * 768 * 2 * 3 + 768 * 768 * 2 + 2 * M * 96, f"M={M} N=768 K=768 bias + LN(residual) + row stats"),
     "attention": (4.0 * (M // 30) * 12 * 30 * 30 * 64, M * 2304 * 2 + M * 768 * 2, f"{M // 30} titles x 12 heads, T=30"),
     "gemm_grad": (2.0 * M * 384 * 768, M * (384 + 768) * 2 + 384 * 768 * 4, f"dW[384,768] += dY^T X, K={M}"),
     "layernorm": (0.0, M * 768 * 2 * 2, f"{M} rows x 768 bf16"),

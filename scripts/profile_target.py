@@ -1,6 +1,7 @@
 """Tiny single-GPU drivers for `ncu --set full` captures (one kernel family per invocation).
 
-usage: python scripts/profile_target.py gemm_ffn1|gemm_out|gemm_qkv|gemm_ffn2|attention|gemm_grad|step
+usage: python scripts/profile_target.py gemm_ffn1|gemm_out|gemm_qkv|gemm_ffn2|attention|gemm_grad|layernorm|aggregate|step
+       gemm_fold_qkv|gemm_fold_ffn1|gemm_fold_out|gemm_fold_ffn2   (the LayerNorm-folding variants the trunk runs by default)
 """
 import os
 import sys
@@ -15,7 +16,26 @@ what = sys.argv[1] if len(sys.argv) > 1 else "gemm_ffn1"
 M = int(os.environ.get("FEDREC_PROFILE_M", "27000"))
 torch.manual_seed(0)
 
-if what.startswith("gemm_") and what != "gemm_grad":
+if what.startswith("gemm_fold_"):
+    N, K, epi = {"gemm_fold_ffn1": (3072, 768, "gelu"), "gemm_fold_out": (768, 768, "resid"),
+                 "gemm_fold_qkv": (2304, 768, "bias"), "gemm_fold_ffn2": (768, 3072, "resid")}[what]
+    x = (torch.randn(M, K, device=DEV) * 0.5).bfloat16()
+    w = (torch.randn(N, K, device=DEV) / K ** 0.5).bfloat16()
+    b = torch.randn(N, device=DEV)
+    out = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    kw = {}
+    if epi == "resid":                       # residual normalised on the fly + row statistics of the output
+        r = torch.randn(M, N, device=DEV).bfloat16()
+        rf = r.float().view(M, N // 64, 64)
+        kw = dict(resid=r, r_stats=torch.stack([rf.sum(2), (rf * rf).sum(2)], 2).contiguous(),
+                  r_gamma=torch.rand(N, device=DEV) + 0.5, r_beta=torch.randn(N, device=DEV) * 0.1,
+                  stats_out=torch.empty(M, N // 64, 2, device=DEV))
+    else:                                    # LayerNorm of the input applied in the epilogue
+        xf = x.float().view(M, K // 64, 64)
+        kw = dict(a_stats=torch.stack([xf.sum(2), (xf * xf).sum(2)], 2).contiguous(), col_c=w.float().sum(1).contiguous())
+    for _ in range(6):
+        D.linear_bf16_fold(x, w, b, epi, out, **kw)
+elif what.startswith("gemm_") and what != "gemm_grad":
     N, K, epi = {"gemm_ffn1": (3072, 768, "gelu"), "gemm_out": (768, 768, "resid"), "gemm_qkv": (2304, 768, "bias"),
                  "gemm_ffn2": (768, 3072, "resid")}[what]
     x = (torch.randn(M, K, device=DEV) * 0.5).bfloat16()
