@@ -72,3 +72,60 @@ def test_packed_trunk_builds_the_folded_weights_in_place(monkeypatch):
     tr.repack()
     assert {k: v.data_ptr() for k, v in L1.items()} == ptrs                   # refilled in place
     assert not torch.equal(L1["wqkvf"], wf)                                   # and with the new values
+
+
+def _attention_core(blk, qkv, mask):
+    """Soft-max attention of one block from an already projected (q | k | v), then nothing else (no out-projection)."""
+    n, T, D3 = qkv.shape
+    D = D3 // 3
+    H = blk.attention.n_heads
+    dh = D // H
+    q, k, v = (t.view(n, T, H, dh).transpose(1, 2) for t in qkv.split(D, dim=-1))
+    s = (q / dh ** 0.5) @ k.transpose(-1, -2)
+    if mask is not None:
+        s = s.masked_fill((mask == 0)[:, None, None, :], torch.finfo(s.dtype).min)
+    return (torch.softmax(s, -1) @ v).transpose(1, 2).reshape(n, T, D)
+
+
+def test_folded_trunk_wiring_equals_the_module_forward():
+    """The wiring of FusedStep._trunk_folded stated in fp32 PyTorch: un-normalised block outputs travel between the
+    GEMMs, FFN1 folds sa_layer_norm of its block, QKV of block l >= 1 folds output_layer_norm of block l-1, residuals are
+    normalised on the fly, only the last output_layer_norm is applied as such. Must equal DistilBertTrunk.forward."""
+    from fedrec_b200.models.distilbert import DistilBertConfigLite, DistilBertTrunk
+    torch.manual_seed(0)
+    bert = DistilBertTrunk(DistilBertConfigLite(n_layers=3, dim=64, hidden_dim=128, n_heads=4)).eval()
+    with torch.no_grad():
+        for blk in bert.transformer.layer:
+            for ln in (blk.sa_layer_norm, blk.output_layer_norm):
+                ln.weight.uniform_(0.5, 1.5)
+                ln.bias.uniform_(-0.2, 0.2)
+    ids = torch.randint(1, 1000, (5, 12))
+    mask = torch.ones(5, 12, dtype=torch.long)
+    mask[:, 9:] = 0
+    with torch.no_grad():
+        want = bert(ids, mask)[0]
+        x = bert.embeddings(ids)                                   # normalised input of block 0
+        n, T, D = x.shape
+        flat = lambda t: t.reshape(n * T, -1)                      # noqa: E731
+        ln = lambda t, m: F.layer_norm(t, (D,), m.weight, m.bias, 1e-12)   # noqa: E731
+
+        def fold_lin(inp, w, b, norm):                             # Linear(LayerNorm(inp)) from the un-normalised inp
+            wf, c, bf = ref.fold_layernorm(w, b, norm.weight, norm.bias)
+            return ref.linear_after_layernorm_folded(flat(inp), wf.float(), c, bf).view(n, T, -1)
+
+        y2, prev = None, None
+        for l, blk in enumerate(bert.transformer.layer):
+            a = blk.attention
+            wqkv = torch.cat([a.q_lin.weight, a.k_lin.weight, a.v_lin.weight], 0)
+            bqkv = torch.cat([a.q_lin.bias, a.k_lin.bias, a.v_lin.bias])
+            if l == 0:
+                qkv, resid = x @ wqkv.t() + bqkv, x
+            else:
+                qkv, resid = fold_lin(y2, wqkv, bqkv, prev.output_layer_norm), ln(y2, prev.output_layer_norm)
+            y1 = a.out_lin(_attention_core(blk, qkv, mask)) + resid            # un-normalised
+            h = F.gelu(fold_lin(y1, blk.ffn.lin1.weight, blk.ffn.lin1.bias, blk.sa_layer_norm))
+            y2 = blk.ffn.lin2(h) + ln(y1, blk.sa_layer_norm)                    # un-normalised
+            prev = blk
+        got = ln(y2, prev.output_layer_norm)
+    # fold_layernorm rounds W∘gamma to bf16 (it is the GEMM operand), so the comparison is at bf16 weight precision
+    assert float((got - want).abs().max()) < 0.05 and float((got - want).abs().mean()) < 5e-3
