@@ -116,7 +116,8 @@ def finish(args, impl, rank, world, ms_per_step, e2e_ms, h2d, d2h, launches, clo
     value = world * B_USERS / (ms_per_step * 1e-3)
     e2e_val = world * B_USERS / (e2e_ms * 1e-3)
     cfg = {"model": "FedRec joint DistilBERT-base text encoder + user encoder (MHA 20x20 + additive attention)",
-           "mode": "Gradient_Averaging_main: per-round gradient averaging, clip C=%g + LDP sigma=%g" % (CLIP, SIGMA),
+           "mode": ("Gradient_Averaging_main: per-round gradient averaging" +
+                    (", clip C=%g + LDP sigma=%g" % (CLIP, SIGMA) if impl != "reference" else " (upstream: no clip, no noise)")),
            "global_batch": world * B_USERS, "users_per_client_per_round": B_USERS, "seq_len": TITLE_LEN,
            "history_len": HIS_LEN, "negatives_per_positive": NPRATIO, "num_news": NUM_NEWS,
            "parallelism": f"dp{world} (one federated client per GPU)",
@@ -125,7 +126,7 @@ def finish(args, impl, rank, world, ms_per_step, e2e_ms, h2d, d2h, launches, clo
     cfg.update(extra_cfg)
     out = {"metric": "training impressions/sec/box", "value": round(value, 2), "unit": "impressions/s",
            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
-           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if impl == "ours" else "fp32",
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32" if impl == "reference" else "bf16",
            "data": "synthetic MIND-shaped impressions (Zipf news popularity), random-init weights",
            "impl": impl, "config": cfg, "clocks": clocks,
            "e2e": {"value": round(e2e_val, 2), "unit": "impressions/s", "ms_per_step": round(e2e_ms, 4),
@@ -135,6 +136,12 @@ def finish(args, impl, rank, world, ms_per_step, e2e_ms, h2d, d2h, launches, clo
 
 
 # ---- our framework -------------------------------------------------------------------------------------
+def pack_ids(torch, cand_h, his_h):
+    """[n, B*L + B*C] int32, histories first: the step's one input buffer (FusedStep.run_packed)."""
+    n = cand_h.shape[0]
+    return torch.cat([torch.from_numpy(his_h).reshape(n, -1), torch.from_numpy(cand_h).reshape(n, -1)], 1).to(torch.int32)
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -147,32 +154,36 @@ def run_ours(args):
     from fedrec_b200.config import FedRecConfig
     from fedrec_b200.engine.federated import FederatedRunner
     from fedrec_b200.ops import dispatch as D
+    from fedrec_b200.utils.readback import LaggedScalars
     cfg = FedRecConfig(mode=args.mode, local_steps=args.local_steps, average_frozen=args.average_frozen, batch_size=B_USERS, max_his_len=HIS_LEN, npratio=NPRATIO, title_len=TITLE_LEN,
                        num_news=NUM_NEWS, clip_norm=CLIP, noise_multiplier=SIGMA, synthetic=True, snapshot_path="",
                        log_dir="", transport=args.transport, num_train=8, num_valid=1, seed=1234,
-                       trunk_cache=args.trunk_cache,
+                       trunk_cache=args.trunk_cache, pipeline_optimizer=args.pipeline == "on",
+                       agg_timeout_s=args.agg_timeout_s, heartbeat_s=0.0, cuda_graph=args.graph == "on",
                        ln_fold={"on": True, "off": False}.get(args.ln_fold, FedRecConfig().ln_fold))
     news_index = synthetic_news_index(np)
     runner = FederatedRunner(cfg, news_index=news_index, nid2index={"<unk>": 0}, train_sam=[], valid_sam=[])
     dev = runner.device
     total = args.warmup + args.steps
     cand_h, his_h = make_batches(np, total, rank)
-    cand_pin = torch.from_numpy(cand_h).to(torch.int32).pin_memory()
-    his_pin = torch.from_numpy(his_h).to(torch.int32).pin_memory()
-    cand_d, his_d = cand_pin.to(dev), his_pin.to(dev)
+    ids_pin = pack_ids(torch, cand_h, his_h).pin_memory()           # [total, B*(L+C)] int32, pinned
+    ids_d = ids_pin.to(dev)
+    B, C, L = B_USERS, 1 + NPRATIO, HIS_LEN
 
     weights = runner.fedavg_weights()
     state = {"n": 0}
 
-    def one_step(c, h):
-        loss = runner.step.run(c, h, train=True)
+    def one_step(ids):
+        loss = runner.step.run_packed(ids, B, C, L)
         if args.mode == "grad_avg":                     # BASELINE.json config 2/4: average gradients, then Adam
-            c_ = runner.cfg
-            runner.grad_agg.allreduce_mean_and_adam_(c_.lr, c_.beta1, c_.beta2, c_.adam_eps)   # one kernel when W > 1
+            if not runner.pipelined:                    # pipelined: the step itself applies the previous update
+                c_ = runner.cfg
+                runner.grad_agg.allreduce_mean_and_adam_(c_.lr, c_.beta1, c_.beta2, c_.adam_eps)
         else:                                           # config 3: local Adam steps, FedAvg every `local_steps`
-            runner.model.adam_step()
+            runner._local_adam()
             state["n"] += 1
             if state["n"] % args.local_steps == 0:
+                runner.step.flush()
                 runner.param_agg.average_(runner.model.flat.param, weights)
                 if args.average_frozen:
                     runner._average_frozen(weights)
@@ -185,43 +196,137 @@ def run_ours(args):
 
     # ---- device-timed: ids already on the device ----
     for i in range(args.warmup):
-        one_step(cand_d[i], his_d[i])
+        one_step(ids_d[i])
+    runner.flush()
     barrier()
     sampler = ClockSampler(local_rank).start() if rank == 0 else None
     l0 = D.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for i in range(args.warmup, total):
-        loss = one_step(cand_d[i], his_d[i])
+        loss = one_step(ids_d[i])
+    runner.step.flush()                                 # the last step's update belongs to the timed region
     e1.record()
     barrier()
+    runner.flush()
     launches = D.launch_count() - l0
     ms = e0.elapsed_time(e1) / args.steps
-    # ---- end to end: pinned host ids in, loss out, every step ----
-    stage_c = torch.empty_like(cand_d[0]); stage_h = torch.empty_like(his_d[0])
+    # ---- end to end: pinned host ids in (one H2D copy per step), loss out to the host every step. The loss of step i is
+    #      read while step i+1 is already queued (utils/readback.py), so the host never drains the launch queue ----
+    lag = LaggedScalars(dev, lag=args.e2e_lag)
     barrier()
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     t0.record()
-    host_loss = 0.0
+    host_loss, n_read = 0.0, 0
     for i in range(args.warmup, total):
-        stage_c.copy_(cand_pin[i], non_blocking=True)
-        stage_h.copy_(his_pin[i], non_blocking=True)
-        host_loss = float(one_step(stage_c, stage_h).item())
+        v = lag.push(one_step(ids_pin[i]))
+        if v is not None:
+            host_loss, n_read = v, n_read + 1
+    runner.step.flush()
+    for v in lag.drain():
+        host_loss, n_read = v, n_read + 1
     t1.record()
     barrier()
+    runner.flush()
+    assert n_read == args.steps
     clocks = sampler.stop() if sampler else None
     e2e_ms = t0.elapsed_time(t1) / args.steps
-    h2d = cand_pin[0].numel() * 4 + his_pin[0].numel() * 4
+    h2d = ids_pin[0].numel() * 4
+    symm = runner.symm
     finish(args, "ours", rank, world, ms, e2e_ms, h2d, 4, launches, clocks,
            {"transport": runner.grad_agg.transport, "step_impl": runner.step.impl, "ln_fold": bool(cfg.ln_fold),
-            "last_loss": host_loss,
-            "peer_heap": (f"{runner.symm.backend}{'+nvls-multimem' if runner.symm.mc_ptr else ''}" if runner.symm else "none"),
+            "optimizer": ("pipelined into the next step's graph (aggregation + Adam beside the frozen trunk)"
+                          if runner.pipelined else "after the step"),
+            "e2e_loss_read_lag_steps": args.e2e_lag, "last_loss": host_loss,
+            "degraded": runner.degraded,
+            "peer_heap": (symm.describe() if symm else "none"),
             **({"trunk_cache": "ON — trunk outputs cached across steps; not comparable with the headline number"}
                if args.trunk_cache else {}),
             **({} if args.mode == "grad_avg" else
                {"mode": f"Parameter_Averaging_main: FedAvg every {args.local_steps} local steps"
                         f"{' incl. the frozen trunk (270 MB)' if args.average_frozen else ' (trainable state)'}"})})
     runner.close()
+
+
+# ---- strong baseline: this repo's algorithm on library kernels ---------------------------------------------------
+def run_torch(args):
+    """Same algorithm as ``ours`` (per-step de-dup, one batched frozen-trunk pass, no second trunk pass, clip + noise +
+    mean + Adam) on library kernels only: PyTorch modules under bf16 autocast (cuBLAS GEMMs, SDPA attention), NCCL
+    all-reduce, torch ops for clip/noise, torch.optim.Adam(fused). Isolates what the hand-written kernels earn."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": "torch", "unavailable": "no CUDA device visible"}))
+        return
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.step import TrainStep
+    from fedrec_b200.models import UserModel
+    from fedrec_b200.parallel import init_distributed
+    info = init_distributed()
+    dev = info.device
+    cfg = FedRecConfig(mode="grad_avg", batch_size=B_USERS, max_his_len=HIS_LEN, npratio=NPRATIO, title_len=TITLE_LEN,
+                       num_news=NUM_NEWS, clip_norm=CLIP, noise_multiplier=SIGMA, synthetic=True, snapshot_path="",
+                       log_dir="", transport="collective", seed=1234, fused=False)
+    torch.manual_seed(cfg.seed)
+    model = UserModel(None, synthetic_news_index(np), dev, config=cfg)
+    for mod in model.text_encoder.DistillBert.modules():
+        if hasattr(mod, "use_sdpa"):
+            mod.use_sdpa = True
+    step = TrainStep(model, cfg, impl="torch")
+    fl = model.flat
+    opt = torch.optim.Adam([p for p in model.parameters() if p.requires_grad], lr=cfg.lr, fused=True)
+    total = args.warmup + args.steps
+    cand_h, his_h = make_batches(np, total, rank)
+    cand_pin = torch.from_numpy(cand_h).pin_memory(); his_pin = torch.from_numpy(his_h).pin_memory()
+    cand_d, his_d = cand_pin.to(dev), his_pin.to(dev)
+    std = SIGMA * CLIP
+
+    def one_step(c, h):
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = step.run(c, h, train=True)
+        g = fl.grad
+        g.mul_(torch.clamp(CLIP / g.norm().clamp_min(1e-30), max=1.0))
+        g.add_(torch.randn_like(g), alpha=std)
+        if world > 1:
+            dist.all_reduce(g)
+            g.mul_(1.0 / world)
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        one_step(cand_d[i], his_d[i])
+    barrier()
+    sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.warmup, total):
+        one_step(cand_d[i], his_d[i])
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1) / args.steps
+    barrier()
+    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+    t0.record()
+    host_loss = 0.0
+    for i in range(args.warmup, total):
+        host_loss = float(one_step(cand_pin[i].to(dev, non_blocking=True), his_pin[i].to(dev, non_blocking=True)).item())
+    t1.record()
+    barrier()
+    clocks = sampler.stop() if sampler else None
+    h2d = (cand_pin[0].numel() + his_pin[0].numel()) * 8
+    finish(args, "torch", rank, world, ms, t0.elapsed_time(t1) / args.steps, h2d, 4, 0, clocks,
+           {"note": "this repo's algorithm (per-step de-dup, one frozen-trunk pass, head-only backward) on library kernels: "
+                    "PyTorch bf16 autocast (cuBLAS, SDPA), NCCL all-reduce, torch clip/noise, torch.optim.Adam(fused)",
+            "last_loss": host_loss})
+    if dist.is_initialized():
+        dist.destroy_process_group()
 
 
 # ---- the upstream code, unmodified, from baseline/_ref ---------------------------------------------------------
@@ -292,7 +397,14 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=None)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "torch"],
+                    help="ours = the sm_100a framework; reference = the unmodified upstream code; torch = this repo's "
+                         "algorithm on library kernels (strong baseline)")
+    ap.add_argument("--pipeline", choices=["on", "off"], default="on",
+                    help="apply step i's aggregation + Adam inside step i+1's graph, beside the frozen trunk")
+    ap.add_argument("--graph", choices=["on", "off"], default="on", help="replay the step from a CUDA graph")
+    ap.add_argument("--e2e_lag", type=int, default=1, help="steps between queuing a loss read-back and consuming it")
+    ap.add_argument("--agg_timeout_s", type=float, default=30.0)
     ap.add_argument("--transport", default="nvlink", choices=["nvlink", "collective"])
     ap.add_argument("--mode", default="grad_avg", choices=["grad_avg", "param_avg"],
                     help="grad_avg = BASELINE.json configs 2/4 (default, the headline); param_avg = config 3")
@@ -304,14 +416,13 @@ def main():
                     help="NOT the headline: keep trunk outputs of seen news resident in HBM (skips DistilBERT work for repeats)")
     args = ap.parse_args()
     if args.steps is None:
-        args.steps = 100 if args.impl == "ours" else 5
-    args.warmup = max(args.warmup, 3)
+        args.steps = {"ours": 200, "torch": 50}.get(args.impl, 5)
     if args.gpus > 1 and "RANK" not in os.environ:
         # convenience: re-launch under torch.distributed.run
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
                "--master-addr", "127.0.0.1", "--master-port", os.environ.get("MASTER_PORT", "29517"), __file__] + sys.argv[1:]
         raise SystemExit(subprocess.call(cmd))
-    (run_ours if args.impl == "ours" else run_reference)(args)
+    {"ours": run_ours, "reference": run_reference, "torch": run_torch}[args.impl](args)
 
 
 if __name__ == "__main__":

@@ -80,8 +80,12 @@ class FedRecConfig:
     snapshot_path: str = "snapshot.pt"
     log_dir: str = "logs"
     precomputed_news: bool = False  # BASELINE.json config 1: user encoder over cached news vectors
-    timeout_s: float = 1800.0
-    heartbeat_s: float = 0.0       # >0 enables the straggler/failure detector
+    timeout_s: float = 1800.0      # host-side waits: process group, store barriers (upstream: two days, client.py:227)
+    agg_timeout_s: float = 30.0    # in-kernel bound on waiting for a peer GPU; on expiry the run degrades to NCCL
+    agg_blocks: int = 0            # grid of the aggregation kernels (0 = default)
+    pipeline_optimizer: bool = True  # apply step i's aggregation + Adam at the start of step i+1, beside the frozen trunk
+    steps_per_epoch: int = 0       # 0 = one pass over the client's shard per epoch (upstream main.py:55-91)
+    heartbeat_s: float = 5.0       # straggler/failure detector period when world_size > 1 (0 = off)
 
     # ------------------------------------------------------------------------------
     @classmethod

@@ -68,7 +68,7 @@ class FederatedRunner:
             heap_mb = 64 + (288 if cfg.average_frozen else 0)       # the full fp32 state_dict is 257.6 MiB
             ok = torch.zeros(1, device=self.device)
             try:
-                self.symm = SymmetricHeap.create(self.info, heap_bytes=heap_mb << 20)
+                self.symm = SymmetricHeap.create(self.info, heap_bytes=heap_mb << 20, timeout_s=cfg.agg_timeout_s)
                 ok.fill_(1.0)
             except Exception as e:  # noqa: BLE001  (no peer access / IPC not permitted in this container)
                 print(f"[fedrec r{self.rank}] peer-mapped heap unavailable ({e}); aggregation falls back to NCCL", flush=True)
@@ -92,9 +92,20 @@ class FederatedRunner:
         self.step = None if self.is_server else TrainStep(self.model, cfg)
         transport = "nvlink" if self.symm is not None else "collective"
         participants = [r for r in range(self.W) if not (cfg.mode == "client_server" and self.W > 1 and r == cfg.server_rank)]
+        symm = self.symm
+        if self.W == 1 and self.device.type == "cuda" and cfg.transport == "nvlink" and cfg.fused:
+            from ..parallel.symm import SymmetricHeap
+            symm, transport = SymmetricHeap.single(self.device), "local"     # same kernel chain, no peers
+            self._local_pad = symm
         self.grad_agg = GradAggregator(self.model.flat, self.W, self.rank, transport, cfg.clip_norm,
-                                       cfg.noise_multiplier, cfg.seed, self.symm, participants=participants)
-        self.param_agg = ParamAggregator(self.W, self.rank, transport, self.symm)
+                                       cfg.noise_multiplier, cfg.seed, symm, participants=participants,
+                                       blocks=cfg.agg_blocks)
+        # rounds with long, uneven local phases (a server idling through the clients' epochs, snapshot writes) line the
+        # ranks up on the host before the kernel that waits for peers
+        self.param_agg = ParamAggregator(self.W, self.rank, "nvlink" if self.symm is not None else "collective",
+                                         self.symm, host_align=cfg.mode in ("client_server", "param_avg"),
+                                         timeout_s=cfg.timeout_s)
+        self.local_opt = None
         self.sampler = None
         if not self.is_server and train_sam:
             table = ImpressionTable(train_sam, nid2index, cfg.max_his_len)
@@ -105,6 +116,7 @@ class FederatedRunner:
         self.tracer = Tracer(enabled=os.environ.get("FEDREC_TRACE") == "1", device=self.device)
         self.faults = FaultInjector()
         self.heartbeat: Optional[Heartbeat] = None
+        self.degraded: Optional[str] = None
         if cfg.heartbeat_s > 0 and self.W > 1:
             store = dist.distributed_c10d._get_default_store()
             self.heartbeat = Heartbeat(store, self.rank, self.W, period_s=cfg.heartbeat_s,
@@ -119,6 +131,63 @@ class FederatedRunner:
             print(f"Resuming training from snapshot at Epoch {self.epochs_run}")
         if self.W > 1:
             self._sync_initial_state()
+        self._attach_optimizer()
+
+    # ---- optimiser placement ---------------------------------------------------------------------------
+    def _attach_optimizer(self) -> None:
+        """Pipeline the update into the step where the kernels allow it (fused step + device chain): gradient modes
+        use the cross-client chain, the local-step modes a one-rank chain (Adam only). Otherwise the loops below call
+        aggregation / Adam after each step, like upstream's ``model.update()`` (main.py:90)."""
+        cfg = self.cfg
+        self.pipelined = False
+        if self.step is None or not cfg.pipeline_optimizer:
+            return
+        if cfg.mode in ("ddp", "grad_avg"):
+            self.pipelined = self.step.attach_optimizer(self.grad_agg, cfg.lr, cfg.beta1, cfg.beta2, cfg.adam_eps)
+        elif self.step.impl == "fused":
+            from ..parallel.symm import SymmetricHeap
+            self.local_opt = GradAggregator(self.model.flat, 1, 0, "local", 0.0, 0.0, cfg.seed,
+                                            SymmetricHeap.single(self.device), blocks=cfg.agg_blocks)
+            self.pipelined = self.step.attach_optimizer(self.local_opt, cfg.lr, cfg.beta1, cfg.beta2, cfg.adam_eps)
+
+    def flush(self) -> None:
+        """Apply the update the pipelined step still owes and surface any aggregation failure."""
+        if self.step is not None:
+            self.step.flush()
+        if self.symm is not None:
+            self.symm.check()
+
+    def _local_adam(self) -> None:
+        if not self.pipelined:
+            self.model.adam_step()
+
+    def _degrade(self, err: Exception, epoch: int) -> int:
+        """A peer-memory aggregation gave up (a rank was late beyond ``agg_timeout_s``, or died). Every rank ends up
+        here: the abort word stops all chains. Agree on where to resume, put the pads back, continue over NCCL, and
+        re-synchronise weights and optimiser state from rank 0. Upstream: "if a client fails the entire training will
+        fail" (report p.4); here a late client costs the steps in flight."""
+        from ..parallel.comm import agree_max
+        print(f"[fedrec r{self.rank}] {err}; continuing with transport=collective", flush=True)
+        self.degraded = str(err)
+        resume = agree_max(epoch, "degrade", self.cfg.timeout_s)
+        if self.step is not None:
+            fused = self.step._fused
+            if fused is not None:
+                fused._pending = False
+                fused._opt = None
+                fused._graphs.clear()
+        self.pipelined = False
+        self.symm.reset()
+        self.grad_agg.degrade()
+        self.param_agg.degrade()
+        fl = self.model.flat
+        for t in (fl.param, fl.exp_avg, fl.exp_avg_sq):
+            dist.broadcast(t, src=0)
+        st = torch.tensor([fl.step], device=self.device, dtype=torch.int64)
+        dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        fl.step = int(st.item())
+        self.logger.log({"event": "transport_degraded", "reason": str(err), "resume_epoch": resume}, step=epoch)
+        return resume
 
     # ------------------------------------------------------------------------------------------
     def _on_stale(self, ranks: List[int]) -> None:
@@ -159,46 +228,86 @@ class FederatedRunner:
     def validate(self):
         if self.is_server or not self.valid_sam:
             return None
+        self.flush()
         return validate_impressions(self.step, self.model, self.valid_sam, self.nid2index)
 
     def save(self, epoch: int) -> None:
+        self.flush()
         ckpt.save_snapshot(self.cfg.snapshot_path, self.model, next_epoch=epoch + 1, rank=self.rank,
                            extra={"ROUND": self.round})
 
     # ---- modes ---------------------------------------------------------------------------------------
+    def steps_per_epoch(self) -> int:
+        """Steps in one epoch: ``cfg.steps_per_epoch`` if set, else one pass over this client's shard
+        (ceil(impressions / batch_size); upstream's epoch is a pass over its DataLoader, main.py:55-91,135-139)."""
+        if self.cfg.steps_per_epoch > 0:
+            return self.cfg.steps_per_epoch
+        n = len(self.sampler.table) if self.sampler is not None else 0
+        return max(1, -(-n // max(self.cfg.batch_size, 1)))
+
     def run_gradient_averaging(self) -> float:
+        from ..parallel.symm import AggregationError
         cfg = self.cfg
         loss = torch.zeros((), device=self.device)
-        for epoch in range(self.epochs_run, cfg.total_epochs):
-            self.faults.maybe_fire(self.rank, epoch)
-            loss = self.local_step()
-            with self.tracer.span("aggregate+adam"):          # one kernel over NVLink: clip, noise, mean and the Adam step
-                self.grad_agg.allreduce_mean_and_adam_(cfg.lr, cfg.beta1, cfg.beta2, cfg.adam_eps)
-            self.round += 1
-            if self.heartbeat:
-                self.heartbeat.beat(self.round)
-            self._end_of_epoch(epoch, loss, reduce_loss=cfg.mode == "grad_avg")
+        spe = self._agreed_steps_per_epoch()
+        epoch = self.epochs_run
+        while epoch < cfg.total_epochs:
+            try:
+                self.faults.maybe_fire(self.rank, epoch)
+                for _ in range(spe):
+                    loss = self.local_step()                  # pipelined: also applies the previous step's update
+                    if not self.pipelined:
+                        with self.tracer.span("aggregate+adam"):  # clip, noise, mean over NVLink and the Adam step
+                            self.grad_agg.allreduce_mean_and_adam_(cfg.lr, cfg.beta1, cfg.beta2, cfg.adam_eps)
+                    self.round += 1
+                    if self.heartbeat:
+                        self.heartbeat.beat(self.round)
+                self._end_of_epoch(epoch, loss, reduce_loss=cfg.mode == "grad_avg")
+                epoch += 1
+            except AggregationError as e:
+                epoch = self._degrade(e, epoch)
+        self.flush()
         return float(loss)
 
+    def _agreed_steps_per_epoch(self) -> int:
+        """Gradient modes step in lockstep: every client takes as many steps per epoch as the largest shard needs
+        (smaller shards wrap around)."""
+        spe = self.steps_per_epoch()
+        if self.W > 1:
+            t = torch.tensor([spe], device=self.device, dtype=torch.int64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            spe = int(t.item())
+        return spe
+
     def run_parameter_averaging(self) -> float:
+        from ..parallel.symm import AggregationError
         cfg = self.cfg
         loss = torch.zeros((), device=self.device)
         weights = self.fedavg_weights()
-        for epoch in range(self.epochs_run, cfg.total_epochs):
-            self.faults.maybe_fire(self.rank, epoch)
-            for _ in range(max(cfg.local_steps, 1)):
-                loss = self.local_step()
-                self.model.adam_step()
-            if (epoch + 1) % cfg.save_every == 0 and cfg.snapshot_path:
-                self.save(epoch)                                  # saved before averaging, as PA:140-141
-            with self.tracer.span("aggregate"):
-                self.param_agg.average_(self.model.flat.param, weights)
-                if cfg.average_frozen and self.W > 1:
-                    self._average_frozen(weights)
-            self.round += 1
-            if self.heartbeat:
-                self.heartbeat.beat(self.round)
-            self._end_of_epoch(epoch, loss, reduce_loss=False, save=False)
+        spe = self._agreed_steps_per_epoch()
+        epoch = self.epochs_run
+        while epoch < cfg.total_epochs:
+            try:
+                self.faults.maybe_fire(self.rank, epoch)
+                for it in range(spe):
+                    for _ in range(max(cfg.local_steps, 1)):
+                        loss = self.local_step()
+                        self._local_adam()
+                    self.flush()
+                    if it == spe - 1 and (epoch + 1) % cfg.save_every == 0 and cfg.snapshot_path:
+                        self.save(epoch)                              # saved before averaging, as PA:140-141
+                    with self.tracer.span("aggregate"):
+                        self.param_agg.average_(self.model.flat.param, weights)
+                        if cfg.average_frozen and self.W > 1:
+                            self._average_frozen(weights)
+                    self.round += 1
+                    if self.heartbeat:
+                        self.heartbeat.beat(self.round)
+                self._end_of_epoch(epoch, loss, reduce_loss=False, save=False)
+                epoch += 1
+            except AggregationError as e:
+                epoch = self._degrade(e, epoch)
+        self.flush()
         return float(loss)
 
     def _average_frozen(self, weights) -> None:
@@ -232,9 +341,10 @@ class FederatedRunner:
             self.faults.maybe_fire(self.rank, rnd)
             self.param_agg.broadcast_(self.model.flat.param, src)  # X8 model sync
             if not self.is_server:
-                for _ in range(max(cfg.total_epochs, 1)):
+                for _ in range(max(cfg.total_epochs, 1) * self.steps_per_epoch()):   # client.py:284: local epochs per round
                     loss = self.local_step()
-                    self.model.adam_step()
+                    self._local_adam()
+                self.flush()
                 v = self.validate()
                 rec = {"round": rnd, "training_loss": float(loss)}
                 if v:
@@ -283,6 +393,9 @@ class FederatedRunner:
         self.logger.log(rec, step=epoch)
         if save and cfg.snapshot_path and (epoch + 1) % cfg.save_every == 0:
             self.save(epoch)
+            if self.W > 1 and self.symm is not None and not self.degraded:
+                from ..parallel.comm import host_barrier
+                host_barrier("after-save", cfg.timeout_s)          # rank 0 wrote 270 MB: do not let the peers' kernels wait it out
 
     def run(self) -> float:
         mode = self.cfg.mode
@@ -298,6 +411,11 @@ class FederatedRunner:
             self.close()
 
     def close(self) -> None:
+        try:
+            if self.step is not None:
+                self.step.flush()
+        except Exception:  # noqa: BLE001  (closing after a failure must not raise again)
+            pass
         if self.heartbeat:
             self.heartbeat.stop()
         if self.tracer.enabled:

@@ -17,6 +17,7 @@ free of host synchronisation and can be captured in a CUDA graph.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Optional
 
 import torch
@@ -132,6 +133,47 @@ class FusedStep:
         self._dedup_ws: Optional[torch.Tensor] = None
         self._gen = torch.Generator(device=self.dev)
         self._gen.manual_seed(cfg.seed + 17)
+        # optimiser pipelined into the step (attach_optimizer): the chain that consumes step i's gradients runs at the
+        # start of step i+1 on its own high-priority branch, beside the frozen trunk
+        self._opt = None
+        # Normal priority on purpose: with a high-priority branch the captured graph (PDL edges between the trunk kernels,
+        # TMEM allocated before griddepcontrol.wait) deadlocked on a B200 (an attention CTA never got its TMEM); the same
+        # branch was fine with priority 0, with FEDREC_PDL=0, and without graph capture (profiles/pipeline_ab.md).
+        self._opt_stream = torch.cuda.Stream(device=self.dev, priority=int(os.environ.get("FEDREC_OPT_PRIORITY", "0")))
+        self._pending = False
+        self._opt_forked = False
+        self._side_forked = False
+
+    # ---- optimiser pipelined into the step -----------------------------------------------------------------
+    def attach_optimizer(self, grad_agg, lr: float, b1: float, b2: float, eps: float) -> None:
+        """From now on ``run(train=True)`` also *applies* the update: clip + noise + cross-client mean + Adam of step i
+        run at the start of step i+1 (or in ``flush()``), on a side branch next to the frozen trunk, which reads
+        nothing they write. The arithmetic and its order are those of "step, aggregate, Adam" run back to back
+        (upstream: model.update() after the batch loop, main.py:90; DDP overlapping its buckets, main.py:69-70).
+        ``grad_agg``: a ``GradAggregator`` with a device chain (transport nvlink or local)."""
+        assert grad_agg.on_device_chain, "the pipelined optimiser needs the nvlink or local transport"
+        self.flush()
+        self._opt = (grad_agg, float(lr), float(b1), float(b2), float(eps))
+        grad_agg.symm.set_step(self.model.flat.step)
+
+    def detach_optimizer(self) -> None:
+        self.flush()
+        self._opt = None
+
+    def _opt_chain(self, count: bool) -> None:
+        agg, lr, b1, b2, eps = self._opt
+        if count:
+            agg.chain_(lr, b1, b2, eps, gated=True)
+        else:                                   # warm-up / capture: launches only, host counters untouched
+            step, rnd = agg.flat.step, agg.round
+            agg.chain_(lr, b1, b2, eps, gated=True)
+            agg.flat.step, agg.round = step, rnd
+
+    def flush(self) -> None:
+        """Apply the update of the last step now (before anything reads the trainable weights or the run ends)."""
+        if self._opt is not None and self._pending:
+            self._opt_chain(count=True)
+            self._pending = False
 
     def repack_trunk(self) -> None:
         self.trunk.repack()
@@ -182,10 +224,17 @@ class FusedStep:
     def _fork(self):
         """Start a side branch that sees everything queued on the current stream so far."""
         self._side.wait_stream(torch.cuda.current_stream(self.dev))
+        self._side_forked = True
         return torch.cuda.stream(self._side)
 
     def _join(self) -> None:
-        torch.cuda.current_stream(self.dev).wait_stream(self._side)
+        cur = torch.cuda.current_stream(self.dev)
+        if self._side_forked:          # only branches that were forked from this stream (a capture admits no others)
+            cur.wait_stream(self._side)
+            self._side_forked = False
+        if self._opt_forked:
+            cur.wait_stream(self._opt_stream)
+            self._opt_forked = False
 
     # ---- buffers ---------------------------------------------------------------------------------
     def _buffers(self, K: int) -> Dict[str, torch.Tensor]:
@@ -213,7 +262,13 @@ class FusedStep:
 
     # ---- trunk + head forward ------------------------------------------------------------------------
     @torch.no_grad()
-    def encode(self, uniq: torch.Tensor, count: Optional[torch.Tensor], K: int, packed: bool = False) -> Dict[str, torch.Tensor]:
+    def encode(self, uniq: torch.Tensor, count: Optional[torch.Tensor], K: int) -> Dict[str, torch.Tensor]:
+        """Inference entry: pending optimiser work is applied first, then ``_encode``."""
+        self.flush()
+        return self._encode(uniq, count, K)
+
+    @torch.no_grad()
+    def _encode(self, uniq: torch.Tensor, count: Optional[torch.Tensor], K: int, packed: bool = False) -> Dict[str, torch.Tensor]:
         """``uniq`` int32 [K] news rows (first ``*count`` valid) → buffers with ``hidden`` (=x) and ``news_vecs``.
 
         ``packed=True`` means the caller already refreshed the bf16 weight copies on the side stream (joined here,
@@ -293,8 +348,9 @@ class FusedStep:
         last = tr.layers[-1]
         D.layernorm_bf16(y2, last["ln2_g"], last["ln2_b"], out=x, count=count, rows_per_item=T)
 
-    def _ids(self, cand, his):
-        ids = torch.cat([his.reshape(-1), cand.reshape(-1)]).to(torch.int32)
+    def _ids(self, cand, his, ids: Optional[torch.Tensor] = None):
+        if ids is None:
+            ids = torch.cat([his.reshape(-1), cand.reshape(-1)]).to(torch.int32)
         K = ids.numel()
         if self.cfg.dedup:
             need = ops.require_native().fr_dedup_workspace_ints(self.model.news_tokens.shape[0])
@@ -400,64 +456,134 @@ class FusedStep:
         self._join()                                         # every gradient is in the flat buffer
 
     # ---- full step -----------------------------------------------------------------------------------------
+    def _graph_key(self, B: int, C: int, L: int) -> tuple:
+        cfg = self.cfg      # everything a captured launch bakes in as a constant is part of the key
+        opt = None
+        if self._opt is not None:
+            agg = self._opt[0]
+            opt = (id(agg), agg.clip, agg.noise_std, len(agg.participants), bool(agg.symm.mc_ptr)) + self._opt[1:]
+        return (B, C, L, float(cfg.news_grad_noise), bool(cfg.mask_padding), bool(cfg.dedup), bool(cfg.trunk_cache),
+                bool(cfg.ln_fold), float(self.model.user_encoder.dropout_rate), opt)
+
     def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
         """One step. With ``cfg.cuda_graph`` the whole kernel sequence (≈90 launches) is captured once per batch
-        shape and replayed; ids are copied into the graph's static input buffers and a device-side counter salts
-        the dropout / noise streams so every replay draws fresh randomness."""
+        shape and replayed; the ids go into the graph's one static input buffer (histories first, then candidates)
+        and a device-side counter salts the dropout / noise streams so every replay draws fresh randomness.
+        With an attached optimiser (``attach_optimizer``) the step also applies the previous step's update."""
         if not (train and self.cfg.cuda_graph):
-            return self._run_eager(cand, his, train)
-        cfg = self.cfg      # everything a captured launch bakes in as a constant is part of the key
-        key = (tuple(cand.shape), tuple(his.shape), float(cfg.news_grad_noise), bool(cfg.mask_padding), bool(cfg.dedup),
-               bool(cfg.trunk_cache), bool(cfg.ln_fold), float(self.model.user_encoder.dropout_rate))
-        g = self._graphs.get(key)
-        if g is None:
-            g = self._capture(cand, his, key)
-        g["cand"].copy_(cand, non_blocking=True)
-        g["his"].copy_(his, non_blocking=True)
+            return self._step_eager(cand, his, train)
+        B, C = cand.shape
+        L = his.shape[1]
+        g = self._graph_for(B, C, L)
+        if cand.dtype == torch.int32 and his.dtype == torch.int32:
+            torch.cat((his.reshape(-1), cand.reshape(-1)), out=g["ids"])        # one kernel, no copy-engine hop
+        else:
+            g["ids"][: B * L].copy_(his.reshape(-1), non_blocking=True)
+            g["ids"][B * L:].copy_(cand.reshape(-1), non_blocking=True)
+        return self._replay(g)
+
+    def run_packed(self, ids: torch.Tensor, B: int, C: int, L: int) -> torch.Tensor:
+        """``run`` for callers that already hold the step's ids in the graph's input layout: int32 ``[B*L + B*C]``,
+        the B histories first, then the B candidate lists. ``ids`` may be pinned host memory: the step then starts
+        with exactly one host-to-device copy straight into the static buffer."""
+        assert ids.dtype == torch.int32 and ids.numel() == B * (L + C)
+        if not self.cfg.cuda_graph:
+            d = ids.to(self.dev, non_blocking=True)
+            return self._step_eager(d[B * L:].view(B, C), d[: B * L].view(B, L), True)
+        g = self._graph_for(B, C, L)
+        g["ids"].copy_(ids, non_blocking=True)
+        return self._replay(g)
+
+    def _count_update(self) -> None:
+        agg = self._opt[0]
+        agg.symm.check()
+        agg.round += 1
+        agg.flat.step += 1
+
+    def _replay(self, g) -> torch.Tensor:
+        pipelined = self._opt is not None
+        if pipelined and self._pending:
+            self._count_update()                        # this replay applies the previous step's update
         g["graph"].replay()
         D.count_launches(g["launches"])
+        if pipelined:
+            self._pending = True
         return g["loss"]
 
-    def _capture(self, cand, his, key):
-        static_c = torch.zeros(cand.shape, dtype=torch.int32, device=self.dev)
-        static_h = torch.zeros(his.shape, dtype=torch.int32, device=self.dev)
-        static_c.copy_(cand)
-        static_h.copy_(his)
+    def _step_eager(self, cand, his, train) -> torch.Tensor:
+        pipelined = train and self._opt is not None
+        if pipelined and self._pending:
+            self._count_update()
+        loss = self._run_eager(cand, his, train)
+        if pipelined:
+            self._pending = True
+        return loss
+
+    def _graph_for(self, B: int, C: int, L: int):
+        key = self._graph_key(B, C, L)
+        g = self._graphs.get(key)
+        if g is None:
+            g = self._capture(B, C, L, key)
+        return g
+
+    def _capture(self, B: int, C: int, L: int, key):
+        self.flush()                                        # no pending update may leak into the warm-up runs
+        ids = torch.ones(B * (L + C), dtype=torch.int32, device=self.dev)
+        static_h, static_c = ids[: B * L].view(B, L), ids[B * L:].view(B, C)
         side = torch.cuda.Stream(device=self.dev)
         side.wait_stream(torch.cuda.current_stream(self.dev))
-        with torch.cuda.stream(side):                       # warm-up: buffers, attributes, tensor maps
+        with torch.cuda.stream(side):                       # warm-up: buffers, attributes, tensor maps, module loads
             for _ in range(2):
-                self._run_eager(static_c, static_h, True)
+                self._run_eager(static_c, static_h, True, warm=True)
         torch.cuda.current_stream(self.dev).wait_stream(side)
         torch.cuda.synchronize(self.dev)
         graph = torch.cuda.CUDAGraph()
         n0 = D.launch_count()
         with torch.cuda.graph(graph):
-            loss = self._run_eager(static_c, static_h, True)
-        g = {"graph": graph, "cand": static_c, "his": static_h, "loss": loss, "launches": D.launch_count() - n0}
+            loss = self._run_eager(static_c, static_h, True, ids=ids)
+        g = {"graph": graph, "ids": ids, "cand": static_c, "his": static_h, "loss": loss,
+             "launches": D.launch_count() - n0}
         self._graphs[key] = g
         return g
 
     @torch.no_grad()
-    def _run_eager(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
+    def _run_eager(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True, warm: bool = False,
+                   ids: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """The step's launches on the current stream. ``warm``: a warm-up pass before capture — the optimiser chain is
+        launched (its kernels return at once: nothing is pending) but gradients are not marked pending.
+        ``ids``: the already concatenated int32 ids (histories, then candidates) when the caller has them."""
         m = self.model
         B, C = cand.shape
         L = his.shape[1]
         self._step_no += 1
         seed = self.cfg.seed * 1000003 + 3 * self._step_no
         D.counter_advance(self._seed_dev, 0x9E3779B97F4A7C15 & (2 ** 63 - 1))
-        with self._fork():                                   # trainable-weight copies: off the critical path
-            self._pack_weights(train)
-        ids, uniq, count, inv, K = self._ids(cand, his)
-        if train:
+        opt = self._opt if train else None
+        cur = torch.cuda.current_stream(self.dev)
+        if opt is not None:
+            # the previous step's update, then everything that depends on it (zeroed gradients, bf16 weight copies),
+            # on a high-priority branch beside the frozen trunk
+            self._opt_stream.wait_stream(cur)
+            with torch.cuda.stream(self._opt_stream):
+                self._opt_chain(count=False)
+                m.flat.zero_grad()
+                self._pack_weights(train)
+            self._opt_forked = True
+        else:
+            with self._fork():                               # trainable-weight copies: off the critical path
+                self._pack_weights(train)
+        ids, uniq, count, inv, K = self._ids(cand, his, ids)
+        if train and opt is None:
             m.flat.zero_grad()
-        b = self.encode(uniq, count, K, packed=True)
+        b = self._encode(uniq, count, K, packed=True)
         if train:
             b["d_news"].zero_()
         u, p, his_flat, use_mask = self._user_forward(b, inv, his, B, L, C, train, seed)
         if train:
             self._user_backward(u, b, inv, his_flat, use_mask, B, L, C, p, seed)
             self._text_head_backward(b, count if count is not None else None, K)
+            if opt is not None:
+                opt[0].symm.mark_pending(arm=not warm)       # gradients complete: arm the chain of the next step
         self.last_scores = u["score"]
         return u["loss"].clone()
 
@@ -469,9 +595,10 @@ class FusedStep:
         if B > chunk:
             return torch.cat([self.scores(cand[i:i + chunk], his[i:i + chunk], chunk) for i in range(0, B, chunk)])
         L = his.shape[1]
+        self.flush()
         with self._fork():
             self._pack_weights(False)
         ids, uniq, count, inv, K = self._ids(cand, his)
-        b = self.encode(uniq, count, K, packed=True)
+        b = self._encode(uniq, count, K, packed=True)
         u, _, _, _ = self._user_forward(b, inv, his, B, L, C, False, 0)
         return u["score"].clone()

@@ -57,6 +57,35 @@ class TrainStep:
             return self._fused.run(cand, his, train=train)
         return self._run_torch(cand, his, train)
 
+    # ---- optimiser pipelined into the step (fused implementation only) -------------------------------------------
+    def attach_optimizer(self, grad_agg, lr: float, b1: float, b2: float, eps: float) -> bool:
+        """Let ``run`` also apply the update (aggregation + Adam of step i at the start of step i+1, beside the frozen
+        trunk; ``flush`` applies the last one). Returns False when this step implementation cannot pipeline — the
+        caller then runs aggregation and Adam itself after every ``run``."""
+        if self._fused is None or not grad_agg.on_device_chain:
+            return False
+        self._fused.attach_optimizer(grad_agg, lr, b1, b2, eps)
+        return True
+
+    @property
+    def pipelined(self) -> bool:
+        return self._fused is not None and self._fused._opt is not None
+
+    def flush(self) -> None:
+        if self._fused is not None:
+            self._fused.flush()
+
+    def detach_optimizer(self) -> None:
+        if self._fused is not None:
+            self._fused.detach_optimizer()
+
+    def run_packed(self, ids: torch.Tensor, B: int, C: int, L: int) -> torch.Tensor:
+        """``run`` with the ids already in one int32 buffer ``[B*L + B*C]`` (histories first), device or pinned host."""
+        if self._fused is not None:
+            return self._fused.run_packed(ids, B, C, L)
+        d = ids.to(self.model.device)
+        return self._run_torch(d[B * L:].view(B, C), d[: B * L].view(B, L), True)
+
     def scores(self, cand: torch.Tensor, his: torch.Tensor) -> torch.Tensor:
         """Inference: ``sigmoid(cand · user)`` ``[B, C]`` without touching gradients."""
         if self._fused is not None:

@@ -63,6 +63,7 @@ class _SelfAttention(nn.Module):
         self.v_lin = nn.Linear(c.dim, c.dim)
         self.out_lin = nn.Linear(c.dim, c.dim)
         self.dropout = nn.Dropout(c.attention_dropout)
+        self.use_sdpa = False          # library attention (F.scaled_dot_product_attention) for the strong-baseline bench arm
 
     def forward(self, x: torch.Tensor, mask: Optional[torch.Tensor]) -> torch.Tensor:
         n, T, D = x.shape
@@ -70,6 +71,12 @@ class _SelfAttention(nn.Module):
 
         def split(t):
             return t.view(n, T, H, dh).transpose(1, 2)
+
+        if self.use_sdpa and not (self.training and self.dropout.p > 0):
+            am = None if mask is None else (mask != 0)[:, None, None, :]
+            ctx = F.scaled_dot_product_attention(split(self.q_lin(x)), split(self.k_lin(x)), split(self.v_lin(x)),
+                                                 attn_mask=am)
+            return self.out_lin(ctx.transpose(1, 2).reshape(n, T, D))
 
         q = split(self.q_lin(x)) / math.sqrt(dh)
         k = split(self.k_lin(x))

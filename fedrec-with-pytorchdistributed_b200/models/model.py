@@ -113,8 +113,18 @@ class UserModel(nn.Module):
         ids, vals = self._reduced_news_grads()
         return {int(i): v for i, v in zip(ids.tolist(), vals)}
 
+    def sync_optimizer(self) -> None:
+        """Apply an update the pipelined step still owes (engine/fused.py ``attach_optimizer``); no-op otherwise."""
+        if self._fused is not None:
+            self._fused.flush()
+
+    def state_dict(self, *args, **kwargs):
+        self.sync_optimizer()
+        return super().state_dict(*args, **kwargs)
+
     def adam_step(self) -> None:
         from .. import ops
+        self.sync_optimizer()
         ops.adam_flat(self.flat, self.cfg.lr, self.cfg.beta1, self.cfg.beta2, self.cfg.adam_eps)
 
     # ---- encoding ------------------------------------------------------------------
@@ -291,6 +301,7 @@ class UserModel(nn.Module):
         self.cnt += 1
 
     def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        self.sync_optimizer()
         out = super().load_state_dict(state_dict, strict=strict, assign=False)
         self.flat.rebind()
         if self.flat_frozen is not None:

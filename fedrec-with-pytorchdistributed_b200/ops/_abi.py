@@ -1,5 +1,5 @@
 """ctypes signatures of the C ABI in ``include/fedrec_b200.h`` (kept in the same order)."""
-from ctypes import (c_char_p, c_float, c_int, c_longlong, c_uint, c_ulonglong, c_void_p, POINTER)
+from ctypes import (c_char_p, c_double, c_float, c_int, c_longlong, c_uint, c_ulonglong, c_void_p, POINTER)
 
 P = c_void_p
 I = c_int
@@ -45,10 +45,18 @@ SIGNATURES = {
     # gemm_grad_sm100.cu
     "fr_gemm_grad_bf16": (I, [P, P, P, I, I, I, I, I, I, P, I, I, P]),
     # aggregate.cu
-    "fr_grad_allreduce": (I, [P, P, P, I, I, I, LL, c_uint, F, F, F, c_ulonglong, I, P]),
-    "fr_grad_allreduce_adam": (I, [P, P, P, I, I, I, LL, c_uint, F, F, F, c_ulonglong, P, P, P, F, F, F, F, F, F, I, P]),
-    "fr_param_average": (I, [P, P, P, P, I, I, I, LL, c_uint, I, P]),
+    "fr_agg_chain_launches": (I, [I, I, I, F, F, I, I]),
+    "fr_grad_allreduce": (I, [P, P, P, I, I, I, LL, F, F, F, c_ulonglong, I, I, LL, P, P]),
+    "fr_grad_allreduce_adam": (I, [P, P, P, I, I, I, LL, F, F, F, c_ulonglong, P, P, P, F, c_double, c_double, F, I, I, I,
+                                   LL, P, P]),
+    "fr_param_average": (I, [P, P, P, P, I, I, I, LL, I, LL, P, P]),
+    "fr_agg_mark_pending": (I, [P, I, I, P]),
+    "fr_agg_pad_read": (I, [P, P, I, I]),
+    "fr_agg_pad_set_step": (I, [P, c_uint]),
+    "fr_agg_pad_reset": (I, [P, I]),
     "fr_signal_pad_bytes": (I, []),
+    "fr_agg_errbuf_alloc": (I, [P, P]),
+    "fr_agg_errbuf_free": (I, [P]),
     "fr_symm_alloc": (I, [P, LL]),
     "fr_symm_free": (I, [P]),
     "fr_symm_export": (I, [P, P]),

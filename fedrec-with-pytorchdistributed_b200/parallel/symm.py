@@ -1,20 +1,40 @@
 """Symmetric (peer-mapped) memory runtime for the aggregation kernels.
 
 Each rank allocates one heap — a signal pad followed by a data region — with identical
-layout on every GPU, exports it through CUDA IPC, and maps every peer's heap into its own
-address space. The 64-byte IPC handles travel once over the regular process group
-(``all_gather_object``); after that the process group is not used by the aggregation paths.
-Tensors handed out by ``alloc_f32`` are ordinary torch tensors viewing the heap, so the flat
-parameter/gradient buffers of the model live directly in memory the peers can load from.
+layout on every GPU, exports it through CUDA IPC (or allocates it through the driver's
+VMM + multicast API), and maps every peer's heap into its own address space. The handles
+travel once over the regular process group; after that the process group is not used by
+the aggregation paths. Tensors handed out by ``alloc_f32`` are ordinary torch tensors
+viewing the heap, so the flat parameter/gradient buffers of the model live directly in
+memory the peers can load from.
+
+Upstream counterpart: none — its aggregation is gloo collectives per tensor
+(Parameter_Averaging_main.py:144-148), DDP buckets (main.py:117) and a TCP file upload
+(client.py:191-210). What must match is the behaviour "any world size just works".
+
+Robustness (round-2 redesign):
+
+* ranks are lined up on the **host** (store barrier, no GPU work) at ``finalize`` on both
+  backends, so the first in-kernel wait never has to cover process start-up skew;
+* ``finalize`` ends with a **self-test**: one tiny gradient all-reduce and one broadcast
+  with a 2 s in-kernel deadline, checked against the closed form and agreed on by all
+  ranks. If the NVLS (multimem) kernels fail it, the heap falls back to plain peer
+  loads/stores; if those fail too the caller falls back to NCCL — together, on every rank;
+* a cross-rank wait that runs out **reports** instead of trapping: the wait kernel writes
+  ``{rank, peer, phase, have, want}`` into a host-mapped record, raises the abort word in
+  every pad and returns; ``check()`` turns the record into ``AggregationError`` naming the
+  silent rank, and ``reset()`` brings all pads back to the initial state.
 
 ``SymmetricHeap.local(world)`` builds ``world`` heaps on the *current* GPU: the kernels then
-run all logical ranks inside one cooperative launch (``ranks_here = world``), which is how the
-single-GPU tests exercise the exact multi-rank code path without spinning kernels that wait on
-each other across launches.
+run all logical ranks as ``blockIdx.y`` slices of every launch (``ranks_here = world``),
+which is how the single-GPU tests exercise the exact multi-rank code path.
+``SymmetricHeap.single(device)`` is the one-rank case (a pad, no peers): the same chain
+then does clip + noise + Adam locally.
 """
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional, Sequence
 
 import torch
@@ -24,6 +44,22 @@ from ..ops.native import check, require_native
 from ..ops.dispatch import count_launches, stream_ptr
 
 _ALIGN = 256
+_SELFTEST_FLOATS = 4096
+_PHASES = {1: "arrival", 2: "completion"}
+
+
+class AggregationError(RuntimeError):
+    """An aggregation chain gave up waiting for a peer. ``rank`` waited for ``peer`` (-1: a peer raised the abort first)."""
+
+    def __init__(self, rank: int, peer: int, status: int, phase: int, have: int, want: int, waited_ms: int):
+        self.rank, self.peer, self.status, self.phase = rank, peer, status, phase
+        self.have, self.want, self.waited_ms = have, want, waited_ms
+        if status == 1:
+            msg = (f"rank {rank}: no {_PHASES.get(phase, '?')} signal from rank {peer} for aggregation #{want} after "
+                   f"{waited_ms} ms (last seen #{have}); that rank is late, stuck or dead")
+        else:
+            msg = f"rank {rank}: aggregation #{want} abandoned because a peer rank timed out waiting for another rank"
+        super().__init__(msg)
 
 
 class _RawCuda:
@@ -38,7 +74,7 @@ def _as_tensor(ptr: int, nbytes: int, device: torch.device) -> torch.Tensor:
 
 
 class SymmetricHeap:
-    def __init__(self, device: torch.device, rank: int, world: int, heap_bytes: int):
+    def __init__(self, device: torch.device, rank: int, world: int, heap_bytes: int, timeout_s: float = 30.0):
         self.lib = require_native()
         self.device, self.rank, self.W = device, rank, world
         self.pad_bytes = int(self.lib.fr_signal_pad_bytes())
@@ -47,37 +83,43 @@ class SymmetricHeap:
         self.peer_ptrs: List[int] = []
         self._imported: List[int] = []
         self._cursor = (self.pad_bytes + _ALIGN - 1) // _ALIGN * _ALIGN
-        self._epoch = 0
         self._local_heaps: Optional[List[int]] = None     # single-GPU emulation: all ranks' heaps are ours
         self._bytes_tensor: Optional[torch.Tensor] = None
         self.mc_ptr: int = 0
         self.backend = "ipc"
         self._vmm_handle = None
+        self.timeout_ms = int(timeout_s * 1000)
+        self._selftest: Optional[torch.Tensor] = None
+        self.selftest_note = ""
+        self._err_host = ctypes.c_void_p()
+        self._err_dev = ctypes.c_void_p()
+        with torch.cuda.device(device):
+            check(self.lib.fr_agg_errbuf_alloc(ctypes.byref(self._err_host), ctypes.byref(self._err_dev)), "fr_agg_errbuf_alloc")
+        self._err = (ctypes.c_int * 16).from_address(self._err_host.value)
 
     # ---- construction -----------------------------------------------------------------------------------
     @classmethod
-    def create(cls, info, heap_bytes: int = 64 << 20, backend: Optional[str] = None) -> "SymmetricHeap":
-        """``backend``: "ipc" (default; cudaMalloc + CUDA IPC, peer loads/stores) or "vmm" (driver VMM allocation through
+    def create(cls, info, heap_bytes: int = 64 << 20, backend: Optional[str] = None, timeout_s: float = 30.0) -> "SymmetricHeap":
+        """``backend``: "ipc" (cudaMalloc + CUDA IPC, peer loads/stores) or "vmm" (driver VMM allocation through
         ``torch.distributed._symmetric_memory``, which also yields an NVLS multicast mapping when the fabric supports
-        it, so the kernels switch to ``multimem.ld_reduce`` / ``multimem.st``). ``FEDREC_SYMM`` overrides."""
-        import os
+        it, so the kernels switch to ``multimem.ld_reduce`` / ``multimem.st``). ``FEDREC_SYMM`` overrides; "auto"
+        picks vmm from 4 ranks (measured: profiles/agg_sweep_w*.json) and verifies the choice in ``finalize``."""
         backend = backend or os.environ.get("FEDREC_SYMM", "auto")
         if backend == "auto":
-            # measured (profiles/agg_sweep_w*.json): with 2 ranks plain peer loads win; from 4 ranks on the in-switch
-            # reduction is as fast for small buffers and 20-30 % faster than both peer loads and NCCL for large ones
             backend = "vmm" if info.world_size >= 4 else "ipc"
             if backend == "vmm":
                 try:
-                    return cls.create(info, heap_bytes, backend="vmm")
+                    return cls.create(info, heap_bytes, backend="vmm", timeout_s=timeout_s)
                 except Exception as e:  # noqa: BLE001  (same outcome on every rank: API or fabric support is per box)
                     print(f"[fedrec r{info.rank}] VMM/multicast heap unavailable ({e}); using CUDA IPC", flush=True)
                     backend = "ipc"
-        h = cls(info.device, info.rank, info.world_size, heap_bytes)
+        h = cls(info.device, info.rank, info.world_size, heap_bytes, timeout_s)
         h.backend = backend
         if backend == "vmm":
             import torch.distributed._symmetric_memory as symm_mem
             t = symm_mem.empty(h.heap_bytes, dtype=torch.uint8, device=info.device)
             t.zero_()
+            torch.cuda.synchronize(info.device)
             hdl = symm_mem.rendezvous(t, dist.group.WORLD)
             h._vmm_handle = hdl
             h._bytes_tensor = t
@@ -85,52 +127,100 @@ class SymmetricHeap:
             h.peer_ptrs = [int(x) for x in hdl.buffer_ptrs]
             mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
             h.mc_ptr = mc if os.environ.get("FEDREC_NVLS", "1") != "0" else 0
-            torch.cuda.synchronize(info.device)
-            dist.barrier()
-            return h
-        p = ctypes.c_void_p()
-        with torch.cuda.device(info.device):
-            check(h.lib.fr_symm_alloc(ctypes.byref(p), h.heap_bytes), "fr_symm_alloc")
-        h.local_ptr = p.value
-        h._bytes_tensor = _as_tensor(h.local_ptr, h.heap_bytes, h.device)
+        else:
+            p = ctypes.c_void_p()
+            with torch.cuda.device(info.device):
+                check(h.lib.fr_symm_alloc(ctypes.byref(p), h.heap_bytes), "fr_symm_alloc")
+            h.local_ptr = p.value
+            h._bytes_tensor = _as_tensor(h.local_ptr, h.heap_bytes, h.device)
+        h._selftest = h.alloc_f32(_SELFTEST_FLOATS)       # same offset on every rank: first allocation after the pad
         return h
 
-    def finalize(self) -> None:
-        """Exchange IPC handles and map every peer's heap (collective over the default process group)."""
-        if self.peer_ptrs:
-            return
-        handle = ctypes.create_string_buffer(64)
-        check(self.lib.fr_symm_export(self.local_ptr, handle), "fr_symm_export")
-        gathered: List[Optional[bytes]] = [None] * self.W
-        dist.all_gather_object(gathered, handle.raw)
-        ptrs, err = [], None
-        with torch.cuda.device(self.device):
-            for r, raw in enumerate(gathered):
-                if r == self.rank:
-                    ptrs.append(self.local_ptr)
-                    continue
-                q = ctypes.c_void_p()
-                rc = self.lib.fr_symm_import(ctypes.create_string_buffer(raw, 64), ctypes.byref(q))
-                if rc != 0:
-                    err = f"mapping rank {r}'s heap failed: {self.lib.fr_last_error().decode()}"
-                    break
-                ptrs.append(q.value)
-                self._imported.append(q.value)
-        ok = torch.tensor([0.0 if err else 1.0], device=self.device)
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)           # all ranks map every peer, or nobody uses the heap
-        if float(ok) < 1.0:
-            raise RuntimeError(err or "a peer rank could not map this rank's heap (no peer access between the GPUs?)")
-        self.peer_ptrs = ptrs
+    def finalize(self, selftest: bool = True) -> None:
+        """Map every peer's heap (IPC backend), line the ranks up on the host, and prove the kernels work on this box.
+
+        Collective over the default process group. Raises ``RuntimeError`` on every rank together when the heap cannot
+        be used (no peer access, or the self-test fails even with plain peer loads); the caller then uses NCCL."""
+        from .comm import agree_all, host_barrier
+        if not self.peer_ptrs:
+            handle = ctypes.create_string_buffer(64)
+            check(self.lib.fr_symm_export(self.local_ptr, handle), "fr_symm_export")
+            gathered: List[Optional[bytes]] = [None] * self.W
+            dist.all_gather_object(gathered, handle.raw)
+            ptrs, err = [], None
+            with torch.cuda.device(self.device):
+                for r, raw in enumerate(gathered):
+                    if r == self.rank:
+                        ptrs.append(self.local_ptr)
+                        continue
+                    q = ctypes.c_void_p()
+                    rc = self.lib.fr_symm_import(ctypes.create_string_buffer(raw, 64), ctypes.byref(q))
+                    if rc != 0:
+                        err = f"mapping rank {r}'s heap failed: {self.lib.fr_last_error().decode()}"
+                        break
+                    ptrs.append(q.value)
+                    self._imported.append(q.value)
+            if not agree_all(err is None, "symm-map", self._host_timeout()):   # all ranks map every peer, or nobody uses the heap
+                raise RuntimeError(err or "a peer rank could not map this rank's heap (no peer access between the GPUs?)")
+            self.peer_ptrs = ptrs
+        # every rank has built its model and zeroed its buffers before anyone launches a kernel that waits for peers
         torch.cuda.synchronize(self.device)
-        dist.barrier()
+        host_barrier("symm-finalize", self._host_timeout())
+        if not selftest or os.environ.get("FEDREC_SYMM_SELFTEST", "1") == "0":
+            return
+        T = self._host_timeout()
+        if not agree_all(bool(self.mc_ptr), "symm-has-mc", T):
+            self.mc_ptr = 0                                   # multicast on every rank or on none
+        why = self._self_test()
+        ok = agree_all(why is None, "symm-selftest", T)
+        if not ok and self.mc_ptr:
+            print(f"[fedrec r{self.rank}] NVLS self-test failed ({why or 'on a peer rank'}); retrying with plain peer "
+                  f"loads/stores", flush=True)
+            self.selftest_note = f"nvls disabled: {why or 'self-test failed on a peer rank'}"
+            self.mc_ptr = 0
+            self.reset()
+            why = self._self_test()
+            ok = agree_all(why is None, "symm-selftest-p2p", T)
+        if not ok:
+            self.reset()
+            raise RuntimeError(f"aggregation self-test over peer memory failed ({why or 'on a peer rank'})")
+
+    def _host_timeout(self) -> float:
+        return float(os.environ.get("FEDREC_HOST_TIMEOUT_S", "1800"))
+
+    def _self_test(self) -> Optional[str]:
+        """One gradient mean and one broadcast on a 16 KB scratch buffer with a short deadline. None = passed."""
+        t, W = self._selftest, self.W
+        saved, self.timeout_ms = self.timeout_ms, int(float(os.environ.get("FEDREC_SELFTEST_TIMEOUT_S", "3")) * 1000)
+        try:
+            t.fill_(float(self.rank + 1))
+            torch.cuda.synchronize(self.device)
+            self.grad_allreduce_(t, clip=0.0, noise_std=0.0, seed=0, scale=1.0 / W)
+            self.check(sync=True)
+            want = (W + 1) / 2.0
+            if not torch.allclose(t, torch.full_like(t, want), rtol=1e-6, atol=0):
+                return f"mean of (1..{W}) came back as {float(t[0])}..{float(t[-1])}, expected {want}"
+            t.fill_(float(self.rank + 1))
+            w = [0.0] * W
+            w[W - 1] = 1.0
+            self.param_average_(t, w)
+            self.check(sync=True)
+            if not torch.equal(t, torch.full_like(t, float(W))):
+                return f"broadcast from rank {W - 1} came back as {float(t[0])}..{float(t[-1])}"
+            return None
+        except AggregationError as e:
+            return str(e)
+        finally:
+            self.timeout_ms = saved
 
     @classmethod
-    def local(cls, world: int, heap_bytes: int = 16 << 20, device: Optional[torch.device] = None) -> List["SymmetricHeap"]:
+    def local(cls, world: int, heap_bytes: int = 16 << 20, device: Optional[torch.device] = None,
+              timeout_s: float = 10.0) -> List["SymmetricHeap"]:
         """``world`` heaps on one GPU, each seeing all of them as peers (single-GPU emulation)."""
         device = device or torch.device("cuda", torch.cuda.current_device())
         heaps = []
         for r in range(world):
-            h = cls(device, r, world, heap_bytes)
+            h = cls(device, r, world, heap_bytes, timeout_s)
             p = ctypes.c_void_p()
             check(h.lib.fr_symm_alloc(ctypes.byref(p), heap_bytes), "fr_symm_alloc")
             h.local_ptr = p.value
@@ -141,6 +231,16 @@ class SymmetricHeap:
             h.peer_ptrs = list(ptrs)
             h._local_heaps = ptrs
         return heaps
+
+    @classmethod
+    def single(cls, device: torch.device) -> "SymmetricHeap":
+        """One rank, no peers: a pad so the same chain (clip + noise + Adam, device-side step counter) runs locally."""
+        h = cls(device, 0, 1, 4096)
+        h._bytes_tensor = torch.zeros(4096, dtype=torch.uint8, device=device)
+        h.local_ptr = h._bytes_tensor.data_ptr()
+        h.peer_ptrs = [h.local_ptr]
+        h.backend = "local"
+        return h
 
     # ---- allocation ----------------------------------------------------------------------------------------
     def alloc_f32(self, numel: int) -> torch.Tensor:
@@ -159,35 +259,94 @@ class SymmetricHeap:
             raise ValueError("tensor does not live in this symmetric heap")
         return off
 
+    # ---- failure reporting -------------------------------------------------------------------------------
+    def failed(self) -> bool:
+        """Has a wait kernel reported a failure? A plain host read of the mapped record: no synchronisation."""
+        return self._err[0] != 0
+
+    def check(self, sync: bool = False) -> None:
+        """Raise ``AggregationError`` if an aggregation chain gave up. ``sync=True`` first waits for the device."""
+        if sync:
+            torch.cuda.synchronize(self.device)
+        e = self._err
+        if e[0] != 0:
+            raise AggregationError(rank=e[1], peer=e[2], status=e[0], phase=e[3], have=e[4], want=e[5], waited_ms=e[6])
+
+    def reset(self, collective: bool = True) -> None:
+        """After a failed aggregation: wait for every rank (host barrier), put the pads back to their initial state and
+        clear the record. The step counter in the pad survives. ``collective=False`` skips the barriers (emulation)."""
+        from .comm import host_barrier
+        torch.cuda.synchronize(self.device)
+        if collective and self._local_heaps is None and self.W > 1:
+            host_barrier("symm-reset-a", self._host_timeout())
+        pads = self._local_heaps if self._local_heaps is not None else [self.local_ptr]
+        with torch.cuda.device(self.device):
+            for p in pads:
+                check(self.lib.fr_agg_pad_reset(ctypes.c_void_p(p), 1), "fr_agg_pad_reset")
+        for i in range(16):
+            self._err[i] = 0
+        torch.cuda.synchronize(self.device)
+        if collective and self._local_heaps is None and self.W > 1:
+            host_barrier("symm-reset-b", self._host_timeout())
+
+    def pad_words(self, first: int = 64, count: int = 16, rank: Optional[int] = None) -> List[int]:
+        """Debug/test view of this (or an emulated) rank's pad: epoch, sum of squares, counters, abort, pending, step."""
+        out = (ctypes.c_uint * count)()
+        ptr = self.peer_ptrs[self.rank if rank is None else rank]
+        check(self.lib.fr_agg_pad_read(ctypes.c_void_p(ptr), out, first, count), "fr_agg_pad_read")
+        return list(out)
+
+    def set_step(self, step: int) -> None:
+        """Device-side Adam step counter (used by gated chains, whose bias corrections cannot come from the host)."""
+        pads = self._local_heaps if self._local_heaps is not None else [self.local_ptr]
+        torch.cuda.synchronize(self.device)
+        for p in pads:
+            check(self.lib.fr_agg_pad_set_step(ctypes.c_void_p(p), int(step)), "fr_agg_pad_set_step")
+
     # ---- kernels ---------------------------------------------------------------------------------------------
-    def _ptr_arrays(self, off: int):
+    def _ptr_arrays(self, t: torch.Tensor):
+        if self.W == 1:
+            return (ctypes.c_void_p * 1)(t.data_ptr()), (ctypes.c_void_p * 1)(self.local_ptr), None
+        off = self.offset_of(t)
         bufs = (ctypes.c_void_p * self.W)(*[p + off for p in self.peer_ptrs])
         pads = (ctypes.c_void_p * self.W)(*self.peer_ptrs)
-        return bufs, pads
+        return bufs, pads, (self.mc_ptr + off) if self.mc_ptr else None
 
-    def _next_epoch(self) -> int:
-        self._epoch += 1
-        return self._epoch
+    def _err_arg(self):
+        return self._err_dev
+
+    def mark_pending(self, ranks_here: int = 1, arm: bool = True) -> None:
+        """The step's gradients are complete: arm the next gated chain (one tiny kernel on the current stream).
+        ``arm=False`` launches the kernel without arming (warm-up before a graph capture: every kernel a capture
+        launches has run once before, so nothing is loaded lazily inside the capture)."""
+        ptrs = self.peer_ptrs[:ranks_here] if ranks_here > 1 else [self.local_ptr]
+        for i in range(0, len(ptrs), 4):
+            chunk = ptrs[i:i + 4]
+            arr = (ctypes.c_void_p * len(chunk))(*chunk)
+            check(self.lib.fr_agg_mark_pending(arr, len(chunk), int(arm), stream_ptr(self.device)), "fr_agg_mark_pending")
+            count_launches(1)
 
     def grad_allreduce_(self, g: torch.Tensor, clip: float, noise_std: float, seed: int, scale: float,
-                        ranks_here: int = 1, blocks: int = 0) -> torch.Tensor:
+                        ranks_here: int = 1, blocks: int = 0, gated: bool = False) -> torch.Tensor:
         assert self.peer_ptrs, "call finalize() first"
-        bufs, pads = self._ptr_arrays(self.offset_of(g))
+        bufs, pads, mc = self._ptr_arrays(g)
         n = (g.numel() + 3) // 4 * 4
-        check(self.lib.fr_grad_allreduce(bufs, pads, (self.mc_ptr + self.offset_of(g)) if self.mc_ptr else None, self.W, self.rank if ranks_here == 1 else 0,
-                                         ranks_here, n, self._next_epoch(), float(clip), float(noise_std), float(scale),
-                                         int(seed) & (2 ** 64 - 1), blocks, stream_ptr(self.device)), "fr_grad_allreduce")
-        count_launches(1)
+        check(self.lib.fr_grad_allreduce(bufs, pads, mc, self.W, self.rank if ranks_here == 1 else 0, ranks_here, n,
+                                         float(clip), float(noise_std), float(scale), int(seed) & (2 ** 64 - 1),
+                                         int(gated), blocks, self.timeout_ms, self._err_arg(), stream_ptr(self.device)),
+              "fr_grad_allreduce")
+        count_launches(self.lib.fr_agg_chain_launches(self.W, 0, int(bool(mc)), float(clip), float(noise_std), 1, 0))
         return g
 
     def grad_allreduce_adam_(self, g: torch.Tensor, clip: float, noise_std: float, seed: int, scale: float,
                              params, exp_avg, exp_avg_sq, step: int, lr: float, b1: float, b2: float, eps: float,
-                             ranks_here: int = 1, blocks: int = 0) -> torch.Tensor:
-        """``grad_allreduce_`` + one Adam step in the same kernel. ``params`` / ``exp_avg`` / ``exp_avg_sq`` are this
-        rank's flat fp32 buffers (or, with ``ranks_here > 1``, lists with one entry per emulated rank); ``step`` is the
-        1-based step count after this update."""
+                             ranks_here: int = 1, blocks: int = 0, gated: bool = False) -> torch.Tensor:
+        """Clip + noise + NVLink mean, then one Adam step on the result, as one chain of kernels on the current stream.
+        ``params`` / ``exp_avg`` / ``exp_avg_sq`` are this rank's flat fp32 buffers (or, with ``ranks_here > 1``, lists
+        with one entry per emulated rank); ``step`` is the 1-based step count after this update, or 0 to use the
+        device-side counter (``set_step``; required for chains replayed from a CUDA graph)."""
         assert self.peer_ptrs, "call finalize() first"
-        bufs, pads = self._ptr_arrays(self.offset_of(g))
+        bufs, pads, mc = self._ptr_arrays(g)
         n = (g.numel() + 3) // 4 * 4
 
         def arr(x):
@@ -199,23 +358,28 @@ class SymmetricHeap:
                 slots[base + i] = t.data_ptr()
             return (ctypes.c_void_p * self.W)(*slots)
         check(self.lib.fr_grad_allreduce_adam(
-            bufs, pads, (self.mc_ptr + self.offset_of(g)) if self.mc_ptr else None, self.W,
-            self.rank if ranks_here == 1 else 0, ranks_here, n, self._next_epoch(), float(clip), float(noise_std),
+            bufs, pads, mc, self.W, self.rank if ranks_here == 1 else 0, ranks_here, n, float(clip), float(noise_std),
             float(scale), int(seed) & (2 ** 64 - 1), arr(params), arr(exp_avg), arr(exp_avg_sq), float(lr), float(b1),
-            float(b2), float(eps), 1.0 - b1 ** step, 1.0 - b2 ** step, blocks, stream_ptr(self.device)),
-            "fr_grad_allreduce_adam")
-        count_launches(1)
+            float(b2), float(eps), int(step), int(gated), blocks, self.timeout_ms, self._err_arg(),
+            stream_ptr(self.device)), "fr_grad_allreduce_adam")
+        count_launches(self.lib.fr_agg_chain_launches(self.W, 0, int(bool(mc)), float(clip), float(noise_std), 1, 1))
         return g
 
     def param_average_(self, buf: torch.Tensor, weights: Sequence[float], ranks_here: int = 1, blocks: int = 0) -> torch.Tensor:
         assert self.peer_ptrs, "call finalize() first"
-        bufs, pads = self._ptr_arrays(self.offset_of(buf))
+        bufs, pads, mc = self._ptr_arrays(buf)
         w = (ctypes.c_float * self.W)(*[float(x) for x in weights])
         n = (buf.numel() + 3) // 4 * 4
-        check(self.lib.fr_param_average(bufs, pads, (self.mc_ptr + self.offset_of(buf)) if self.mc_ptr else None, w, self.W, self.rank if ranks_here == 1 else 0,
-                                        ranks_here, n, self._next_epoch(), blocks, stream_ptr(self.device)), "fr_param_average")
-        count_launches(1)
+        check(self.lib.fr_param_average(bufs, pads, mc, w, self.W, self.rank if ranks_here == 1 else 0, ranks_here, n,
+                                        blocks, self.timeout_ms, self._err_arg(), stream_ptr(self.device)),
+              "fr_param_average")
+        uniform = int(all(float(x) == float(weights[0]) for x in weights))
+        count_launches(self.lib.fr_agg_chain_launches(self.W, 1, int(bool(mc)), 0.0, 0.0, uniform, 0))
         return buf
+
+    def describe(self) -> str:
+        s = self.backend + ("+nvls-multimem" if self.mc_ptr else "")
+        return s + (f" ({self.selftest_note})" if self.selftest_note else "")
 
     def close(self) -> None:
         if self.local_ptr == 0:

@@ -150,27 +150,54 @@ int fr_transpose_cast(const float* in, void* out, int R, int Ccols, int ld_out, 
 
 /* Every rank owns one fp32 buffer of n floats and one signal pad (fr_signal_pad_bytes(), zero-initialised) in
  * peer-mapped memory; bufs_host[i]/pads_host[i] are THIS process's mappings of rank i's. mc_buf: NVLS multicast
- * mapping of the buffers or NULL (plain peer loads/stores). epoch: > 0 and increasing by one per call on a pad
- * set (shared by both functions). ranks_here = 1 normally (rank = rank_base); ranks_here > 1 runs that many
- * logical ranks inside one cooperative launch on the local GPU (single-GPU testing). blocks <= 0 = default.
+ * mapping of the buffers or NULL (plain peer loads/stores). ranks_here = 1 normally (rank = rank_base);
+ * ranks_here > 1 runs that many logical ranks as blockIdx.y slices of every launch on the local GPU (single-GPU
+ * testing). blocks <= 0 = default grid. Every rank must issue the same sequence of aggregations: the epoch
+ * counter lives in the pad, not on the host, so every function below is capturable in a CUDA graph.
+ *
+ * One call enqueues a short chain of kernels on `stream` (sum of squares, publish, wait, reduce, wait, Adam,
+ * commit; see csrc/aggregate.cu). The only place a rank waits for its peers is a one-warp wait kernel with a
+ * %globaltimer deadline of timeout_ms (0 = for ever). On expiry it fills the host-mapped record err_mapped
+ * (fr_agg_errbuf_alloc: int[16] = {status, rank, peer, phase, have, want, waited_ms}; status 1 = my wait ran
+ * out, 2 = a peer gave up first), raises the abort word in every pad so that all ranks stop together, and the
+ * rest of the chain does nothing; nothing traps. After such a failure call fr_agg_pad_reset on every rank
+ * (no kernel in flight) before the pads are used again. gated != 0: the chain runs only if fr_agg_mark_pending
+ * ran on the stream since the previous gated chain (software-pipelined training steps).
  *
  * fr_grad_allreduce: buf_r <- scale * sum_i [ buf_i * min(1, clip/||buf_i||) + N(0, noise_std^2) ] on every rank.
  *   Replaces DDP's gradient all-reduce and Gradient_Averaging_main.py:146; noise: client.py:87-89.
  * fr_param_average: buf_r <- sum_i weights_host[i] * buf_i on every rank (weighted FedAvg + redistribution).
  *   Replaces Parameter_Averaging_main.py:144-148, server.py:37-55,76-77 and client.py:261-264. */
 int fr_grad_allreduce(void* const* bufs_host, void* const* pads_host, void* mc_buf, int W, int rank_base,
-                      int ranks_here, long long n, unsigned epoch, float clip, float noise_std, float scale,
-                      unsigned long long seed, int blocks, void* stream);
-/* fr_grad_allreduce with the optimiser fused in: after the averaged gradient has arrived, the same kernel applies one Adam
- * step (torch.optim.Adam defaults) to each local rank's flat parameters. params/m/v_host: W pointers (only the local ranks'
- * entries are read), bc1 = 1 - b1^t, bc2 = 1 - b2^t. Replaces DDP all-reduce + model.py:89,93 (two Adam steps). */
+                      int ranks_here, long long n, float clip, float noise_std, float scale, unsigned long long seed,
+                      int gated, int blocks, long long timeout_ms, void* err_mapped, void* stream);
+/* fr_grad_allreduce followed on the same stream by one Adam step (torch.optim.Adam defaults) of each local rank's flat
+ * parameters on the averaged gradient. params/m/v_host: W pointers (only the local ranks' entries are read). step > 0:
+ * 1-based step count for the bias corrections; step == 0: the pad's device-side counter (fr_agg_pad_set_step), which
+ * the chain advances itself. W == 1 is allowed (clip + noise + Adam locally, pads_host[0] = any zeroed pad).
+ * Replaces DDP all-reduce + model.py:89,93 (two Adam steps). */
 int fr_grad_allreduce_adam(void* const* bufs_host, void* const* pads_host, void* mc_buf, int W, int rank_base,
-                           int ranks_here, long long n, unsigned epoch, float clip, float noise_std, float scale,
+                           int ranks_here, long long n, float clip, float noise_std, float scale,
                            unsigned long long seed, void* const* params_host, void* const* m_host, void* const* v_host,
-                           float lr, float b1, float b2, float eps, float bc1, float bc2, int blocks, void* stream);
+                           float lr, double b1, double b2, float eps, int step, int gated, int blocks,
+                           long long timeout_ms, void* err_mapped, void* stream);
 int fr_param_average(void* const* bufs_host, void* const* pads_host, void* mc_buf, const float* weights_host, int W,
-                     int rank_base, int ranks_here, long long n, unsigned epoch, int blocks, void* stream);
+                     int rank_base, int ranks_here, long long n, int blocks, long long timeout_ms, void* err_mapped,
+                     void* stream);
+/* Kernels one chain launches for this configuration (launch accounting). */
+int fr_agg_chain_launches(int W, int mode, int nvls, float clip, float noise_std, int uniform_weights, int adam);
+/* Arm the next gated chain of up to 4 local pads (one 1-warp kernel; arm == 0 only launches it, for warm-up passes
+ * before a graph capture). No upstream counterpart: upstream applies its optimiser inline (model.py:66-70). */
+int fr_agg_mark_pending(void* const* pads_host, int count, int arm, void* stream);
+/* Synchronous host-side pad access for set-up, recovery and tests: read words [first, first+count), set the Adam
+ * step counter, reset a pad to its initial state (keep_step != 0 preserves the step counter). */
+int fr_agg_pad_read(const void* pad, unsigned* out_words_host, int first, int count);
+int fr_agg_pad_set_step(void* pad, unsigned step);
+int fr_agg_pad_reset(void* pad, int keep_step);
 int fr_signal_pad_bytes(void);
+/* Host-mapped error record (int[16]) the wait kernels report into: *host_out for the CPU, *dev_out for err_mapped. */
+int fr_agg_errbuf_alloc(void** host_out_host, void** dev_out_host);
+int fr_agg_errbuf_free(void* host_ptr_host);
 
 /* Peer-mappable allocations through CUDA IPC: alloc (zeroed), export a 64-byte handle, import a peer's handle
  * (enables peer access lazily), close an imported mapping, free. Replaces init_process_group's role as the

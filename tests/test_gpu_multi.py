@@ -32,9 +32,9 @@ def _worker(rank, world, port, q):
     try:
         cfg = FedRecConfig(mode="grad_avg", synthetic=True, num_news=2000, num_train=64, num_valid=8, title_len=30,
                            batch_size=8, total_epochs=2, dropout=0.0, clip_norm=2.0, noise_multiplier=0.0,
-                           snapshot_path="", log_dir="", transport="nvlink")
+                           snapshot_path="", log_dir="", transport="nvlink", pipeline_optimizer=False, heartbeat_s=0.0)
         r = FederatedRunner(cfg)
-        assert r.symm is not None and r.grad_agg.transport == "nvlink"
+        assert r.symm is not None and r.grad_agg.transport == "nvlink" and not r.pipelined
         r.local_step()
         g = r.model.flat.grad
         mine = g.clone()
@@ -69,6 +69,218 @@ def _worker(rank, world, port, q):
         import traceback
         res["error"] = f"{e}\n{traceback.format_exc()}"
     q.put((rank, res))
+
+
+def _worlds():
+    n = torch.cuda.device_count() if torch.cuda.is_available() else 0
+    return [w for w in (2, 4, 8) if w <= n] or [2]
+
+
+def _spawn(target, world, *args, timeout=600):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=target, args=(r, world, port, q) + args) for r in range(world)]
+    [p.start() for p in procs]
+    try:
+        out = dict(q.get(timeout=timeout) for _ in range(world))
+    finally:
+        [p.join(60) for p in procs]
+        [p.kill() for p in procs if p.is_alive()]
+    for r in range(world):
+        assert "error" not in out[r], out[r].get("error")
+    return out
+
+
+def _worker_numerics(rank, world, port, q, backend, nvls):
+    """The aggregation kernels against NCCL + PyTorch on real peers: clip exactness with mixed clipped/unclipped ranks,
+    noise statistics, three Adam steps against torch.optim.Adam, weighted FedAvg with a zero-weight rank, broadcast."""
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port), FEDREC_SYMM=backend, FEDREC_NVLS="1" if nvls else "0")
+    import math
+    import torch.distributed as dist
+    from fedrec_b200.parallel import init_distributed
+    from fedrec_b200.parallel.symm import SymmetricHeap
+    res = {}
+    try:
+        info = init_distributed()
+        dev = info.device
+        N = 1_164_896
+        heap = SymmetricHeap.create(info, heap_bytes=32 << 20, timeout_s=20.0)
+        g = heap.alloc_f32(N)
+        heap.finalize()
+        res["heap"] = heap.describe()
+        res["nvls"] = bool(heap.mc_ptr)
+        W = world
+        torch.manual_seed(100 + rank)
+        # (i) clip only, mixed clipped / unclipped ranks: exact against NCCL
+        clip = 2.0
+        src = torch.randn(N, device=dev) * (0.0005 if rank % 2 else 0.01)
+        sc = min(1.0, clip / float(src.norm()))
+        flags = torch.tensor([float(sc < 1.0), float(sc == 1.0)], device=dev)
+        dist.all_reduce(flags)
+        res["mixed"] = bool(flags[0] > 0 and flags[1] > 0)
+        want = src * sc
+        dist.all_reduce(want)
+        want /= W
+        g.copy_(src)
+        torch.cuda.synchronize(); dist.barrier()
+        heap.grad_allreduce_(g, clip=clip, noise_std=0.0, seed=5, scale=1.0 / W)
+        heap.check(sync=True)
+        res["clip_max_abs_err"] = float((g - want).abs().max())
+        res["clip_rel_err"] = float((g - want).norm() / want.norm())
+        # (ii) noise on: mean / variance of (result - exact), identical on every rank
+        std = 0.05 * clip
+        dist.barrier()
+        g.copy_(src)
+        torch.cuda.synchronize(); dist.barrier()
+        heap.grad_allreduce_(g, clip=clip, noise_std=std, seed=6, scale=1.0 / W)
+        heap.check(sync=True)
+        noise = g - want
+        res["noise_mean"] = float(noise.mean())
+        res["noise_std_ratio"] = float(noise.std()) / (std / math.sqrt(W))
+        res["noise_mean_bound"] = 5 * std / math.sqrt(W * N)
+        gathered = [torch.zeros_like(g) for _ in range(W)]
+        dist.all_gather(gathered, g)
+        res["noise_identical"] = all(torch.equal(gathered[0], x) for x in gathered)
+        # (iii) three aggregation + Adam steps against torch.optim.Adam on the NCCL mean
+        p = torch.randn(N, device=dev, generator=torch.Generator(device=dev).manual_seed(7))
+        m, v = torch.zeros(N, device=dev), torch.zeros(N, device=dev)
+        ref = torch.nn.Parameter(p.clone())
+        opt = torch.optim.Adam([ref], lr=5e-5)
+        for step in (1, 2, 3):
+            src = torch.randn(N, device=dev) * 0.01 * (1 + rank)
+            want = src.clone()
+            dist.all_reduce(want)
+            want /= W
+            dist.barrier()
+            g.copy_(src)
+            torch.cuda.synchronize(); dist.barrier()
+            heap.grad_allreduce_adam_(g, clip=0.0, noise_std=0.0, seed=1, scale=1.0 / W, params=p, exp_avg=m,
+                                      exp_avg_sq=v, step=step, lr=5e-5, b1=0.9, b2=0.999, eps=1e-8)
+            heap.check(sync=True)
+            ref.grad = want.clone()
+            opt.step()
+        res["adam_max_abs_err"] = float((p - ref.data).abs().max())
+        res["adam_grad_err"] = float((g - want).abs().max())
+        # (iv) FedAvg with unequal weights and a zero-weight (server) rank, then a one-hot broadcast
+        w = [float(i + 1) for i in range(W)]
+        w[1] = 0.0
+        tot = sum(w)
+        src = torch.randn(N, device=dev)
+        wantp = src * (w[rank] / tot)
+        dist.all_reduce(wantp)
+        dist.barrier()
+        g.copy_(src)
+        torch.cuda.synchronize(); dist.barrier()
+        heap.param_average_(g, [x / tot for x in w])
+        heap.check(sync=True)
+        res["fedavg_max_abs_err"] = float((g - wantp).abs().max())
+        onehot = [0.0] * W
+        onehot[W - 1] = 1.0
+        wantb = src.clone()
+        dist.broadcast(wantb, src=W - 1)
+        dist.barrier()
+        g.copy_(src)
+        torch.cuda.synchronize(); dist.barrier()
+        heap.param_average_(g, onehot)
+        heap.check(sync=True)
+        res["broadcast_exact"] = bool(torch.equal(g, wantb))
+        # uniform weights (the upstream mean, Parameter_Averaging_main.py:144-148)
+        wantu = src.clone()
+        dist.all_reduce(wantu)
+        wantu /= W
+        dist.barrier()
+        g.copy_(src)
+        torch.cuda.synchronize(); dist.barrier()
+        heap.param_average_(g, [1.0 / W] * W)
+        heap.check(sync=True)
+        res["uniform_max_abs_err"] = float((g - wantu).abs().max())
+        dist.barrier()
+        heap.close()
+        dist.destroy_process_group()
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        res["error"] = f"{e}\n{traceback.format_exc()}"
+    q.put((rank, res))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("backend,nvls", [("ipc", False), ("vmm", False), ("vmm", True)])
+@pytest.mark.parametrize("world", _worlds())
+def test_aggregation_kernels_match_nccl_and_torch(world, backend, nvls):
+    out = _spawn(_worker_numerics, world, backend, nvls)
+    print(f"W={world} requested {backend} nvls={nvls}: heap = {out[0]['heap']}")
+    for r in range(world):
+        o = out[r]
+        assert o["mixed"], "the test needs both clipped and unclipped ranks"
+        assert o["clip_max_abs_err"] < 2e-7 and o["clip_rel_err"] < 1e-5, o
+        assert abs(o["noise_mean"]) < o["noise_mean_bound"] and abs(o["noise_std_ratio"] - 1.0) < 0.02, o
+        assert o["noise_identical"], o
+        assert o["adam_max_abs_err"] < 2e-6 and o["adam_grad_err"] < 2e-7, o
+        assert o["fedavg_max_abs_err"] < 2e-6 and o["uniform_max_abs_err"] < 2e-6 and o["broadcast_exact"], o
+    if nvls and world >= 2:
+        assert out[0]["nvls"] or "nvls disabled" in out[0]["heap"], out[0]
+
+
+def _worker_bench_loop(rank, world, port, q, backend, nvls, fault):
+    """The driver's scaling bench in small: FederatedRunner in gradient mode, pipelined step, 25 rounds."""
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port), FEDREC_SYMM=backend, FEDREC_NVLS="1" if nvls else "0")
+    if fault:
+        os.environ["FEDREC_FAULT"] = fault
+    import torch.distributed as dist
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    res = {}
+    try:
+        cfg = FedRecConfig(mode="grad_avg", synthetic=True, num_news=2000, num_train=64, num_valid=8, title_len=30,
+                           batch_size=8, total_epochs=25, steps_per_epoch=1, dropout=0.0, clip_norm=2.0,
+                           noise_multiplier=0.0, snapshot_path="", log_dir="", transport="nvlink",
+                           agg_timeout_s=2.0 if fault else 20.0, heartbeat_s=0.0)
+        r = FederatedRunner(cfg)
+        res["heap"] = r.symm.describe() if r.symm is not None else "none"
+        res["pipelined"] = bool(r.pipelined)
+        loss = r.run_gradient_averaging()
+        res["loss"] = loss
+        res["degraded"] = r.degraded
+        res["transport"] = r.grad_agg.transport
+        res["step"] = r.model.flat.step
+        p = r.model.flat.param
+        gathered = [torch.zeros_like(p) for _ in range(world)]
+        dist.all_gather(gathered, p)
+        res["identical"] = all(torch.equal(gathered[0], x) for x in gathered)
+        r.close()
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        res["error"] = f"{e}\n{traceback.format_exc()}"
+    q.put((rank, res))
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+@pytest.mark.parametrize("world", _worlds())
+def test_bench_loop_runs_at_every_world_size(world):
+    """the shipped default configuration at every world size the box offers (auto heap backend)."""
+    out = _spawn(_worker_bench_loop, world, "auto", True, "")
+    print(f"W={world}: heap = {out[0]['heap']}, pipelined = {out[0]['pipelined']}")
+    for r in range(world):
+        o = out[r]
+        assert o["loss"] == o["loss"] and o["degraded"] is None and o["transport"] == "nvlink", o
+        assert o["identical"] and o["step"] == 25 and o["pipelined"], o
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_a_slow_rank_is_named_and_training_completes_over_nccl():
+    """FEDREC_FAULT delays rank 1 by 8 s at round 3 with a 2 s in-kernel deadline: the others name rank 1, every rank
+    falls back to the collective transport together, and the run finishes with identical weights."""
+    out = _spawn(_worker_bench_loop, 2, "ipc", False, "delay:1:3:8")
+    for r in range(2):
+        o = out[r]
+        assert o["degraded"] is not None and o["transport"] == "collective", o
+        assert o["identical"] and o["loss"] == o["loss"], o
+    assert "rank 1" in out[0]["degraded"], out[0]["degraded"]
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")

@@ -130,3 +130,62 @@ def test_captured_graph_follows_trunk_weight_changes():
     assert abs(float(la) - l0) > 1e-6                                   # the change was visible at all
     rel = float((a.flat.grad - b.flat.grad).norm() / b.flat.grad.norm())
     assert rel < 5e-2, rel
+
+
+@pytest.mark.parametrize("graph", [True, False], ids=["graph", "eager"])
+def test_pipelined_optimizer_equals_step_then_aggregate_then_adam(graph):
+    """attach_optimizer moves clip + Adam of step i to the start of step i+1 (beside the frozen trunk). Same arithmetic
+    in the same order as running them back to back: weights and losses must agree to fp32 rounding of the atomics."""
+    from fedrec_b200.parallel import GradAggregator
+    from fedrec_b200.parallel.symm import SymmetricHeap
+    a, b = _models(cuda_graph=graph)
+    a.cfg.lr = b.cfg.lr = 1e-3
+    pipe, seq = TrainStep(a, impl="fused"), TrainStep(b, impl="fused")
+    agg_a = GradAggregator(a.flat, 1, 0, "local", clip_norm=0.05, noise_multiplier=0.0, seed=3, symm=SymmetricHeap.single(a.device))
+    agg_b = GradAggregator(b.flat, 1, 0, "local", clip_norm=0.05, noise_multiplier=0.0, seed=3, symm=SymmetricHeap.single(b.device))
+    assert pipe.attach_optimizer(agg_a, 1e-3, 0.9, 0.999, 1e-8) and pipe.pipelined
+    g = torch.Generator(device=DEV).manual_seed(11)
+    for it in range(5):
+        cand = torch.randint(1, 600, (6, 5), device=DEV, generator=g, dtype=torch.int32)
+        his = torch.randint(0, 600, (6, 50), device=DEV, generator=g, dtype=torch.int32)
+        la = float(pipe.run(cand, his))
+        lb = float(seq.run(cand, his))
+        agg_b.allreduce_mean_and_adam_(1e-3, 0.9, 0.999, 1e-8)
+        assert la == pytest.approx(lb, abs=2e-4), it
+    assert a.flat.step == 4 and b.flat.step == 5           # the pipelined model still owes the last update
+    pipe.flush()
+    pipe.flush()                                           # idempotent
+    torch.cuda.synchronize()
+    assert a.flat.step == 5
+    assert agg_a.symm.pad_words(73, 1)[0] == 5             # device-side step counter agrees
+    # The first moment is linear in the gradients: it must agree to the rounding of the atomics in the gradient
+    # accumulation. The weights themselves are compared in bulk: Adam divides by sqrt(v), so a coordinate whose gradient
+    # is rounding noise (the cancellation-prone text-head fc1) moves by +-lr whichever way that rounding went.
+    rel_m = float((a.flat.exp_avg - b.flat.exp_avg).norm() / b.flat.exp_avg.norm())
+    assert rel_m < 1e-3, rel_m
+    rel_v = float((a.flat.exp_avg_sq - b.flat.exp_avg_sq).norm() / b.flat.exp_avg_sq.norm())
+    assert rel_v < 1e-3, rel_v
+    diff = (a.flat.param - b.flat.param).abs()
+    assert float(diff.max()) < 5e-3 and float((diff > 2e-5).float().mean()) < 1e-2, (float(diff.max()), float((diff > 2e-5).float().mean()))
+    rel_p = float((a.flat.param - b.flat.param).norm() / b.flat.param.norm())
+    assert rel_p < 1e-4, rel_p
+    # inference and checkpoints see the flushed weights
+    cand = torch.randint(1, 600, (6, 5), device=DEV, generator=g, dtype=torch.int32)
+    his = torch.randint(0, 600, (6, 50), device=DEV, generator=g, dtype=torch.int32)
+    pipe.run(cand, his); seq.run(cand, his); agg_b.allreduce_mean_and_adam_(1e-3, 0.9, 0.999, 1e-8)
+    torch.testing.assert_close(pipe.scores(cand, his), seq.scores(cand, his), atol=1e-4, rtol=1e-3)
+    assert a.flat.step == 6
+
+
+def test_run_packed_takes_pinned_host_ids():
+    a, b = _models()
+    fa, fb = TrainStep(a, impl="fused"), TrainStep(b, impl="fused")
+    g = torch.Generator(device=DEV).manual_seed(12)
+    cand = torch.randint(1, 600, (6, 5), device=DEV, generator=g, dtype=torch.int32)
+    his = torch.randint(0, 600, (6, 50), device=DEV, generator=g, dtype=torch.int32)
+    ids = torch.cat([his.reshape(-1), cand.reshape(-1)]).cpu().pin_memory()
+    la = float(fa.run_packed(ids, 6, 5, 50))
+    lb = float(fb.run(cand, his))
+    assert la == pytest.approx(lb, abs=1e-5)
+    rel = float((a.flat.grad - b.flat.grad).norm() / b.flat.grad.norm())
+    assert rel < 1e-4, rel
