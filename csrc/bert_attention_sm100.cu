@@ -170,9 +170,15 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
       const int njob = job + 1;
       const bool has_next = njob < job_end;
       const int ntile = njob / heads, nh = njob - ntile * heads;
-      mbar_wait(bar_qk, ph_qk);
-      ph_qk ^= 1;
+      // Only the MMA-issuing thread consumes Q/K, so only it waits for them. Round 1 had every thread wait here: thread 0
+      // could then pass, run S = QK^T, and re-arm this barrier for the next job (load_qk below) before a slower warp had
+      // looked at it; once that second phase completed, the parity the slow warp was polling for read "not yet" again,
+      // the warp never left, and thread 0 stopped at the __syncthreads below: a hang that needed an unlucky few
+      // microseconds of warp scheduling (measured: 1 run in 3 with a high-priority branch sharing the SMs; consistent with
+      // the round-1 4-GPU scaling failure, where one rank sat in a step kernel while its peers timed out waiting for it).
+      // bar_mma is waited on by everyone, but its two completions per job are separated by a __syncthreads each.
       if (tid == 0) {
+        mbar_wait(bar_qk, ph_qk, 1);
         tc_fence_after();
         constexpr uint32_t id1 = att_idesc(128, 128, 0);
         const uint32_t q = smem_u32(sQ), k = smem_u32(sK);
@@ -181,7 +187,8 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
           umma_bf16_ss(tS, att_desc_k_sw128(q + ks * 32), att_desc_k_sw128(k + ks * 32), id1, ks > 0);
         umma_commit(bar_mma);
       }
-      mbar_wait(bar_mma, ph_mma);
+      ph_qk ^= 1;
+      mbar_wait(bar_mma, ph_mma, 2);
       ph_mma ^= 1;
       tc_fence_after();
       if (tid == 0 && has_next) load_qk(ntile, nh);          // sQ / sK are free again
@@ -233,7 +240,7 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
       tc_fence_before();
       __syncthreads();
       if (tid == 0) {
-        mbar_wait(bar_v, ph_v);
+        mbar_wait(bar_v, ph_v, 3);
         tc_fence_after();
         constexpr uint32_t id2 = att_idesc(128, 64, 1);
         const uint32_t pa = smem_u32(sP), v = smem_u32(sV);
@@ -243,7 +250,7 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
         umma_commit(bar_mma);
       }
       ph_v ^= 1;
-      mbar_wait(bar_mma, ph_mma);
+      mbar_wait(bar_mma, ph_mma, 4);
       ph_mma ^= 1;
       tc_fence_after();
       if (tid == 0 && has_next) load_v(ntile, nh);           // sV is free again

@@ -97,7 +97,7 @@ gemm_grad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(&empty_bar[stage], phase ^ 1);
+        mbar_wait(&empty_bar[stage], phase ^ 1, 21);
         uint8_t* sa = smem + stage * kStageBytes;
         uint8_t* sb = sa + kABytes;
         mbar_arrive_expect_tx(&full_bar[stage], kStageBytes);
@@ -113,7 +113,7 @@ gemm_grad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       constexpr uint32_t idesc = make_idesc_bf16_mn(GBM, BN);
       int stage = 0; uint32_t phase = 0;
       for (int kb = kb0; kb < kb1; ++kb) {
-        mbar_wait(&full_bar[stage], phase);
+        mbar_wait(&full_bar[stage], phase, 22);
         tc_fence_after();
         const uint32_t sa = smem_u32(smem + stage * kStageBytes);
         const uint32_t sb = sa + kABytes;
@@ -131,7 +131,7 @@ gemm_grad_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   } else {
     const int quarter = warp & 3;
-    mbar_wait(done_bar, 0);
+    mbar_wait(done_bar, 0, 23);
     tc_fence_after();
     const int row = m0 + quarter * 32 + lane;
 #pragma unroll 1

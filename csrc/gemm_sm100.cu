@@ -179,7 +179,7 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         const int m0 = (tile / n_blocks) * (BM * CG) + (int)cta_rank * BM;
         const int n0 = (tile % n_blocks) * BN + (int)cta_rank * (BN / CG) * (CG - 1);
         for (int kb = 0; kb < k_blocks; ++kb) {
-          mbar_wait(&empty_bar[stage], phase ^ 1);
+          mbar_wait(&empty_bar[stage], phase ^ 1, 11);
           uint8_t* sa = smem + stage * C::kStageBytes;
           uint8_t* sb = sa + C::kABytes;
           if (CG == 2) {
@@ -206,11 +206,11 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
-        mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+        mbar_wait(&tmem_empty[acc], acc_phase ^ 1, 12);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
         for (int kb = 0; kb < k_blocks; ++kb) {
-          mbar_wait(&full_bar[stage], phase);
+          mbar_wait(&full_bar[stage], phase, 13);
           tc_fence_after();
           const uint32_t sa = smem_u32(smem + stage * C::kStageBytes);
           const uint64_t da = make_smem_desc_sw128(sa);
@@ -330,11 +330,11 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           }
         }
       }
-      mbar_wait(&tmem_full[acc], acc_phase);
+      mbar_wait(&tmem_full[acc], acc_phase, 14);
       tc_fence_after();
       if (work) {
         if (TMA_EPI && EPI == EPI_BIAS_RESID) {
-          mbar_wait(&resid_bar[ew], rphase);
+          mbar_wait(&resid_bar[ew], rphase, 15);
           rphase ^= 1;
         }
         uint32_t packed[kCols / 2];                          // bf16x2 results of the whole slice (TMA path)

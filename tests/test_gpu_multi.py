@@ -72,8 +72,10 @@ def _worker(rank, world, port, q):
 
 
 def _worlds():
+    """World sizes this box offers; FEDREC_TEST_WORLDS=8 (comma-separated) narrows the list to save GPU time."""
     n = torch.cuda.device_count() if torch.cuda.is_available() else 0
-    return [w for w in (2, 4, 8) if w <= n] or [2]
+    want = [int(x) for x in os.environ.get("FEDREC_TEST_WORLDS", "2,4,8").split(",") if x]
+    return [w for w in want if w <= n] or [2]
 
 
 def _spawn(target, world, *args, timeout=600):
