@@ -154,7 +154,6 @@ def run_ours(args):
     from fedrec_b200.config import FedRecConfig
     from fedrec_b200.engine.federated import FederatedRunner
     from fedrec_b200.ops import dispatch as D
-    from fedrec_b200.utils.readback import LaggedScalars
     cfg = FedRecConfig(mode=args.mode, local_steps=args.local_steps, average_frozen=args.average_frozen, batch_size=B_USERS, max_his_len=HIS_LEN, npratio=NPRATIO, title_len=TITLE_LEN,
                        num_news=NUM_NEWS, clip_norm=CLIP, noise_multiplier=SIGMA, synthetic=True, snapshot_path="",
                        log_dir="", transport=args.transport, num_train=8, num_valid=1, seed=1234,
@@ -211,20 +210,46 @@ def run_ours(args):
     runner.flush()
     launches = D.launch_count() - l0
     ms = e0.elapsed_time(e1) / args.steps
-    # ---- end to end: pinned host ids in (one H2D copy per step), loss out to the host every step. The loss of step i is
-    #      read while step i+1 is already queued (utils/readback.py), so the host never drains the launch queue ----
-    lag = LaggedScalars(dev, lag=args.e2e_lag)
+    # ---- end to end through the public API (TrainStep.run_host / loss_of): every step the ids travel from pinned host
+    #      memory to the device (pulled over PCIe by the step's first kernel) and the step's loss travels back into host
+    #      memory (pushed by its last kernel) where the host reads it. The host reads the loss of step i while step
+    #      i + e2e_lag is already queued, so it never drains the launch queue ----
+    from collections import deque
+    ids_host = ids_pin.numpy()
+    step = runner.step
+    step.enable_host_io(B, C, L, slots=max(4, args.e2e_lag + 2))
+
+    def one_step_host(i):
+        t = step.run_host(ids_host[i])
+        if args.mode == "grad_avg":
+            if not runner.pipelined:
+                c_ = runner.cfg
+                runner.grad_agg.allreduce_mean_and_adam_(c_.lr, c_.beta1, c_.beta2, c_.adam_eps)
+        else:
+            runner._local_adam()
+            state["n"] += 1
+            if state["n"] % args.local_steps == 0:
+                runner.step.flush()
+                runner.param_agg.average_(runner.model.flat.param, weights)
+                if args.average_frozen:
+                    runner._average_frozen(weights)
+        return t
+
+    for i in range(min(args.warmup, 3)):                # captures the host-I/O variant of the graph
+        step.loss_of(one_step_host(i))
+    runner.flush()
     barrier()
+    tickets = deque()
     t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
     t0.record()
     host_loss, n_read = 0.0, 0
     for i in range(args.warmup, total):
-        v = lag.push(one_step(ids_pin[i]))
-        if v is not None:
-            host_loss, n_read = v, n_read + 1
+        tickets.append(one_step_host(i))
+        if len(tickets) > args.e2e_lag:
+            host_loss, n_read = step.loss_of(tickets.popleft()), n_read + 1
     runner.step.flush()
-    for v in lag.drain():
-        host_loss, n_read = v, n_read + 1
+    while tickets:
+        host_loss, n_read = step.loss_of(tickets.popleft()), n_read + 1
     t1.record()
     barrier()
     runner.flush()
@@ -233,7 +258,7 @@ def run_ours(args):
     e2e_ms = t0.elapsed_time(t1) / args.steps
     h2d = ids_pin[0].numel() * 4
     symm = runner.symm
-    finish(args, "ours", rank, world, ms, e2e_ms, h2d, 4, launches, clocks,
+    finish(args, "ours", rank, world, ms, e2e_ms, h2d, 8, launches, clocks,
            {"transport": runner.grad_agg.transport, "step_impl": runner.step.impl, "ln_fold": bool(cfg.ln_fold),
             "optimizer": ("pipelined into the next step's graph (aggregation + Adam beside the frozen trunk)"
                           if runner.pipelined else "after the step"),

@@ -5,6 +5,7 @@
 // Reference behaviour being replaced: model.py:121-126 (bmm, sigmoid, CrossEntropyLoss),
 // main.py:20-42 (Python dict segment-sum), model.py:22-23,89,93 (two torch Adam steps).
 #include "common.cuh"
+#include <string.h>
 
 namespace fr {
 
@@ -410,6 +411,61 @@ FR_API int fr_dedup_static(const int* ids, int K, int N, int* uniq, int* count, 
   dedup_scan_kernel<<<1, 1024, 0, s>>>(block_counts, nb, count);
   dedup_compact_kernel<<<nb, kDedupBlock, 0, s>>>(flag, N, block_counts, uniq);
   dedup_inverse_kernel<<<(K + 255) / 256, 256, 0, s>>>(ids, K, N, flag, inv, count, uniq);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Host I/O of a training step without copy-engine hops or CUDA API calls per step.
+//
+// The reference moves every batch and every result through blocking copies inside its batch loop (main.py:59-64,
+// 72-79, 90). Here the step's ids wait in a small ring of slots in host-mapped pinned memory; the first kernel of the
+// (captured) step pulls this step's slot over PCIe into the step's static id buffer, and the last kernel pushes
+// {loss, sequence number} back into a second host-mapped ring that the host polls. Which slot is a function of a
+// device-side step counter, so the very same launches replay from a CUDA graph. The host must stay fewer than
+// `slots` steps ahead of the device (engine/fused.py enforces that by waiting on the result ring).
+// ---------------------------------------------------------------------------------------------------------
+namespace fr {
+__global__ void __launch_bounds__(1024) hostio_fetch_kernel(int* __restrict__ dst, const int* __restrict__ ring, int n,
+                                                             int slots, unsigned long long* step_ctr) {
+  const unsigned long long s = *reinterpret_cast<volatile unsigned long long*>(step_ctr);
+  const int* src = ring + (size_t)(s % (unsigned long long)slots) * (size_t)n;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = __ldcv(src + i);     // host memory: never cached
+  __syncthreads();
+  if (threadIdx.x == 0) *step_ctr = s + 1ull;
+}
+__global__ void hostio_publish_kernel(volatile unsigned* out_ring, const float* __restrict__ value, int slots,
+                                      const unsigned long long* step_ctr) {
+  const unsigned long long seq = *step_ctr;                    // 1-based number of the step that just finished
+  volatile unsigned* slot = out_ring + 4 * (size_t)((seq - 1ull) % (unsigned long long)slots);
+  slot[0] = __float_as_uint(*value);
+  __threadfence_system();
+  slot[1] = (unsigned)seq;
+}
+}  // namespace fr
+
+FR_API int fr_host_mapped_alloc(long long bytes, void** host_out, void** dev_out) {
+  FR_REQUIRE(bytes > 0, "fr_host_mapped_alloc: bytes=%lld", bytes);
+  void* h = nullptr;
+  FR_CHECK(cudaHostAlloc(&h, (size_t)bytes, cudaHostAllocMapped | cudaHostAllocPortable));
+  memset(h, 0, (size_t)bytes);
+  void* d = nullptr;
+  FR_CHECK(cudaHostGetDevicePointer(&d, h, 0));
+  *host_out = h; *dev_out = d;
+  return 0;
+}
+FR_API int fr_host_mapped_free(void* host) { FR_CHECK(cudaFreeHost(host)); return 0; }
+
+FR_API int fr_hostio_fetch(int* dst, const int* ring_mapped, int n, int slots, unsigned long long* step_ctr, void* stream) {
+  FR_REQUIRE(n >= 1 && slots >= 1, "fr_hostio_fetch: n=%d slots=%d", n, slots);
+  hostio_fetch_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(dst, ring_mapped, n, slots, step_ctr);
+  FR_LAUNCH_CHECK();
+  return 0;
+}
+FR_API int fr_hostio_publish(void* out_ring_mapped, const float* value, int slots, const unsigned long long* step_ctr,
+                             void* stream) {
+  FR_REQUIRE(slots >= 1, "fr_hostio_publish: slots=%d", slots);
+  hostio_publish_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((volatile unsigned*)out_ring_mapped, value, slots, step_ctr);
   FR_LAUNCH_CHECK();
   return 0;
 }

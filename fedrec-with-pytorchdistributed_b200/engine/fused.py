@@ -143,6 +143,7 @@ class FusedStep:
         self._pending = False
         self._opt_forked = False
         self._side_forked = False
+        self._io = None                 # host-mapped rings for run_host / loss_of (enable_host_io)
 
     # ---- optimiser pipelined into the step -----------------------------------------------------------------
     def attach_optimizer(self, grad_agg, lr: float, b1: float, b2: float, eps: float) -> None:
@@ -455,15 +456,71 @@ class FusedStep:
         D.gemm_grad(b["d_pre"], b["x"], g("text_encoder.additive_attention.att_fc1.weight"), k_dev=count, k_scale=T)
         self._join()                                         # every gradient is in the flat buffer
 
+    # ---- host I/O through host-mapped rings --------------------------------------------------------------------
+    def enable_host_io(self, n_ids: int, slots: int = 4) -> None:
+        """Rings in pinned, device-visible host memory: ``slots`` x ``n_ids`` int32 going in, ``slots`` x {loss, sequence
+        number} coming out. The captured step starts with a kernel that pulls its slot over PCIe and ends with one that
+        pushes the loss back, so a step costs the host one memcpy into pinned memory, one graph launch and a poll of
+        host memory: no copy-engine hop, no event, no stream synchronisation."""
+        import ctypes
+        import numpy as np
+        lib = ops.require_native()
+        if self._io is not None and self._io["n"] == n_ids and self._io["slots"] == slots:
+            return
+        assert self._io is None, "host I/O rings are sized once"
+        hp, dp = ctypes.c_void_p(), ctypes.c_void_p()
+        ho, do = ctypes.c_void_p(), ctypes.c_void_p()
+        with torch.cuda.device(self.dev):
+            D.check(lib.fr_host_mapped_alloc(slots * n_ids * 4, ctypes.byref(hp), ctypes.byref(dp)), "fr_host_mapped_alloc")
+            D.check(lib.fr_host_mapped_alloc(slots * 16, ctypes.byref(ho), ctypes.byref(do)), "fr_host_mapped_alloc")
+        ring = np.ctypeslib.as_array((ctypes.c_int32 * (slots * n_ids)).from_address(hp.value)).reshape(slots, n_ids)
+        out = np.ctypeslib.as_array((ctypes.c_uint32 * (slots * 4)).from_address(ho.value)).reshape(slots, 4)
+        self._io = {"n": n_ids, "slots": slots, "ring": ring, "ring_dev": dp.value, "out": out, "out_dev": do.value,
+                    "ctr": torch.zeros(1, dtype=torch.int64, device=self.dev), "issued": 0, "confirmed": 0}
+
+    def run_host(self, ids, B: int, C: int, L: int) -> int:
+        """One training step whose ids come from host memory (``ids``: int32 ``[B*L + B*C]``, histories first; numpy or
+        CPU tensor). Returns a ticket for ``loss_of``. Call ``enable_host_io`` first. The host may run at most
+        ``slots - 1`` steps ahead of the results it has read; beyond that this call waits for the oldest one."""
+        import numpy as np
+        io = self._io
+        assert io is not None and io["n"] == B * (L + C), "enable_host_io(B * (L + C)) first"
+        if io["issued"] - io["confirmed"] >= io["slots"] - 1:
+            self.loss_of(io["confirmed"] + 1)
+        src = ids.numpy() if isinstance(ids, torch.Tensor) else np.asarray(ids)
+        np.copyto(io["ring"][io["issued"] % io["slots"]], src.reshape(-1), casting="no")
+        io["issued"] += 1
+        if self.cfg.cuda_graph:
+            self._replay(self._graph_for(B, C, L, hostio=True))
+        else:
+            self._step_eager(None, None, True, hostio=(B, C, L))
+        return io["issued"]
+
+    def loss_of(self, ticket: int, timeout_s: float = 120.0) -> float:
+        """Loss of the step ``run_host`` returned ``ticket`` for; waits (polling host memory) until it has landed."""
+        import time
+        io = self._io
+        assert 0 < ticket <= io["issued"] and ticket > io["issued"] - io["slots"], "result already overwritten"
+        slot = io["out"][(ticket - 1) % io["slots"]]
+        t0 = None
+        while int(slot[1]) != (ticket & 0xFFFFFFFF):
+            if t0 is None:
+                t0 = time.monotonic()
+            elif time.monotonic() - t0 > timeout_s:
+                torch.cuda.synchronize(self.dev)           # surfaces a device-side failure as an exception
+                raise TimeoutError(f"step {ticket}: no result after {timeout_s:.0f}s")
+        io["confirmed"] = max(io["confirmed"], ticket)
+        return float(slot[:1].view("float32")[0])
+
     # ---- full step -----------------------------------------------------------------------------------------
-    def _graph_key(self, B: int, C: int, L: int) -> tuple:
+    def _graph_key(self, B: int, C: int, L: int, hostio: bool = False) -> tuple:
         cfg = self.cfg      # everything a captured launch bakes in as a constant is part of the key
         opt = None
         if self._opt is not None:
             agg = self._opt[0]
             opt = (id(agg), agg.clip, agg.noise_std, len(agg.participants), bool(agg.symm.mc_ptr)) + self._opt[1:]
         return (B, C, L, float(cfg.news_grad_noise), bool(cfg.mask_padding), bool(cfg.dedup), bool(cfg.trunk_cache),
-                bool(cfg.ln_fold), float(self.model.user_encoder.dropout_rate), opt)
+                bool(cfg.ln_fold), float(self.model.user_encoder.dropout_rate), opt, hostio)
 
     def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
         """One step. With ``cfg.cuda_graph`` the whole kernel sequence (≈90 launches) is captured once per batch
@@ -510,23 +567,28 @@ class FusedStep:
             self._pending = True
         return g["loss"]
 
-    def _step_eager(self, cand, his, train) -> torch.Tensor:
+    def _step_eager(self, cand, his, train, hostio=None) -> torch.Tensor:
         pipelined = train and self._opt is not None
         if pipelined and self._pending:
             self._count_update()
-        loss = self._run_eager(cand, his, train)
+        if hostio is not None:
+            B, C, L = hostio
+            ids = self._io.setdefault("ids_eager", torch.zeros(B * (L + C), dtype=torch.int32, device=self.dev))
+            loss = self._run_eager(ids[B * L:].view(B, C), ids[: B * L].view(B, L), train, ids=ids, hostio=True)
+        else:
+            loss = self._run_eager(cand, his, train)
         if pipelined:
             self._pending = True
         return loss
 
-    def _graph_for(self, B: int, C: int, L: int):
-        key = self._graph_key(B, C, L)
+    def _graph_for(self, B: int, C: int, L: int, hostio: bool = False):
+        key = self._graph_key(B, C, L, hostio)
         g = self._graphs.get(key)
         if g is None:
-            g = self._capture(B, C, L, key)
+            g = self._capture(B, C, L, key, hostio)
         return g
 
-    def _capture(self, B: int, C: int, L: int, key):
+    def _capture(self, B: int, C: int, L: int, key, hostio: bool = False):
         self.flush()                                        # no pending update may leak into the warm-up runs
         ids = torch.ones(B * (L + C), dtype=torch.int32, device=self.dev)
         static_h, static_c = ids[: B * L].view(B, L), ids[B * L:].view(B, C)
@@ -534,13 +596,17 @@ class FusedStep:
         side.wait_stream(torch.cuda.current_stream(self.dev))
         with torch.cuda.stream(side):                       # warm-up: buffers, attributes, tensor maps, module loads
             for _ in range(2):
-                self._run_eager(static_c, static_h, True, warm=True)
+                self._run_eager(static_c, static_h, True, warm=True, ids=ids if hostio else None, hostio=hostio)
         torch.cuda.current_stream(self.dev).wait_stream(side)
         torch.cuda.synchronize(self.dev)
+        if hostio:      # the warm-up passes consumed ring slots and published results: put the counter back
+            self._io["ctr"].fill_(self._io["issued"] - 1)
+            self._io["out"][:, 1] = 0
+            torch.cuda.synchronize(self.dev)
         graph = torch.cuda.CUDAGraph()
         n0 = D.launch_count()
         with torch.cuda.graph(graph):
-            loss = self._run_eager(static_c, static_h, True, ids=ids)
+            loss = self._run_eager(static_c, static_h, True, ids=ids, hostio=hostio)
         g = {"graph": graph, "ids": ids, "cand": static_c, "his": static_h, "loss": loss,
              "launches": D.launch_count() - n0}
         self._graphs[key] = g
@@ -548,7 +614,7 @@ class FusedStep:
 
     @torch.no_grad()
     def _run_eager(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True, warm: bool = False,
-                   ids: Optional[torch.Tensor] = None) -> torch.Tensor:
+                   ids: Optional[torch.Tensor] = None, hostio: bool = False) -> torch.Tensor:
         """The step's launches on the current stream. ``warm``: a warm-up pass before capture — the optimiser chain is
         launched (its kernels return at once: nothing is pending) but gradients are not marked pending.
         ``ids``: the already concatenated int32 ids (histories, then candidates) when the caller has them."""
@@ -558,6 +624,9 @@ class FusedStep:
         self._step_no += 1
         seed = self.cfg.seed * 1000003 + 3 * self._step_no
         D.counter_advance(self._seed_dev, 0x9E3779B97F4A7C15 & (2 ** 63 - 1))
+        if hostio:                                           # this step's ids: host ring slot -> static id buffer
+            io = self._io
+            D.hostio_fetch(ids, io["ring_dev"], io["n"], io["slots"], io["ctr"])
         opt = self._opt if train else None
         cur = torch.cuda.current_stream(self.dev)
         if opt is not None:
@@ -585,6 +654,8 @@ class FusedStep:
             if opt is not None:
                 opt[0].symm.mark_pending(arm=not warm)       # gradients complete: arm the chain of the next step
         self.last_scores = u["score"]
+        if hostio:
+            D.hostio_publish(self._io["out_dev"], u["loss"], self._io["slots"], self._io["ctr"])
         return u["loss"].clone()
 
     @torch.no_grad()

@@ -86,6 +86,32 @@ class TrainStep:
         d = ids.to(self.model.device)
         return self._run_torch(d[B * L:].view(B, C), d[: B * L].view(B, L), True)
 
+    # ---- end-to-end stepping from host memory ------------------------------------------------------------------
+    def enable_host_io(self, B: int, C: int, L: int, slots: int = 4) -> None:
+        """Prepare ``run_host`` / ``loss_of`` for batches of this shape (fused: pinned host-mapped rings read and written
+        by the step's own first and last kernel; PyTorch path: plain copies)."""
+        self._io_shape = (B, C, L)
+        self._io_results = {}
+        self._io_issued = 0
+        if self._fused is not None:
+            self._fused.enable_host_io(B * (L + C), slots)
+
+    def run_host(self, ids) -> int:
+        """One training step on ids held in host memory (int32 ``[B*L + B*C]``, histories first). Returns a ticket;
+        ``loss_of(ticket)`` delivers that step's loss to the host. The host may run a few steps ahead of the results."""
+        B, C, L = self._io_shape
+        if self._fused is not None:
+            return self._fused.run_host(ids, B, C, L)
+        d = torch.as_tensor(ids).to(self.model.device)
+        self._io_issued += 1
+        self._io_results[self._io_issued] = self._run_torch(d[B * L:].view(B, C), d[: B * L].view(B, L), True)
+        return self._io_issued
+
+    def loss_of(self, ticket: int) -> float:
+        if self._fused is not None:
+            return self._fused.loss_of(ticket)
+        return float(self._io_results.pop(ticket))
+
     def scores(self, cand: torch.Tensor, his: torch.Tensor) -> torch.Tensor:
         """Inference: ``sigmoid(cand · user)`` ``[B, C]`` without touching gradients."""
         if self._fused is not None:

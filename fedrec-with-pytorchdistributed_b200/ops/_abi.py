@@ -22,6 +22,10 @@ SIGNATURES = {
     "fr_dedup_static": (I, [P, I, I, P, P, P, P]),
     "fr_sq_norm": (I, [P, LL, P, P]),
     "fr_clip_noise": (I, [P, LL, P, F, F, c_ulonglong, c_uint, P]),
+    "fr_host_mapped_alloc": (I, [LL, P, P]),
+    "fr_host_mapped_free": (I, [P]),
+    "fr_hostio_fetch": (I, [P, P, I, I, P, P]),
+    "fr_hostio_publish": (I, [P, P, I, P, P]),
     # bert_ops.cu
     "fr_bert_embed_ln": (I, [P, P, P, I, I, P, P, P, P, P, F, I, P]),
     "fr_layernorm_bf16": (I, [P, P, P, P, I, P, I, F, I, P]),

@@ -259,6 +259,19 @@ def cast_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tens
 
 
 # ---- user encoder / loss / gradient GEMMs (CUDA only) -------------------------------------------------------
+def hostio_fetch(dst: torch.Tensor, ring_dev: int, n: int, slots: int, ctr: torch.Tensor) -> None:
+    """``dst[:n] = ring[*ctr % slots]; *ctr += 1`` with ``ring`` in host-mapped pinned memory (engine/fused.py run_host)."""
+    check(require_native().fr_hostio_fetch(dst.data_ptr(), ring_dev, n, slots, ctr.data_ptr(), stream_ptr(dst.device)),
+          "fr_hostio_fetch")
+    count_launches(1)
+
+
+def hostio_publish(out_dev: int, value: torch.Tensor, slots: int, ctr: torch.Tensor) -> None:
+    check(require_native().fr_hostio_publish(out_dev, value.data_ptr(), slots, ctr.data_ptr(), stream_ptr(value.device)),
+          "fr_hostio_publish")
+    count_launches(1)
+
+
 def counter_advance(ctr: torch.Tensor, inc: int = 1) -> None:
     lib = require_native()
     check(lib.fr_counter_advance(ctr.data_ptr(), int(inc), stream_ptr(ctr.device)), "fr_counter_advance")

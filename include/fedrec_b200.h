@@ -57,6 +57,17 @@ int fr_sq_norm(const float* x, long long n, float* out, void* stream);
 int fr_clip_noise(float* x, long long n, const float* sq, float clip, float noise_std, unsigned long long seed,
                   unsigned stream_id, void* stream);
 
+/* Host I/O of a step through host-mapped pinned rings, usable from inside a CUDA graph: fr_hostio_fetch copies slot
+ * (*step_ctr % slots) of ring_mapped (slots x n ints, device-visible address of pinned host memory) into dst and
+ * increments *step_ctr; fr_hostio_publish writes {value bits, *step_ctr} into entry ((*step_ctr - 1) % slots) of
+ * out_ring_mapped (slots x 4 uints), sequence number last, for the host to poll. fr_host_mapped_alloc returns both
+ * addresses of a zeroed pinned allocation. Replaces the per-batch host/device copies of main.py:59-64,72-79,90. */
+int fr_host_mapped_alloc(long long bytes, void** host_out_host, void** dev_out_host);
+int fr_host_mapped_free(void* host_ptr_host);
+int fr_hostio_fetch(int* dst, const int* ring_mapped, int n, int slots, unsigned long long* step_ctr, void* stream);
+int fr_hostio_publish(void* out_ring_mapped, const float* value, int slots, const unsigned long long* step_ctr,
+                      void* stream);
+
 /* ---- DistilBERT trunk / text head, memory-bound parts (csrc/bert_ops.cu) ----------------------------- */
 
 /* out[(n*T+t),:] = LayerNorm(word[tokens[items[n],t]] + pos[t]) in bf16, n < min(n_items, *count_dev).

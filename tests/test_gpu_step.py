@@ -189,3 +189,27 @@ def test_run_packed_takes_pinned_host_ids():
     assert la == pytest.approx(lb, abs=1e-5)
     rel = float((a.flat.grad - b.flat.grad).norm() / b.flat.grad.norm())
     assert rel < 1e-4, rel
+
+
+@pytest.mark.parametrize("graph", [True, False], ids=["graph", "eager"])
+def test_run_host_pulls_ids_from_pinned_memory_and_pushes_the_loss_back(graph):
+    """run_host / loss_of: the step's first kernel reads its ids from a host-mapped ring, its last kernel writes
+    {loss, sequence number} into host memory. Same losses and gradients as run() on device-resident ids, for more steps
+    than the ring has slots (the host is held back instead of overwriting a slot that has not been consumed)."""
+    a, b = _models(cuda_graph=graph)
+    fa, fb = TrainStep(a, impl="fused"), TrainStep(b, impl="fused")
+    fa.enable_host_io(6, 5, 50, slots=3)
+    g = torch.Generator(device=DEV).manual_seed(13)
+    tickets, want = [], []
+    for it in range(7):
+        cand = torch.randint(1, 600, (6, 5), device=DEV, generator=g, dtype=torch.int32)
+        his = torch.randint(0, 600, (6, 50), device=DEV, generator=g, dtype=torch.int32)
+        ids = torch.cat([his.reshape(-1), cand.reshape(-1)]).cpu().numpy()
+        tickets.append(fa.run_host(ids))
+        want.append(float(fb.run(cand, his)))
+        rel = float((a.flat.grad - b.flat.grad).norm() / b.flat.grad.norm())
+        assert rel < 1e-4, (it, rel)
+        if it >= 1:
+            assert fa.loss_of(tickets[it - 1]) == pytest.approx(want[it - 1], abs=1e-5)
+    assert tickets == list(range(1, 8))
+    assert fa.loss_of(tickets[-1]) == pytest.approx(want[-1], abs=1e-5)
