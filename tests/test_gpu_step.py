@@ -168,7 +168,7 @@ def test_pipelined_optimizer_equals_step_then_aggregate_then_adam(graph):
     diff = (a.flat.param - b.flat.param).abs()
     assert float(diff.max()) < 5e-3 and float((diff > 2e-5).float().mean()) < 1e-2, (float(diff.max()), float((diff > 2e-5).float().mean()))
     rel_p = float((a.flat.param - b.flat.param).norm() / b.flat.param.norm())
-    assert rel_p < 1e-4, rel_p
+    assert rel_p < 1e-3, rel_p
     # inference and checkpoints see the flushed weights
     cand = torch.randint(1, 600, (6, 5), device=DEV, generator=g, dtype=torch.int32)
     his = torch.randint(0, 600, (6, 50), device=DEV, generator=g, dtype=torch.int32)
