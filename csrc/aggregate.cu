@@ -407,7 +407,7 @@ int fill_common(AggParams& p, void* const* bufs_host, void* const* pads_host, vo
 
 // Launches the whole chain on `s`. Nothing here synchronises or allocates; every launch is graph-capturable.
 int launch_chain(const AggParams& p, const ChainOpts& o, cudaStream_t s) {
-  int sms = kNumSMs, dev = 0;
+  int sms = num_sms(), dev = 0;
   FR_CHECK(cudaGetDevice(&dev));
   FR_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
   int blocks = o.blocks > 0 ? o.blocks : 64;

@@ -312,7 +312,7 @@ FR_API int fr_bert_attention_tc(const void* qkv, const int* mask_table, const in
     attr_set = true;
   }
   long long jobs = (long long)((n_items + TP - 1) / TP) * heads;      // (tile, head) jobs, split evenly over the CTAs
-  int grid = jobs < 2 * kNumSMs ? (int)jobs : 2 * kNumSMs;
+  int grid = jobs < 2 * num_sms() ? (int)jobs : 2 * num_sms();
   if (slot == 32) FR_CHECK(launch_pdl(bert_attention_tc_kernel<32>, dim3(grid), dim3(128), smem, (cudaStream_t)stream, tm, p));
   else FR_CHECK(launch_pdl(bert_attention_tc_kernel<64>, dim3(grid), dim3(128), smem, (cudaStream_t)stream, tm, p));
   return 0;

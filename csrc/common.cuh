@@ -35,7 +35,8 @@ void set_error(const char* fmt, ...);
 
 #define FR_LAUNCH_CHECK() FR_CHECK(cudaGetLastError())
 
-constexpr int kNumSMs = 148;
+constexpr int kNumSMs = 148;      // B200; launchers size their grids from num_sms(), this is only its fallback
+int num_sms();                    // SM count of the current device (runtime.cu; cached per device)
 
 // ---- programmatic dependent launch (PDL) --------------------------------------------------------------------------
 // A kernel launched through launch_pdl may become resident while the previous kernel of the stream is still draining;

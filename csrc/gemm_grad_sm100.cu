@@ -199,7 +199,7 @@ FR_API int fr_gemm_grad_bf16(const void* A, const void* B, float* out, int M1, i
     // One wave of CTAs (197 KB of shared memory = one CTA per SM): measured on the step's shapes
     // (scripts/bench_gemm_grad.py), 9 tiles x 16 splits takes 30.7 us where two waves (33 splits) take 39.9 us, since
     // every CTA pays the pipeline fill and a 128 KB red.global epilogue. At least four k-blocks per split.
-    splits = kNumSMs / tiles;
+    splits = num_sms() / tiles;
     if (splits > kb_total / 4) splits = kb_total / 4;
     if (splits < 1) splits = 1;
   }

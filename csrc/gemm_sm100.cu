@@ -49,7 +49,7 @@ struct GemmParams {
   const float* r_stats;       // [M, N/64, 2] of the residual rows: the residual is LayerNorm(resid) computed on the fly
   const float* r_gamma;       // [N]
   const float* r_beta;        // [N]
-  float* stats_out;           // [M, N/64, 2] = (sum, sum of squares) of every 64-column slice of the output rows
+  float* stats_out;           // [M, N/64, 2] = (sum, M2 about the slice mean) of every 64-column slice of the output rows
   float ln_eps;
   int a_dim, r_dim;           // widths the two statistics were taken over
 };
@@ -99,6 +99,25 @@ template <int kCols>
 __device__ __forceinline__ uint32_t box_off(int r, int j) {
   if (kCols == 64) return (uint32_t)(r * 128 + ((j ^ (r & 7)) << 4));          // SWIZZLE_128B
   return (uint32_t)(r * 64 + ((j ^ ((r >> 1) & 3)) << 4));                       // SWIZZLE_64B
+}
+
+// Mean and (biased) variance of a row from its per-slice statistics. Every 64-column slice carries (sum, M2) with
+// M2 = sum((v - slice mean)^2); slices are merged with the parallel-variance formula
+//   M2_row = sum_s M2_s + 64 * sum_s (mean_s - mean_row)^2,
+// which never subtracts two large numbers: a residual stream with a large common offset or a few outlier channels (what
+// a pretrained DistilBERT produces) keeps its variance to fp32 rounding, where E[x^2] - mean^2 loses it to cancellation.
+__device__ __forceinline__ void merge_row_stats(const float2* sp, int ns, float& mean, float& var) {
+  float sum = 0.f;
+  for (int k = 0; k < ns; ++k) sum += __ldg(sp + k).x;
+  const float n = 64.f * (float)ns;
+  mean = sum / n;
+  float m2 = 0.f;
+  for (int k = 0; k < ns; ++k) {
+    const float2 t = __ldg(sp + k);
+    const float d = t.x * (1.f / 64.f) - mean;
+    m2 += fmaf(64.f * d, d, t.y);
+  }
+  var = fmaxf(m2 / n, 0.f);
 }
 
 template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG, bool FOLD = false>
@@ -296,37 +315,21 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       // FOLD: per-row LayerNorm scalars (this thread owns row `row`), fetched while the MMAs run
       float ra = 1.f, rb = 0.f;            // out = ra * acc + rb * c[col] + bias[col]
       float rr = 1.f, rm = 0.f;            // residual = (resid - rm) * rr * gamma[col] + beta[col]
-      float st_s = 0.f, st_q = 0.f;        // running (sum, sum of squares) of this thread's output row
+      float st_s = 0.f, st_q = 0.f, st_k = 0.f;   // this thread's output row, shifted by its first value st_k: (sum, sum of squares)
       if constexpr (FOLD) {
         if (work && row_ok) {
-          // A row's statistics arrive as one (sum, sum of squares) pair per 64-column slice of the producer's output
-          // (written without atomics, see below) and are added here in a fixed order: bit-reproducible.
+          // A row's statistics arrive as one (sum, M2) pair per 64-column slice of the producer's output (written without
+          // atomics, see below) and are merged here in a fixed order: bit-reproducible.
           if (p.a_stats) {
-            const int ns = p.a_dim >> 6;
-            const float2* sp = reinterpret_cast<const float2*>(p.a_stats) + (size_t)row * ns;
-            float sum = 0.f, sq = 0.f;
-            for (int k = 0; k < ns; ++k) {
-              const float2 t = __ldg(sp + k);
-              sum += t.x;
-              sq += t.y;
-            }
-            const float inv_n = 1.f / (float)p.a_dim;
-            const float mu = sum * inv_n;
-            ra = rsqrtf(fmaxf(fmaf(sq, inv_n, -mu * mu), 0.f) + p.ln_eps);
+            float mu, var;
+            merge_row_stats(reinterpret_cast<const float2*>(p.a_stats) + (size_t)row * (p.a_dim >> 6), p.a_dim >> 6, mu, var);
+            ra = rsqrtf(var + p.ln_eps);
             rb = -ra * mu;
           }
           if (p.r_stats) {
-            const int ns = p.r_dim >> 6;
-            const float2* sp = reinterpret_cast<const float2*>(p.r_stats) + (size_t)row * ns;
-            float sum = 0.f, sq = 0.f;
-            for (int k = 0; k < ns; ++k) {
-              const float2 t = __ldg(sp + k);
-              sum += t.x;
-              sq += t.y;
-            }
-            const float inv_n = 1.f / (float)p.r_dim;
-            rm = sum * inv_n;
-            rr = rsqrtf(fmaxf(fmaf(sq, inv_n, -rm * rm), 0.f) + p.ln_eps);
+            float var;
+            merge_row_stats(reinterpret_cast<const float2*>(p.r_stats) + (size_t)row * (p.r_dim >> 6), p.r_dim >> 6, rm, var);
+            rr = rsqrtf(var + p.ln_eps);
           }
         }
       }
@@ -385,10 +388,12 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           if constexpr (FOLD) {
             if (p.stats_out) {
 #pragma unroll
+              if (cc == 0) st_k = v[0];
               for (int j = 0; j < 32; ++j) {
                 if (j < ncols) {
-                  st_s += v[j];
-                  st_q = fmaf(v[j], v[j], st_q);
+                  const float d = v[j] - st_k;
+                  st_s += d;
+                  st_q = fmaf(d, d, st_q);
                 }
               }
             }
@@ -435,7 +440,8 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
         if constexpr (FOLD) {
           static_assert(!FOLD || kCols == 64, "row statistics are kept per 64-column slice");
           if (p.stats_out && row_ok)       // this warp's 64 columns are slice wcol0 / 64 of the row: a plain store
-            reinterpret_cast<float2*>(p.stats_out)[(size_t)row * (p.N >> 6) + (wcol0 >> 6)] = make_float2(st_s, st_q);
+            reinterpret_cast<float2*>(p.stats_out)[(size_t)row * (p.N >> 6) + (wcol0 >> 6)] =
+                make_float2(fmaf(64.f, st_k, st_s), fmaxf(fmaf(-st_s * (1.f / 64.f), st_s, st_q), 0.f));   // (sum, M2)
         }
         if (TMA_EPI) {
           if (box_full) {
@@ -600,16 +606,7 @@ static int make_tmap_box_swz(CUtensorMap* out, const void* base, long long rows,
   return 0;
 }
 
-static int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
-    if (n <= 0) n = kNumSMs;
-  }
-  return n;
-}
+static int sm_count() { return num_sms(); }
 
 }  // namespace fr
 
@@ -733,7 +730,7 @@ FR_API int fr_gemm_bf16_ex(const void* A, const void* W, const float* bias, cons
 }
 
 // fr_gemm_bf16 with LayerNorm folded around it (frozen-weight trunks; all extra pointers optional, 256-wide tile):
-//   Row statistics are (sum, sum of squares) per 64-column slice: a_stats [M, K/64, 2], r_stats / stats_out [M, N/64, 2];
+//   Row statistics are (sum, M2 = sum of squared deviations from the slice mean) per 64-column slice: a_stats [M, K/64, 2], r_stats / stats_out [M, N/64, 2];
 //   the producer stores its slices (no atomics, nothing to zero) and the consumer adds them in a fixed order.
 //   a_stats + col_c [N]:
 //       out = rstd_A * (A · W^T) - rstd_A * mu_A * col_c + bias      = LayerNorm_gamma,beta(A) · W0^T + b0

@@ -16,6 +16,17 @@ bool pdl_enabled() {
   static const bool on = [] { const char* e = getenv("FEDREC_PDL"); return !(e && atoi(e) == 0); }();
   return on;
 }
+int num_sms() {
+  static int cache[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return kNumSMs;
+  int n = __atomic_load_n(&cache[dev], __ATOMIC_RELAXED);
+  if (n == 0) {
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = kNumSMs;
+    __atomic_store_n(&cache[dev], n, __ATOMIC_RELAXED);
+  }
+  return n;
+}
 }  // namespace fr
 
 FR_API const char* fr_last_error() { return fr::g_err; }

@@ -304,7 +304,7 @@ FR_API int fr_adam_flat(float* p, const float* g, float* m, float* v, long long 
   if (n == 0) return 0;
   const size_t n4 = (size_t)n / 4;
   int blocks = (int)((n4 + 255) / 256);
-  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   adam_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((float4*)p, (const float4*)g, (float4*)m, (float4*)v, n4, lr, b1,
                                                         b2, eps, bc1, bc2, bc_dev, grad_scale);
   FR_LAUNCH_CHECK();
@@ -336,7 +336,7 @@ FR_API int fr_sq_norm(const float* x, long long n, float* out, void* stream) {
   if (n == 0) return 0;
   const size_t n4 = (size_t)n / 4;
   int blocks = (int)((n4 + 255) / 256);
-  if (blocks > kNumSMs * 4) blocks = kNumSMs * 4;
+  if (blocks > num_sms() * 4) blocks = num_sms() * 4;
   sq_norm_kernel<<<blocks, 256, 0, s>>>((const float4*)x, n4, out);
   FR_LAUNCH_CHECK();
   return 0;
@@ -349,7 +349,7 @@ FR_API int fr_clip_noise(float* x, long long n, const float* sq, float clip, flo
   if (n == 0) return 0;
   const size_t n4 = (size_t)n / 4;
   int blocks = (int)((n4 + 255) / 256);
-  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   clip_noise_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>((float4*)x, n4, sq, clip, noise_std, seed, stream_id);
   FR_LAUNCH_CHECK();
   return 0;

@@ -548,7 +548,7 @@ FR_API int fr_ue_gather_dropout(const float* news_vecs, const int* inv_his, void
   if (rows == 0) return 0;
   const size_t total = (size_t)rows * (D / 4);
   int blocks = (int)((total + 255) / 256);
-  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   FR_CHECK(launch_pdl(ue_gather_dropout_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, news_vecs, inv_his,
                       (__nv_bfloat16*)X, rows, D / 4, p, seed, seed_dev));
   FR_LAUNCH_CHECK();
@@ -562,7 +562,7 @@ FR_API int fr_ue_scatter_dx(const float* dX, const int* inv_his, float* d_news, 
   if (rows == 0) return 0;
   const size_t total = (size_t)rows * (D / 4);
   int blocks = (int)((total + 255) / 256);
-  if (blocks > kNumSMs * 8) blocks = kNumSMs * 8;
+  if (blocks > num_sms() * 8) blocks = num_sms() * 8;
   FR_CHECK(launch_pdl(ue_scatter_dx_kernel, dim3(blocks), dim3(256), 0, (cudaStream_t)stream, dX, inv_his, d_news, rows, D / 4, p,
                       seed, noise_std, noise_seed, seed_dev));
   FR_LAUNCH_CHECK();

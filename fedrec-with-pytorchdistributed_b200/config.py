@@ -68,7 +68,7 @@ class FedRecConfig:
     # ---- runtime -----------------------------------------------------------------
     backend: str = "auto"          # auto → nccl when CUDA is present, else gloo
     device: str = "auto"
-    dtype: str = "bf16"            # compute dtype of the fused path
+    dtype: str = "bf16"            # bf16 = the sm_100a kernels (bf16 tensor cores, fp32 accumulate); fp32 = the PyTorch step (debugging)
     fused: bool = True             # use the sm_100a kernels when available
     dedup: bool = True             # encode each distinct news id once per step
     mask_padding: bool = False     # the reference never masks

@@ -269,7 +269,8 @@ class FusedStep:
         return self._encode(uniq, count, K)
 
     @torch.no_grad()
-    def _encode(self, uniq: torch.Tensor, count: Optional[torch.Tensor], K: int, packed: bool = False) -> Dict[str, torch.Tensor]:
+    def _encode(self, uniq: torch.Tensor, count: Optional[torch.Tensor], K: int, packed: bool = False,
+                precomputed: bool = False) -> Dict[str, torch.Tensor]:
         """``uniq`` int32 [K] news rows (first ``*count`` valid) → buffers with ``hidden`` (=x) and ``news_vecs``.
 
         ``packed=True`` means the caller already refreshed the bf16 weight copies on the side stream (joined here,
@@ -278,6 +279,15 @@ class FusedStep:
         if not packed:
             with self._fork():
                 self._pack_weights(train=False)
+        if precomputed:
+            # cfg.precomputed_news: pooled 768-d features come from the cached table; only the 768->400 projection runs
+            if count is None:
+                count = b["full_count"]
+            D.rows_copy(m.news_features_bf16(), uniq, b["pooled"], None, count, K, 1)
+            self._join()
+            D.linear_bf16(b["pooled"], self._packed()["t_wfc"], m.text_encoder.fc.bias.data, "bias", out=b["news_vecs"],
+                          m_dev=count, m_scale=1)
+            return b
         T = m.news_tokens.shape[1]
         x = b["x"]
         want_uniq, want_count = uniq, count
@@ -446,6 +456,9 @@ class FusedStep:
         with self._fork():                                   # needs d_news(_bf), pooled
             D.gemm_grad(b["d_news_bf"], b["pooled"], g("text_encoder.fc.weight"), k_dev=count, k_scale=1)
             D.colsum(b["d_news"], g("text_encoder.fc.bias"), m_dev=count, m_scale=1)
+        if self.cfg.precomputed_news:                        # the additive attention is frozen into the feature cache
+            self._join()
+            return
         D.linear_bf16(b["d_news_bf"], pk["t_wfcT"], None, "bias", out=b["d_pooled"], m_dev=count, m_scale=1)
         D.text_pool_bwd(b["x"], b["e"], b["alpha"], b["d_pooled"], aa.att_fc2.weight.data.view(-1), count, K, T,
                         b["d_pre"], b["da"], None, g("text_encoder.additive_attention.att_fc2.bias"), None)
@@ -520,7 +533,7 @@ class FusedStep:
             agg = self._opt[0]
             opt = (id(agg), agg.clip, agg.noise_std, len(agg.participants), bool(agg.symm.mc_ptr)) + self._opt[1:]
         return (B, C, L, float(cfg.news_grad_noise), bool(cfg.mask_padding), bool(cfg.dedup), bool(cfg.trunk_cache),
-                bool(cfg.ln_fold), float(self.model.user_encoder.dropout_rate), opt, hostio)
+                bool(cfg.ln_fold), float(self.model.user_encoder.dropout_rate), opt, hostio, bool(cfg.precomputed_news))
 
     def run(self, cand: torch.Tensor, his: torch.Tensor, train: bool = True) -> torch.Tensor:
         """One step. With ``cfg.cuda_graph`` the whole kernel sequence (≈90 launches) is captured once per batch
@@ -644,7 +657,10 @@ class FusedStep:
         ids, uniq, count, inv, K = self._ids(cand, his, ids)
         if train and opt is None:
             m.flat.zero_grad()
-        b = self._encode(uniq, count, K, packed=True)
+        pre = bool(self.cfg.precomputed_news)
+        if pre and m.news_features is None:
+            raise RuntimeError("cfg.precomputed_news: call model.build_news_features() (or set_news_features) first")
+        b = self._encode(uniq, count, K, packed=True, precomputed=pre)
         if train:
             b["d_news"].zero_()
         u, p, his_flat, use_mask = self._user_forward(b, inv, his, B, L, C, train, seed)
@@ -670,6 +686,7 @@ class FusedStep:
         with self._fork():
             self._pack_weights(False)
         ids, uniq, count, inv, K = self._ids(cand, his)
-        b = self._encode(uniq, count, K, packed=True)
+        b = self._encode(uniq, count, K, packed=True,
+                         precomputed=bool(self.cfg.precomputed_news) and self.model.news_features is not None)
         u, _, _, _ = self._user_forward(b, inv, his, B, L, C, False, 0)
         return u["score"].clone()

@@ -30,6 +30,13 @@ class TrainStep:
         dev = model.device
         if impl is None:
             impl = "fused" if (dev.type == "cuda" and self.cfg.fused) else "torch"
+            if impl == "fused" and self.cfg.dtype == "fp32":
+                impl = "torch"               # dtype=fp32: the fp32 PyTorch step, for debugging numerics against the bf16 kernels
+            if impl == "fused" and self.cfg.trunk_dropout_in_update:
+                import warnings              # model.py:73 (DistilBERT in train() for the gradient pass) exists only in the oracle step
+                warnings.warn("fedrec_b200: trunk_dropout_in_update is honoured by the PyTorch step only (the sm_100a "
+                              "pipeline reuses the eval-mode trunk output); running the PyTorch path", RuntimeWarning)
+                impl = "torch"
             if impl == "fused":
                 from .fused import fused_unsupported_reason
                 why = fused_unsupported_reason(model, self.cfg)
@@ -122,7 +129,10 @@ class TrainStep:
         with torch.no_grad():
             ids = torch.cat([his.reshape(-1), cand.reshape(-1)]).long()
             uniq, inv = torch.unique(ids, return_inverse=True)
-            vec = m.encode_unique(uniq, keep_cache=False, use_fused=False)
+            if self.cfg.precomputed_news and m.news_features is not None:
+                vec = m.text_encoder.fc(m.news_features[uniq])
+            else:
+                vec = m.encode_unique(uniq, keep_cache=False, use_fused=False)
             B, L = his.shape
             his_mask = (his != 0) if self.cfg.mask_padding else None
             user = m.user_encoder(vec[inv[: B * L]].view(B, L, -1), his_mask)
@@ -141,7 +151,13 @@ class TrainStep:
             uniq, inv = torch.unique(ids, return_inverse=True)
         else:
             uniq, inv = ids, torch.arange(ids.numel(), device=ids.device)
-        if cfg.trunk_dropout_in_update and train:
+        if cfg.precomputed_news:
+            # BASELINE.json config 1: no trunk in the step; the 768-d features are a cached table, the 768->400 projection
+            # and the user encoder train (the text head's additive attention is frozen into the cache)
+            if m.news_features is None:
+                m.build_news_features()
+            vec = m.text_encoder.fc(m.news_features[uniq])
+        elif cfg.trunk_dropout_in_update and train:
             # upstream quirk (model.py:73): the gradient pass re-runs DistilBERT in train mode
             m.text_encoder.DistillBert.train()
             with torch.no_grad():

@@ -82,6 +82,8 @@ class UserModel(nn.Module):
         self._init_grad_param()
         self._cache: Optional[Dict[str, torch.Tensor]] = None
         self._fused = None        # engine.fused.FusedStep, attached lazily by the engine
+        self.news_features: Optional[torch.Tensor] = None     # [N, 768] cache for cfg.precomputed_news
+        self._news_features_bf16: Optional[torch.Tensor] = None
 
     # ---- news table -------------------------------------------------------------
     def set_news_index(self, news_index) -> None:
@@ -188,6 +190,48 @@ class UserModel(nn.Module):
         if torch.isnan(vec).any():
             raise ValueError("news_vecs contains nan")
         return vec[inv].view(*ids.shape, -1)
+
+    # ---- precomputed news features (BASELINE.json config 1) -------------------------------------------------------
+    @torch.no_grad()
+    def build_news_features(self, batch: int = 2048) -> torch.Tensor:
+        """Cache ``[N, 768]`` pooled DistilBERT features of the whole news table (frozen trunk + the text head's additive
+        attention *as it is now*), so that ``cfg.precomputed_news`` steps train the user encoder and the 768→400
+        projection without ever running the trunk. This is the training-side counterpart of what upstream's
+        ``UserDataset`` (dataset.py:92-109) and ``evaluation_split`` (evaluation_functions.py:33-46) anticipate:
+        news vectors computed once, users encoded over the cache."""
+        self.sync_optimizer()
+        te = self.text_encoder
+        N = self.news_tokens.shape[0]
+        feats = torch.empty(N, te.fc.in_features, device=self.device, dtype=torch.float32)
+        fused = self._fused_engine()
+        for i in range(0, N, batch):
+            ids = torch.arange(i, min(N, i + batch), device=self.device)
+            if fused is not None:
+                U = ids.numel()
+                cap = (U + 255) // 256 * 256
+                padded = torch.zeros(cap, dtype=torch.int32, device=self.device)
+                padded[:U] = ids
+                b = fused.encode(padded, torch.tensor([U], dtype=torch.int32, device=self.device), cap)
+                feats[i:i + U] = b["pooled"][:U].float()
+            else:
+                was = te.DistillBert.training
+                te.DistillBert.eval()
+                hidden = te.trunk(self.news_tokens[ids].long(), self.news_mask[ids])
+                te.DistillBert.train(was)
+                feats[i:i + ids.numel()] = te.additive_attention(hidden, self.news_mask[ids] if te.mask_padding else None)
+        self.set_news_features(feats)
+        return feats
+
+    def set_news_features(self, feats: torch.Tensor) -> None:
+        """Install a ``[N, 768]`` feature table (computed elsewhere, e.g. by a server with the full trunk)."""
+        assert feats.dim() == 2 and feats.shape[1] == self.text_encoder.fc.in_features
+        self.news_features = feats.to(self.device, torch.float32).contiguous()
+        self._news_features_bf16 = None
+
+    def news_features_bf16(self) -> torch.Tensor:
+        if getattr(self, "_news_features_bf16", None) is None:
+            self._news_features_bf16 = self.news_features.to(torch.bfloat16).contiguous()
+        return self._news_features_bf16
 
     # ---- precomputed-vector inference (the path upstream's UserDataset / evaluation_split anticipate) ---------------
     @torch.no_grad()

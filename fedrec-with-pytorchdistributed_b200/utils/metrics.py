@@ -38,7 +38,9 @@ def roc_auc_score(y_true, y_score) -> float:
 
 
 def dcg_score(y_true, y_score, k: int = 10) -> float:
-    order = np.argsort(y_score)[::-1]
+    # kind="stable": upstream's bare np.argsort()[::-1] orders ties by whatever the installed numpy's unstable sort does
+    # (SIMD sorts differ by CPU); the stable variant is its documented small-array behaviour — higher index first.
+    order = np.argsort(y_score, kind="stable")[::-1]
     y_true = np.take(y_true, order[:k])
     gains = 2 ** y_true - 1
     discounts = np.log2(np.arange(len(y_true)) + 2)
@@ -50,7 +52,7 @@ def ndcg_score(y_true, y_score, k: int = 10) -> float:
 
 
 def mrr_score(y_true, y_score) -> float:
-    order = np.argsort(y_score)[::-1]
+    order = np.argsort(y_score, kind="stable")[::-1]
     y_true = np.take(y_true, order)
     rr = y_true / (np.arange(len(y_true)) + 1)
     return float(np.sum(rr) / np.sum(y_true))
@@ -94,7 +96,10 @@ def batched_ranking_metrics(scores: torch.Tensor, labels: torch.Tensor) -> Dict[
     win = (diff > 0).to(scores.dtype) + 0.5 * (diff == 0).to(scores.dtype)
     pair = labels[:, :, None] * (1 - labels[:, None, :])
     auc = (win * pair).sum((1, 2)) / (n_pos * n_neg).clamp_min(1)
-    order = scores.argsort(dim=1, descending=True, stable=True)
+    # rank order of the reference: np.argsort(y_score)[::-1] (evaluation_functions.py:6,20), i.e. among equal scores the
+    # HIGHER column comes first. Validation puts the positive in column 0, so a model whose scores saturate to equal
+    # values ranks the positive last (MRR 1/C), not first: no inflated metrics for degenerate models.
+    order = (C - 1) - scores.flip(1).argsort(dim=1, descending=True, stable=True)
     sorted_lab = labels.gather(1, order)
     pos = torch.arange(C, device=scores.device, dtype=scores.dtype)
     mrr = (sorted_lab / (pos + 1)).sum(1) / n_pos.clamp_min(1)

@@ -36,7 +36,9 @@ int fr_adam_flat(float* p, const float* g, float* m, float* v, long long n, floa
                  float bc1, float bc2, const float* bc_dev, float grad_scale, void* stream);
 
 /* Sorted unique of K ids in [0,N): uniq[K] (tail padded with 0), *count, inv[K] with uniq[inv[k]] == ids[k].
- * workspace: fr_dedup_workspace_ints(N) ints of scratch. No host synchronisation.
+ * workspace: fr_dedup_workspace_ints(N) ints of scratch. No host synchronisation. An id outside [0,N) is not an
+ * error: it is left out of uniq/count and its inv entry is 0 (the slot of the smallest id present), so downstream
+ * gathers stay in range; validate ids on the host if such input must be rejected.
  * Replaces nothing upstream (model.py:41-61 encodes every duplicate). */
 long long fr_dedup_workspace_ints(int N);
 int fr_dedup(const int* ids, int K, int N, int* workspace, int* uniq, int* count, int* inv, void* stream);
@@ -47,7 +49,8 @@ int fr_dedup(const int* ids, int K, int N, int* workspace, int* uniq, int* count
  * outputs as fr_dedup. Limit: N <= fr_dedup_static_max_rows() (1,048,576 rows; 4,198,404 bytes of device memory
  * per GPU, held for the life of the process); larger N is refused with an error. Allocates and frees nothing.
  * The first call on each device resolves the scratch address and must come before any stream capture on that
- * device. All calls on a device share the scratch: calls that can overlap on the GPU race; order them. */
+ * device. All calls on a device share the scratch: calls that can overlap on the GPU race; order them. Ids outside
+ * [0,N) are treated as in fr_dedup (skipped, inv = 0). */
 int fr_dedup_static_max_rows(void);
 int fr_dedup_static(const int* ids, int K, int N, int* uniq, int* count, int* inv, void* stream);
 

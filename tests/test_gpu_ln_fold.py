@@ -12,9 +12,9 @@ DEV = "cuda:0"
 
 
 def _stats(x):
-    """[M, W/64, 2]: (sum, sum of squares) of every 64-column slice of every row."""
-    xf = x.float().view(x.shape[0], -1, 64)
-    return torch.stack([xf.sum(2), (xf * xf).sum(2)], 2).contiguous()
+    """[M, W/64, 2]: (sum, M2 = sum of squared deviations from the slice mean) of every 64-column slice of every row."""
+    xf = x.double().view(x.shape[0], -1, 64)
+    return torch.stack([xf.sum(2), ((xf - xf.mean(2, keepdim=True)) ** 2).sum(2)], 2).float().contiguous()
 
 
 @pytest.mark.parametrize("M,epi", [(4500, "bias"), (4500, "gelu"), (300, "gelu")])
@@ -63,10 +63,67 @@ def test_residual_layernorm_on_the_fly_and_row_statistics(M, K, with_ln):
     want = a.float() @ w.float().t() + b + res
     err = (out.float() - want).abs()
     assert float(err.max()) < 0.06 and float(err.mean()) < 6e-3, (float(err.max()), float(err.mean()))
-    torch.testing.assert_close(st, _stats(want), atol=0.05, rtol=2e-3)
+    torch.testing.assert_close(st, _stats(want), atol=0.08, rtol=3e-3)
     st2 = torch.zeros_like(st)
     D.linear_bf16_fold(a, w, b, "resid", out, resid=r, stats_out=st2, **kw)
     assert torch.equal(st, st2)                                         # no atomics: bit-reproducible
+
+
+@pytest.mark.parametrize("case", ["offset50", "outlier_channels", "wide_gamma"])
+def test_folding_survives_pretrained_like_residual_streams(case):
+    """Rows as a pretrained DistilBERT produces them: a large common offset (mean 50, std 1), a few channels 100x larger
+    than the rest, LayerNorm gains spanning 0.1..10. E[x^2] - mean^2 in fp32 loses these to cancellation; the (sum, M2)
+    slices merged with the parallel-variance formula must not. Checked on the statistics a producer GEMM writes and on
+    both consumers (input LayerNorm folded into the GEMM, residual LayerNorm on the fly)."""
+    ops.require_native()
+    g = torch.Generator(device=DEV).manual_seed(7)
+    M, K, N = 2048, 768, 768
+    base = torch.randn(M, K, device=DEV, generator=g)
+    gamma = 1.0 + 0.2 * torch.randn(K, device=DEV, generator=g)
+    if case == "offset50":
+        x32 = base + 50.0
+    elif case == "outlier_channels":
+        x32 = base.clone()
+        x32[:, [5, 300, 301, 767]] *= 100.0
+    else:
+        x32 = base * 1.5 + 0.7
+        gamma = torch.exp(torch.empty(K, device=DEV).uniform_(-2.3, 2.3, generator=g))     # 0.1 .. 10
+    beta = 0.1 * torch.randn(K, device=DEV, generator=g)
+    # (1) a producer writes the row: residual GEMM with a zero product, so out = r exactly and stats_out describes r
+    r = x32.bfloat16()
+    a0 = torch.zeros(M, 64, device=DEV, dtype=torch.bfloat16)
+    w0 = torch.zeros(N, 64, device=DEV, dtype=torch.bfloat16)
+    out = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    st = torch.empty(M, N // 64, 2, device=DEV)
+    D.linear_bf16_fold(a0, w0, None, "resid", out, resid=r, stats_out=st)
+    assert torch.equal(out, r)
+    rf = r.double()
+    mu_true, var_true = rf.mean(1), rf.var(1, unbiased=False)
+    n = float(K)
+    mean_s = st[..., 0].double() / 64.0
+    mu = st[..., 0].double().sum(1) / n
+    var = (st[..., 1].double() + 64.0 * (mean_s - mu[:, None]) ** 2).sum(1) / n
+    assert float(((mu - mu_true).abs() / (mu_true.abs() + 1.0)).max()) < 1e-5
+    assert float(((var - var_true).abs() / var_true).max()) < 2e-3, float(((var - var_true).abs() / var_true).max())
+    # (2) consumer: LN(x) folded into the GEMM, from the kernel-written statistics
+    wlin = torch.randn(512, K, device=DEV, generator=g) * 0.03
+    blin = torch.randn(512, device=DEV, generator=g) * 0.1
+    wf = (wlin * gamma[None, :]).bfloat16()
+    c = wf.float().sum(1).contiguous()
+    bfold = (blin + wlin @ beta).contiguous()
+    o2 = torch.empty(M, 512, device=DEV, dtype=torch.bfloat16)
+    D.linear_bf16_fold(r, wf, bfold, "bias", o2, a_stats=st, col_c=c, ln_eps=1e-12)
+    xn = ((rf - mu_true[:, None]) * torch.rsqrt(var_true[:, None] + 1e-12)).float()
+    want = xn @ wf.float().t() + bfold
+    scale = float(want.abs().mean())
+    err = (o2.float() - want).abs()
+    assert float(err.mean()) < 0.02 * scale + 4e-3, (float(err.mean()), scale)
+    # (3) consumer: residual normalised on the fly
+    o3 = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    D.linear_bf16_fold(a0, w0, None, "resid", o3, resid=r, r_stats=st, r_gamma=gamma, r_beta=beta)
+    want3 = F.layer_norm(r.float(), (N,), gamma, beta, 1e-12)
+    err3 = (o3.float() - want3).abs()
+    assert float(err3.mean()) < 0.01 * float(want3.abs().mean()) + 2e-3, (float(err3.mean()), float(want3.abs().mean()))
 
 
 def test_device_side_row_count_and_accumulation():
@@ -84,7 +141,7 @@ def test_device_side_row_count_and_accumulation():
     want = a[:rows].float() @ w.float().t() + r[:rows].float()
     assert float((out[:rows].float() - want).abs().max()) < 0.06
     assert (out[rows:] == 7.0).all() and (st[rows:] == 0).all()          # nothing past the device-side count is touched
-    torch.testing.assert_close(st[:rows], _stats(want), atol=0.05, rtol=2e-3)
+    torch.testing.assert_close(st[:rows], _stats(want), atol=0.08, rtol=3e-3)
 
 
 def test_folded_trunk_matches_the_unfolded_one():

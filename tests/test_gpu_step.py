@@ -37,16 +37,20 @@ def test_fused_step_matches_oracle(kw):
     ga, gb = a.flat.grad, b.flat.grad
     assert float(gb.norm()) > 0
     rel = float((ga - gb).norm() / gb.norm())
-    assert rel < 5e-2, rel
-    # per tensor: within 10% of its own norm, or (for gradients that are small because their terms nearly cancel, e.g.
-    # the additive-attention fc1 whose per-position factors sum to ~0) within 1% of the whole gradient's norm
+    assert rel < 3e-2, rel
+    # per tensor: within 3% of its own norm. The two additive-attention fc1 layers are the exception: their gradients are
+    # small because the per-position factors sum to ~0 (the soft-max Jacobian), so what is left is dominated by the bf16
+    # rounding of much larger terms; they must stay within 1% of the whole gradient's norm instead.
     report = []
     for name in a.flat.names:
         x, y = a.flat.view(name, grad=True), b.flat.view(name, grad=True)
         err, ny = float((x - y).norm()), float(y.norm())
-        report.append((name, err, ny))
+        report.append((name, round(err / max(ny, 1e-30), 4)))
         if ny > 1e-8:
-            assert err < 0.1 * ny or err < 1e-2 * float(gb.norm()), (name, err, ny, float(gb.norm()), report)
+            if "additive_attention.att_fc1" in name:
+                assert err < 0.1 * ny or err < 1e-2 * float(gb.norm()), (name, err, ny, float(gb.norm()), report)
+            else:
+                assert err < 0.03 * ny, (name, err, ny, report)
     sa, sb = fused.scores(cand, his), oracle.scores(cand, his)
     torch.testing.assert_close(sa, sb, atol=1e-2, rtol=1e-2)
 

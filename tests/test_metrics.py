@@ -60,3 +60,21 @@ def test_evaluation_split():
     up = load_reference_module("evaluation_functions")
     if up is not None:
         np.testing.assert_allclose(out, up.evaluation_split(news_vecs, user_vecs, samples, nid2index), atol=1e-9)
+
+
+def test_tied_scores_rank_like_the_reference():
+    """All-equal scores with the positive in column 0: upstream's argsort()[::-1] puts it last (ADVICE r1)."""
+    import torch
+    from fedrec_b200.utils.metrics import batched_ranking_metrics, compute_amn
+    y = [1, 0, 0, 0, 0]
+    s = [0.5] * 5
+    auc, mrr, n5, n10 = compute_amn(y, s)
+    m = batched_ranking_metrics(torch.tensor([s]), torch.tensor([y]))
+    assert float(m["mrr"][0]) == pytest.approx(mrr) == pytest.approx(0.2)
+    assert float(m["ndcg5"][0]) == pytest.approx(n5) and float(m["ndcg10"][0]) == pytest.approx(n10)
+    assert float(m["auc"][0]) == pytest.approx(auc) == pytest.approx(0.5)
+    # partial ties
+    y2, s2 = [1, 0, 0, 1, 0], [0.7, 0.7, 0.2, 0.2, 0.9]
+    ref = compute_amn(y2, s2)
+    m2 = batched_ranking_metrics(torch.tensor([s2]), torch.tensor([y2]))
+    assert [float(m2[k][0]) for k in ("auc", "mrr", "ndcg5", "ndcg10")] == pytest.approx(list(ref))
