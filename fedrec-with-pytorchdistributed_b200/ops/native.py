@@ -125,7 +125,8 @@ def lib() -> ctypes.CDLL:
                 _load_error = f"{_LIB} not built; run `python -c 'import __graft_entry__ as g; g.build()'`"
                 raise RuntimeError(_load_error)
             try:
-                l = ctypes.CDLL(_LIB, mode=ctypes.RTLD_GLOBAL)
+                # FEDREC_LIB: load another build of the same ABI (same-box A/B of a kernel change; scripts/ab_lib.sh)
+                l = ctypes.CDLL(os.environ.get("FEDREC_LIB") or _LIB, mode=ctypes.RTLD_GLOBAL)
                 _bind(l)
             except OSError as e:
                 _load_error = str(e)

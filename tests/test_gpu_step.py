@@ -46,7 +46,11 @@ def test_fused_step_matches_oracle(kw):
         x, y = a.flat.view(name, grad=True), b.flat.view(name, grad=True)
         err, ny = float((x - y).norm()), float(y.norm())
         report.append((name, round(err / max(ny, 1e-30), 4)))
-        if ny > 1e-8:
+        if ny < 1e-4 * float(gb.norm()):
+            # true value ~0 (a soft-max is invariant to a constant shift of its logits: the att_fc2 biases, and with few
+            # valid positions the att_fc2 weights): only an absolute bound means anything
+            assert err < 1e-3 * float(gb.norm()), (name, err, ny, report)
+        else:
             if "additive_attention.att_fc1" in name:
                 assert err < 0.1 * ny or err < 1e-2 * float(gb.norm()), (name, err, ny, float(gb.norm()), report)
             else:
@@ -166,9 +170,9 @@ def test_pipelined_optimizer_equals_step_then_aggregate_then_adam(graph):
     # accumulation. The weights themselves are compared in bulk: Adam divides by sqrt(v), so a coordinate whose gradient
     # is rounding noise (the cancellation-prone text-head fc1) moves by +-lr whichever way that rounding went.
     rel_m = float((a.flat.exp_avg - b.flat.exp_avg).norm() / b.flat.exp_avg.norm())
-    assert rel_m < 1e-3, rel_m
+    assert rel_m < 5e-3, rel_m
     rel_v = float((a.flat.exp_avg_sq - b.flat.exp_avg_sq).norm() / b.flat.exp_avg_sq.norm())
-    assert rel_v < 1e-3, rel_v
+    assert rel_v < 5e-3, rel_v
     diff = (a.flat.param - b.flat.param).abs()
     assert float(diff.max()) < 5e-3 and float((diff > 2e-5).float().mean()) < 1e-2, (float(diff.max()), float((diff > 2e-5).float().mean()))
     rel_p = float((a.flat.param - b.flat.param).norm() / b.flat.param.norm())
