@@ -52,6 +52,7 @@ struct GemmParams {
   float* stats_out;           // [M, N/64, 2] = (sum, M2 about the slice mean) of every 64-column slice of the output rows
   float ln_eps;
   int a_dim, r_dim;           // widths the two statistics were taken over
+  int tail_split;             // CTA-pair 256-wide kernels: cut the tiles of a short last round in two (see the kernel)
 };
 
 // CG = 1: one CTA per 128 x BN tile. CG = 2: a CTA pair (cta_group::2) per 256 x BN tile; each CTA stages its own
@@ -73,10 +74,16 @@ struct Cfg {
   static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024 /*align slack*/ + 512 /*barriers*/ + kBiasBytes;
 };
 
-// Exact-form GELU 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz–Stegun 7.1.25 (|err| < 2.5e-5, two orders below
-// bf16 resolution). The GELU epilogue is FMA-pipe bound (the tile's 32k elements share the SM with the tensor pipe), so
-// the form is chosen for instruction count: two MUFU ops (rcp.approx, ex2.approx) + 9 FP32 ops per element.
+// GELU in the epilogue. The epilogue shares the SM's issue slots with nothing else but is on the critical path for the
+// K = 768 GEMMs (12 k-blocks per tile), so the form is chosen for instruction count:
+//   default        0.5 x (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3)))   5 FP32 ops + 1 MUFU (tanh.approx) per element.
+//                  Distance to the exact erf form: < 5e-4 absolute everywhere (the approximation's 3e-4 plus
+//                  tanh.approx's 2^-11), a tenth of the bf16 rounding of the stored result. Measured on the FFN1 shape
+//                  (26880 x 3072 x 768): 101 us against 120 us for the erf form and 103 us for a bias-only epilogue.
+//   -DFEDREC_GELU_ERF  0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz–Stegun 7.1.25 (|err| < 2.5e-5):
+//                  9 FP32 ops + 2 MUFU (rcp.approx, ex2.approx) per element; HF DistilBERT's "gelu" to 2.5e-5.
 __device__ __forceinline__ float gelu_erf(float x) {
+#ifdef FEDREC_GELU_ERF
   float t, e;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.33267435f /* 0.47047 / sqrt 2 */, fabsf(x), 1.0f)));
   const float u = x * 0.84932180f;                                  // sqrt(log2(e) / 2): exp(-x^2/2) = 2^-(u^2)
@@ -87,6 +94,13 @@ __device__ __forceinline__ float gelu_erf(float x) {
   const float erf_abs = fmaf(-poly, e, 1.0f);
   const float hx = 0.5f * x;
   return fmaf(hx, copysignf(erf_abs, x), hx);
+#else
+  const float inner = x * fmaf(0.0356774081f, x * x, 0.7978845608f);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(inner));
+  const float hx = 0.5f * x;
+  return fmaf(hx, t, hx);
+#endif
 }
 __device__ __forceinline__ float tanh_fast(float x) {
   float y;
@@ -126,7 +140,7 @@ template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG, bool FOLD = false
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                     const __grid_constant__ CUtensorMap tmap_o, const __grid_constant__ CUtensorMap tmap_r,
-                    const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmap_bh, const GemmParams p) {
   using C = Cfg<BN, TMA_EPI, CG, FOLD>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -155,6 +169,22 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   const int k_blocks = (p.K + BK - 1) / BK;
   const int num_tiles = m_blocks * n_blocks;
   const int tile_first = (int)blockIdx.x / CG, tile_step = (int)gridDim.x / CG;
+  // Tail split (CTA pairs, 256-wide tiles). The tiles are dealt round-robin to the pairs, so when their number is not a
+  // multiple of the pair count the last round keeps a few pairs busy for a whole tile while the rest idle (N = 768:
+  // 315 tiles on 74 pairs = 4 full rounds + 19 tiles). If that last round fills at most half of the pairs, each of its
+  // tiles is cut into two 256 x 128 halves (cta_group::2 MMAs with N = 128, B boxes of 64 rows per CTA through a second
+  // tensor map), which halves the length of the last round. Work items >= split_from are such halves.
+  constexpr bool kTailSplit = (CG == 2 && BN == 256);
+  int split_from = num_tiles, num_items = num_tiles;
+  if (kTailSplit && p.tail_split) {
+    const int full = (num_tiles / tile_step) * tile_step, tail = num_tiles - full;
+    if (tail > 0 && 2 * tail <= tile_step) { split_from = full; num_items = full + 2 * tail; }
+  }
+  // item -> (tile, half): half = -1 for a whole tile, 0 / 1 for the left / right 128 columns of a split tile
+  auto decode = [&](int item, int& tile, int& half) {
+    if (item < split_from) { tile = item; half = -1; }
+    else { tile = split_from + ((item - split_from) >> 1); half = (item - split_from) & 1; }
+  };
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
@@ -196,9 +226,12 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+      for (int item = tile_first; item < num_items; item += tile_step) {
+        int tile, half;
+        decode(item, tile, half);
         const int m0 = (tile / n_blocks) * (BM * CG) + (int)cta_rank * BM;
-        const int n0 = (tile % n_blocks) * BN + (int)cta_rank * (BN / CG) * (CG - 1);
+        const int n0 = half < 0 ? (tile % n_blocks) * BN + (int)cta_rank * (BN / CG) * (CG - 1)
+                                : (tile % n_blocks) * BN + half * (BN / 2) + (int)cta_rank * (BN / 4);
         for (int kb = 0; kb < k_blocks; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1, 11);
           uint8_t* sa = smem + stage * C::kStageBytes;
@@ -206,9 +239,10 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
           if (CG == 2) {
             // both CTAs' bytes are credited to the leader's barrier; only the leader arrives on it
             const uint32_t leader_bar = mapa_u32(smem_u32(&full_bar[stage]), 0);
-            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * C::kStageBytes);
+            if (cta_rank == 0)
+              mbar_arrive_expect_tx(&full_bar[stage], half < 0 ? 2 * C::kStageBytes : 2 * (C::kABytes + C::kBBytes / 2));
             tma_load_2d_pair(sa, &tmap_a, leader_bar, kb * BK, m0);
-            tma_load_2d_pair(sb, &tmap_b, leader_bar, kb * BK, n0);
+            tma_load_2d_pair(sb, half < 0 ? &tmap_b : &tmap_bh, leader_bar, kb * BK, n0);
           } else {
             mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
             tma_load_2d(sa, &tmap_a, &full_bar[stage], kb * BK, m0);
@@ -221,12 +255,14 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
   } else if (warp == 1) {
     // ------------------------------- MMA issuer ---------------------------------
     if (lane == 0 && cta_rank == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN);
+      constexpr uint32_t idesc_full = make_idesc_bf16(BM * CG, BN);
+      constexpr uint32_t idesc_half = make_idesc_bf16(BM * CG, BN / 2);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+      for (int item = tile_first; item < num_items; item += tile_step) {
+        const uint32_t idesc = (kTailSplit && item >= split_from) ? idesc_half : idesc_full;
         mbar_wait(&tmem_empty[acc], acc_phase ^ 1, 12);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
@@ -274,14 +310,16 @@ gemm_bf16_tn_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_con
       if (CG == 2 && cta_rank != 0) mbar_arrive_cluster(empty_remote[a]);
       else mbar_arrive(&tmem_empty[a]);
     };
-    for (int tile = tile_first; tile < num_tiles; tile += tile_step) {
+    for (int item = tile_first; item < num_items; item += tile_step) {
+      int tile, half;
+      decode(item, tile, half);
       const int m0 = (tile / n_blocks) * (BM * CG) + (int)cta_rank * BM;
-      const int n0 = (tile % n_blocks) * BN;
+      const int n0 = (tile % n_blocks) * BN + (half > 0 ? BN / 2 : 0);
       const int brow0 = m0 + quarter * 32;                   // first row of this warp's 32-row box
       const int row = brow0 + lane;
       const bool row_ok = row < M;
       const int wcol0 = n0 + cgroup * kCols;                 // first column of this warp
-      const bool work = active && wcol0 < p.N;               // warp-uniform
+      const bool work = active && wcol0 < p.N && (half < 0 || cgroup * kCols < BN / 2);   // warp-uniform
       const bool box_full = brow0 + 32 <= M;                 // TMA store may cover the whole box
       // While the MMAs of this tile are still running: stage the bias slice, make sure the previous TMA store has
       // drained this warp's box, and start the residual load — nothing after "accumulator ready" waits on memory.
@@ -530,7 +568,7 @@ int make_tmap_bf16_2d_box(CUtensorMap* out, const void* base, long long rows, lo
   return 0;
 }
 
-struct Maps { CUtensorMap a, b, o, r; };
+struct Maps { CUtensorMap a, b, o, r, bh; };
 
 template <int BN, int EPI, bool OUT_F32, bool TMA_EPI, int CG, bool FOLD = false>
 static int launch(const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t s) {
@@ -563,7 +601,7 @@ static int launch(const Maps& m, const GemmParams& p, int max_ctas, cudaStream_t
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  FR_CHECK(cudaLaunchKernelEx(&cfg, kern, m.a, m.b, m.o, m.r, p));
+  FR_CHECK(cudaLaunchKernelEx(&cfg, kern, m.a, m.b, m.o, m.r, m.bh, p));
   return 0;
 }
 
@@ -655,6 +693,11 @@ static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const
   Maps maps;
   if (int e = make_tmap_bf16_2d(&maps.a, A, M, K, lda, BM)) return e;
   if (int e = make_tmap_bf16_2d(&maps.b, W, N, K, ldw, block_n / cta_group)) return e;
+  maps.bh = maps.b;
+  static const bool env_tail = [] { const char* e = getenv("FEDREC_GEMM_TAIL_SPLIT"); return !(e && atoi(e) == 0); }();
+  const bool tail_split = env_tail && cta_group == 2 && block_n == 256;
+  if (tail_split)                                   // B boxes of the half-width tiles of a short last round: 64 rows per CTA
+    if (int e = make_tmap_bf16_2d(&maps.bh, W, N, K, ldw, block_n / 4)) return e;
   // bf16 outputs of the wide tiles leave through shared memory + TMA (FEDREC_GEMM_EPI=direct disables it).
   // For single CTAs the staging boxes cost a pipeline stage, which only pays off when the epilogue dominates (short K).
   static const int env_epi = [] { const char* e = getenv("FEDREC_GEMM_EPI"); return !e ? 0 : (strcmp(e, "direct") == 0 ? -1 : 1); }();
@@ -674,7 +717,7 @@ static int gemm_bf16_impl(const void* A, const void* W, const float* bias, const
   p.bias = bias; p.resid = (const __nv_bfloat16*)resid; p.out = out; p.m_dev = m_dev; p.m_scale = m_scale;
   p.M = M; p.N = N; p.K = K; p.ldo = ldo; p.ldr = ldr;
   p.a_stats = nullptr; p.col_c = nullptr; p.r_stats = nullptr; p.r_gamma = nullptr; p.r_beta = nullptr; p.stats_out = nullptr;
-  p.ln_eps = 0.f; p.a_dim = K; p.r_dim = N;
+  p.ln_eps = 0.f; p.a_dim = K; p.r_dim = N; p.tail_split = tail_split ? 1 : 0;
   cudaStream_t s = (cudaStream_t)stream;
   const int ctas = sm_count();
   if (fold) {

@@ -99,3 +99,18 @@ def test_dynamic_m_from_device():
 
 def test_many_waves_persistent():
     _check(148 * 128 * 3 + 5, 256, 192, block_n=256)
+
+
+@pytest.mark.parametrize("M,N,K,epi,tma", [
+    (26880, 768, 768, "resid", 1),      # 315 tiles on 74 pairs: the 19 tiles of the last round are cut in two
+    (26880, 768, 3072, "resid", -1),    # same, direct epilogue (the FFN2 variant)
+    (26880, 3072, 768, "gelu", 1),      # 1260 tiles: 2 left over
+    (2000, 768, 768, "bias", 1),        # 24 tiles <= half the pairs: every tile is split
+    (2100, 1000, 768, "bias", 1),       # ragged N: the right half of the last column tile is partly (or wholly) past N
+    (26880, 2304, 768, "bias", 1),      # 945 tiles: last round of 57 > half the pairs, nothing is split
+])
+def test_tail_split_of_a_short_last_round(M, N, K, epi, tma):
+    """CTA-pair kernels deal tiles round-robin; a last round that fills at most half of the pairs is run as 256 x 128
+    half tiles (N = 128 MMAs, 64-row B boxes). Same results as the fp32 reference, with and without a device-side M."""
+    _check(M, N, K, epi, block_n=256, cta_group=2, tma_epilogue=tma, seed=3)
+    _check(M, N, K, epi, block_n=256, cta_group=2, tma_epilogue=tma, seed=4, m_dev=M // 30 - 3, m_scale=30)
