@@ -9,12 +9,14 @@ declare -A FILTER=(
   [gemm_ffn1]=gemm_bf16_tn_kernel [gemm_ffn2]=gemm_bf16_tn_kernel [gemm_qkv]=gemm_bf16_tn_kernel [gemm_out]=gemm_bf16_tn_kernel
   [gemm_fold_ffn1]=gemm_bf16_tn_kernel [gemm_fold_ffn2]=gemm_bf16_tn_kernel [gemm_fold_qkv]=gemm_bf16_tn_kernel
   [gemm_fold_out]=gemm_bf16_tn_kernel [attention]=bert_attention_tc [gemm_grad]=gemm_grad_kernel [layernorm]=layernorm_kernel
-  [aggregate]=aggregate_kernel)
+  [aggregate]=agg_)
+declare -A COUNT=([aggregate]=7)
+declare -A SKIP=([aggregate]=14)
 for t in "$@"; do
   f=${FILTER[$t]:-}
   if [ -z "$f" ]; then echo "unknown target $t"; continue; fi
   if timeout 120 python scripts/profile_target.py "$t" > "gpurun_out/ncu/plain_$t.log" 2>&1; then
-    timeout 400 ncu --set full --clock-control none --import-source on -k "regex:$f" -s 2 -c 1 -f \
+    timeout 400 ncu --set full --clock-control none --import-source on -k "regex:$f" -s ${SKIP[$t]:-2} -c ${COUNT[$t]:-1} -f \
       -o "gpurun_out/ncu/$t" python scripts/profile_target.py "$t" > "gpurun_out/ncu/ncu_$t.log" 2>&1
     echo "$t: ncu exit $?"
   else

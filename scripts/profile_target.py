@@ -27,12 +27,13 @@ if what.startswith("gemm_fold_"):
     if epi == "resid":                       # residual normalised on the fly + row statistics of the output
         r = torch.randn(M, N, device=DEV).bfloat16()
         rf = r.float().view(M, N // 64, 64)
-        kw = dict(resid=r, r_stats=torch.stack([rf.sum(2), (rf * rf).sum(2)], 2).contiguous(),
+        kw = dict(resid=r, r_stats=torch.stack([rf.sum(2), ((rf - rf.mean(2, keepdim=True)) ** 2).sum(2)], 2).contiguous(),
                   r_gamma=torch.rand(N, device=DEV) + 0.5, r_beta=torch.randn(N, device=DEV) * 0.1,
                   stats_out=torch.empty(M, N // 64, 2, device=DEV))
     else:                                    # LayerNorm of the input applied in the epilogue
         xf = x.float().view(M, K // 64, 64)
-        kw = dict(a_stats=torch.stack([xf.sum(2), (xf * xf).sum(2)], 2).contiguous(), col_c=w.float().sum(1).contiguous())
+        kw = dict(a_stats=torch.stack([xf.sum(2), ((xf - xf.mean(2, keepdim=True)) ** 2).sum(2)], 2).contiguous(),
+                  col_c=w.float().sum(1).contiguous())
     for _ in range(6):
         D.linear_bf16_fold(x, w, b, epi, out, **kw)
 elif what.startswith("gemm_") and what != "gemm_grad":
@@ -64,8 +65,12 @@ elif what == "aggregate":
     bufs = [h.alloc_f32(n) for h in hs]
     for b_ in bufs:
         b_.normal_()
-    for _ in range(6):
-        hs[0].grad_allreduce_(bufs[0], clip=2.0, noise_std=0.1, seed=3, scale=1.0 / W, ranks_here=W)
+    ps = [torch.randn(n, device=DEV) for _ in range(W)]
+    ms = [torch.zeros(n, device=DEV) for _ in range(W)]
+    vs = [torch.zeros(n, device=DEV) for _ in range(W)]
+    for it in range(4):      # one aggregation = sumsq, publish, wait, reduce, wait, adam, commit (7 launches)
+        hs[0].grad_allreduce_adam_(bufs[0], clip=2.0, noise_std=0.1, seed=3, scale=1.0 / W, params=ps, exp_avg=ms,
+                                   exp_avg_sq=vs, step=it + 1, lr=5e-5, b1=0.9, b2=0.999, eps=1e-8, ranks_here=W)
 elif what == "step":
     from fedrec_b200.config import FedRecConfig
     from fedrec_b200.data import make_synthetic_mind
