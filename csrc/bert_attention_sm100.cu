@@ -287,6 +287,223 @@ bert_attention_tc_kernel(const __grid_constant__ CUtensorMap tmap_qkv, const Att
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// N4 on the tensor cores: the user encoder's multi-head self-attention over the click history (reference:
+// attention.py:32-45 ScaledDotProductAttention, :69-81 MultiHeadAttention; 20 heads x 20 dims over L <= 64 clicks).
+//
+// Same block-diagonal tiling as the title kernel above with 64-row slots: two users share a 128-row tile,
+//   S[128 x 128] = Q_h K_h^T (head dim zero-padded to 32: two UMMA K steps),  O[128 x 64] = P V_h (dims >= dk are zero).
+// What differs from the title attention:
+//   * the reference soft-max has no max subtraction and a +1e-8 in the denominator (attention.py:39-42). Subtracting the
+//     row maximum m for range, the same value is  exp(s - m) / (sum_j exp(s_j - m) mask_j + 1e-8 exp(-m)) ;
+//   * a masked history slot multiplies its probability by zero (attention.py:40-41) instead of adding -inf to its score,
+//     so it still takes part in the maximum; key columns outside the history (j >= L) are excluded outright;
+//   * a head is 20 bf16 = 40 bytes wide, which no TMA box can address (boxes are multiples of 16 bytes), so each thread
+//     copies its own row of Q, K and V into the 128B-swizzled K-major layout with plain 8-byte loads (15 KB per job);
+//   * (row maximum, denominator) are stored per query for the backward kernel, exactly like the CUDA-core forward.
+// One CTA = 4 warps, thread r owns row r; 80 KB shared memory, 256 TMEM columns, two CTAs per SM.
+// ---------------------------------------------------------------------------------------------------------------------
+struct UeAttParams {
+  const __nv_bfloat16* qkv;   // [B*L, 3*H*dk]  (q | k | v)
+  const int* his_ids;         // [B*L] or null: id 0 = padding slot (only read with use_mask)
+  __nv_bfloat16* ctx;         // [B*L, H*dk]
+  float* stats;               // [B*H*L, 2] = (row maximum in natural-log units, denominator)
+  int B, L, H, dk, use_mask;
+  float scale;                // 1 / sqrt(dk)
+};
+
+__global__ void __launch_bounds__(128, 2) ue_attention_tc_kernel(const UeAttParams p) {
+  constexpr int SLOT = 64, TP = 2, NCH = 2;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + 16384;
+  uint8_t* sV = smem + 32768;
+  uint8_t* sP = smem + 49152;
+  uint64_t* bar_mma = reinterpret_cast<uint64_t*>(smem + kAttBar);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mma + 1);
+  float* sKeyBias = reinterpret_cast<float*>(smem + kAttBar + 64);   // [128] 0 or -inf (key column outside the history)
+  float* sKeyMul = sKeyBias + 128;                                   // [128] 0 (masked padding slot) or 1
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  griddep_wait();                                   // launched with the PDL attribute: the QKV GEMM is complete from here on
+  const int B = p.B, L = p.L, H = p.H, dk = p.dk;
+  const int ld = 3 * H * dk, hd = H * dk;
+  if (tid == 0) {
+    mbar_init(bar_mma, 1);
+    fence_barrier_init();
+  }
+  {   // Q, K, V and P start as zeros: padding dims, rows outside the history and P's off-diagonal blocks stay zero
+    const uint32_t z0 = smem_u32(smem) + (uint32_t)tid * 16;
+    for (int c = 0; c < (49152 + 32768) / (128 * 16); ++c)
+      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(z0 + (uint32_t)c * 2048), "r"(0u) : "memory");
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(tmem_slot, 256);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  griddep_launch();                                 // after our TMEM allocation (see the title kernel)
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tO = tmem + 128;
+  uint32_t ph_mma = 0;
+
+  const int num_tiles = (B + TP - 1) / TP;
+  const long long total_jobs = (long long)num_tiles * H;
+  const int job_begin = (int)(total_jobs * blockIdx.x / gridDim.x);
+  const int job_end = (int)(total_jobs * (blockIdx.x + 1) / gridDim.x);
+  const int my_slot = tid / SLOT, my_tok = tid - my_slot * SLOT, col0 = my_slot * SLOT;
+  const uint32_t lane_base = ((uint32_t)(warp * 32) << 16);
+  const float scale_log2 = p.scale * 1.4426950408889634f;
+  const uint32_t row_off = (uint32_t)tid * 128;     // my row inside a K-major 128B-swizzled tile
+  const uint32_t swz = (uint32_t)(tid & 7);
+  const int nquads = dk >> 2;                       // 8-byte groups of a head row (dk % 4 == 0)
+
+  int cur_tile = -1;
+  bool row_ok = false;
+  size_t grow = 0;
+  for (int job = job_begin; job < job_end; ++job) {
+    const int tile = job / H, h = job - tile * H;
+    if (tile != cur_tile) {
+      cur_tile = tile;
+      const int user = tile * TP + my_slot;
+      row_ok = my_tok < L && user < B;
+      grow = (size_t)user * L + my_tok;
+      sKeyBias[tid] = row_ok ? 0.f : -INFINITY;     // key column tid and row tid belong to the same (user, token)
+      sKeyMul[tid] = (row_ok && !(p.use_mask && p.his_ids[grow] == 0)) ? 1.f : 0.f;
+    }
+    // ---- my row of Q, K, V: 8-byte loads, 16-byte swizzled stores (chunks 0..3 = 32 dims; dims >= dk are zero) ----
+    {
+      uint32_t w[3][16];
+#pragma unroll
+      for (int o = 0; o < 3; ++o)
+#pragma unroll
+        for (int j = 0; j < 16; ++j) w[o][j] = 0u;
+      if (row_ok) {
+        const uint2* src = reinterpret_cast<const uint2*>(p.qkv + grow * ld + h * dk);
+#pragma unroll
+        for (int o = 0; o < 3; ++o) {
+          const uint2* so = src + (size_t)o * (hd >> 2);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            if (q < nquads) {
+              const uint2 v = __ldg(so + q);
+              w[o][2 * q] = v.x;
+              w[o][2 * q + 1] = v.y;
+            }
+          }
+        }
+      }
+      const uint32_t base[3] = {smem_u32(sQ) + row_off, smem_u32(sK) + row_off, smem_u32(sV) + row_off};
+#pragma unroll
+      for (int o = 0; o < 3; ++o)
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(base[o] + (((uint32_t)c ^ swz) << 4)),
+                       "r"(w[o][4 * c]), "r"(w[o][4 * c + 1]), "r"(w[o][4 * c + 2]), "r"(w[o][4 * c + 3]) : "memory");
+    }
+    fence_proxy_async();                            // generic-proxy writes → visible to the tensor core
+    tc_fence_before();
+    __syncthreads();                                // also publishes sKeyBias / sKeyMul
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t id1 = att_idesc(128, 128, 0);
+      const uint32_t q = smem_u32(sQ), k = smem_u32(sK);
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)                // head dim padded to 32 = two K steps of 16
+        umma_bf16_ss(tS, att_desc_k_sw128(q + ks * 32), att_desc_k_sw128(k + ks * 32), id1, ks > 0);
+      umma_commit(bar_mma);
+    }
+    mbar_wait(bar_mma, ph_mma, 5);
+    ph_mma ^= 1;
+    tc_fence_after();
+    // ---- soft-max over my row: my user's 64 key columns ----
+    float t[NCH * 32];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tS + lane_base + (uint32_t)(col0 + c * 32), r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int j = 0; j < 32; ++j) t[c * 32 + j] = fmaf(__uint_as_float(r[j]), scale_log2, sKeyBias[col0 + c * 32 + j]);
+    }
+#pragma unroll
+    for (int j = 0; j < NCH * 32; ++j) mx = fmaxf(mx, t[j]);
+    if (mx == -INFINITY) mx = 0.f;                  // rows outside the history: keep the math finite
+    float l = 0.f;
+    const uint32_t prow = smem_u32(sP) + (uint32_t)tid * 128;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      uint32_t packed[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const float e0 = exp2f(t[c * 32 + 2 * j] - mx) * sKeyMul[col0 + c * 32 + 2 * j];
+        const float e1 = exp2f(t[c * 32 + 2 * j + 1] - mx) * sKeyMul[col0 + c * 32 + 2 * j + 1];
+        l += e0 + e1;
+        const __nv_bfloat162 b2 = __floats2bfloat162_rn(e0, e1);
+        packed[j] = *reinterpret_cast<const uint32_t*>(&b2);
+      }
+      const int cc = col0 + c * 32;
+      const uint32_t blk = prow + (uint32_t)(cc >> 6) * kAttPBlk;
+#pragma unroll
+      for (int q4 = 0; q4 < 4; ++q4) {
+        const uint32_t chunk = (uint32_t)(((cc & 63) >> 3) + q4) ^ swz;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(blk + chunk * 16), "r"(packed[4 * q4]),
+                     "r"(packed[4 * q4 + 1]), "r"(packed[4 * q4 + 2]), "r"(packed[4 * q4 + 3]) : "memory");
+      }
+    }
+    const float z = l + 1e-8f * exp2f(-mx);         // the reference's "+ 1e-8", carried into the max-subtracted form
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t id2 = att_idesc(128, 64, 1);
+      const uint32_t pa = smem_u32(sP), v = smem_u32(sV);
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks)
+        umma_bf16_ss(tO, att_desc_k_sw128(pa + (ks >> 2) * kAttPBlk + (ks & 3) * 32), att_desc_mn_sw128(v + ks * 2048), id2, ks > 0);
+      umma_commit(bar_mma);
+    }
+    mbar_wait(bar_mma, ph_mma, 6);
+    ph_mma ^= 1;
+    tc_fence_after();
+    {
+      uint32_t r[32];
+      tmem_ld_32x32(tO + lane_base, r);             // dims 0..31 of my row; only the first dk are real
+      tmem_ld_wait();
+      if (row_ok) {
+        const float inv = 1.f / z;
+        uint2* op = reinterpret_cast<uint2*>(p.ctx + grow * hd + h * dk);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (q < nquads) {
+            const __nv_bfloat162 a = __floats2bfloat162_rn(__uint_as_float(r[4 * q]) * inv, __uint_as_float(r[4 * q + 1]) * inv);
+            const __nv_bfloat162 b = __floats2bfloat162_rn(__uint_as_float(r[4 * q + 2]) * inv, __uint_as_float(r[4 * q + 3]) * inv);
+            op[q] = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+          }
+        }
+        const int user = tile * TP + my_slot;
+        float2* sp = reinterpret_cast<float2*>(p.stats) + ((size_t)(user * H + h) * L + my_tok);
+        *sp = make_float2(mx * 0.6931471805599453f, z);       // maximum back in natural-log units, as the backward expects
+      }
+    }
+    tc_fence_before();
+    __syncthreads();                                // TMEM and the shared tiles are free for the next job
+  }
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 256);
+  }
+}
+
 }  // namespace fr
 
 using namespace fr;
@@ -315,5 +532,28 @@ FR_API int fr_bert_attention_tc(const void* qkv, const int* mask_table, const in
   int grid = jobs < 2 * num_sms() ? (int)jobs : 2 * num_sms();
   if (slot == 32) FR_CHECK(launch_pdl(bert_attention_tc_kernel<32>, dim3(grid), dim3(128), smem, (cudaStream_t)stream, tm, p));
   else FR_CHECK(launch_pdl(bert_attention_tc_kernel<64>, dim3(grid), dim3(128), smem, (cudaStream_t)stream, tm, p));
+  return 0;
+}
+
+// The user encoder's attention on the tensor cores (same contract as fr_ue_mha_fwd in user_encoder.cu, which stays as
+// the cross-check): L <= 64, dk in {4, 8, .., 32}. Replaces attention.py:32-45 / :69-81 for the click history.
+FR_API int fr_ue_attention_tc(const void* qkv, const int* his_ids, void* ctx, float* stats, int B, int L, int H, int dk,
+                              int use_mask, void* stream) {
+  FR_REQUIRE(L >= 1 && L <= 64, "fr_ue_attention_tc: L=%d must be in [1,64]", L);
+  FR_REQUIRE(dk >= 4 && dk <= 32 && dk % 4 == 0, "fr_ue_attention_tc: dk=%d must be a multiple of 4 in [4,32]", dk);
+  FR_REQUIRE(!use_mask || his_ids != nullptr, "fr_ue_attention_tc: use_mask needs his_ids");
+  if (B == 0) return 0;
+  UeAttParams p;
+  p.qkv = (const __nv_bfloat16*)qkv; p.his_ids = his_ids; p.ctx = (__nv_bfloat16*)ctx; p.stats = stats;
+  p.B = B; p.L = L; p.H = H; p.dk = dk; p.use_mask = use_mask; p.scale = 1.f / sqrtf((float)dk);
+  constexpr int smem = kAttBar + 64 + 1024 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    FR_CHECK(cudaFuncSetAttribute(ue_attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  const long long jobs = (long long)((B + 1) / 2) * H;
+  const int grid = jobs < 2LL * num_sms() ? (int)jobs : 2 * num_sms();
+  FR_CHECK(launch_pdl(ue_attention_tc_kernel, dim3(grid), dim3(128), smem, (cudaStream_t)stream, p));
   return 0;
 }

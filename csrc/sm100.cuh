@@ -54,7 +54,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 // Bounded spin: a protocol bug becomes a trap (a reported launch failure) instead of a hung GPU.
 // `tag` names the call site in the message (kernel family * 10 + barrier), so a log line says which wait gave up. The
 // report lives in a function of its own: printf's argument buffer would otherwise put a stack frame into every kernel.
-__device__ __noinline__ void mbar_timeout(int tag, uint32_t parity) {
+static __device__ __noinline__ void mbar_timeout(int tag, uint32_t parity) {
   if ((threadIdx.x & 31) == 0)
     printf("fedrec_b200: mbarrier wait timed out (site %d, block %d,%d of %d,%d, thread %d of %d, parity %u)\n", tag,
            (int)blockIdx.x, (int)blockIdx.y, (int)gridDim.x, (int)gridDim.y, (int)threadIdx.x, (int)blockDim.x, parity);

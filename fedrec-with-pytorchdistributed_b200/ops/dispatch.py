@@ -296,10 +296,14 @@ def ue_scatter_dx(dX, inv_his, d_news, p, seed, noise_std=0.0, noise_seed=0, see
     return d_news
 
 
-def ue_mha_fwd(qkv, his_ids, ctx, stats, B, L, H, dk, use_mask=False):
+def ue_mha_fwd(qkv, his_ids, ctx, stats, B, L, H, dk, use_mask=False, impl: Optional[str] = None):
+    """User-encoder self-attention forward. ``impl``: "tc" = tcgen05 kernel (default; ``FEDREC_UE_ATTN`` overrides),
+    "cuda" = the CUDA-core kernel kept as its cross-check. Same outputs and saved statistics either way."""
     lib = require_native()
-    check(lib.fr_ue_mha_fwd(qkv.data_ptr(), _p(his_ids), ctx.data_ptr(), stats.data_ptr(), B, L, H, dk, int(use_mask),
-                            stream_ptr(qkv.device)), "fr_ue_mha_fwd")
+    impl = impl or os.environ.get("FEDREC_UE_ATTN", "tc")
+    fn, name = (lib.fr_ue_attention_tc, "fr_ue_attention_tc") if impl == "tc" else (lib.fr_ue_mha_fwd, "fr_ue_mha_fwd")
+    check(fn(qkv.data_ptr(), _p(his_ids), ctx.data_ptr(), stats.data_ptr(), B, L, H, dk, int(use_mask),
+             stream_ptr(qkv.device)), name)
     count_launches(1)
     return ctx
 

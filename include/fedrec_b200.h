@@ -139,6 +139,12 @@ int fr_counter_advance(unsigned long long* ctr, unsigned long long inc, void* st
  * [B*L, H*dk], stats fp32 [B*H*L, 2]. attention.py:37-45,69-81. The backward recomputes the probabilities. */
 int fr_ue_mha_fwd(const void* qkv, const int* his_ids, void* ctx, float* stats, int B, int L, int H, int dk,
                   int use_mask, void* stream);
+/* The same attention on the tensor cores (csrc/bert_attention_sm100.cu): two users share a 128-row tile, S = QK^T and
+ * O = PV are tcgen05.mma with TMEM accumulators (head dim zero-padded to 32), the soft-max keeps the reference's
+ * exp(s)/(sum + 1e-8) form. Same arguments, outputs and stats as fr_ue_mha_fwd (L <= 64, dk % 4 == 0, dk <= 32); this is
+ * the default path of the training step. attention.py:32-45,69-81. */
+int fr_ue_attention_tc(const void* qkv, const int* his_ids, void* ctx, float* stats, int B, int L, int H, int dk,
+                       int use_mask, void* stream);
 int fr_ue_mha_bwd(const void* qkv, const void* dctx, const float* stats, const int* his_ids, void* dqkv, int B, int L,
                   int H, int dk, int use_mask, void* stream);
 

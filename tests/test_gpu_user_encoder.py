@@ -195,3 +195,36 @@ def test_text_head_backward_matches_autograd():
     assert abs(float(d_b2) - float(b2r.grad)) < 1e-3 * float(w2r.grad.abs().max())
     assert rel(dW1, w1r.grad) < 3e-2, rel(dW1, w1r.grad)
     assert rel(db1, b1r.grad) < 3e-2
+
+
+@pytest.mark.parametrize("B,L,H,dk,use_mask", [(7, 50, 20, 20, False), (7, 50, 20, 20, True), (50, 50, 20, 20, False),
+                                               (3, 64, 4, 32, True), (5, 33, 6, 16, False), (1, 1, 2, 20, False)])
+def test_tensor_core_user_attention_matches_the_reference_and_the_cuda_core_kernel(B, L, H, dk, use_mask):
+    """fr_ue_attention_tc (tcgen05, two users per 128-row tile, head dim padded to 32) against attention.py's
+    exp(s)/(sum + 1e-8) attention in fp32 and against the CUDA-core kernel, including the (max, denominator) pairs the
+    backward kernel consumes; the backward run on the tensor-core kernel's statistics must match autograd."""
+    ops.require_native()
+    g = torch.Generator(device=DEV).manual_seed(11)
+    qkv = (torch.randn(B * L, 3 * H * dk, device=DEV, generator=g) * 0.8).bfloat16()
+    his = torch.randint(0, 3, (B, L), device=DEV, generator=g, dtype=torch.int32)
+    his[:, 0] = 1
+    ctx_tc = torch.full((B * L, H * dk), 7.0, device=DEV, dtype=torch.bfloat16)
+    ctx_cc = torch.zeros_like(ctx_tc)
+    st_tc = torch.zeros(B * H * L, 2, device=DEV)
+    st_cc = torch.zeros_like(st_tc)
+    D.ue_mha_fwd(qkv, his.reshape(-1), ctx_tc, st_tc, B, L, H, dk, use_mask, impl="tc")
+    D.ue_mha_fwd(qkv, his.reshape(-1), ctx_cc, st_cc, B, L, H, dk, use_mask, impl="cuda")
+    qf = qkv.float().requires_grad_()
+    q, k, v = [t.view(B, L, H, dk).transpose(1, 2) for t in qf.split(H * dk, dim=1)]
+    s = q @ k.transpose(-1, -2) / dk ** 0.5
+    km = (his != 0).float()[:, None, None, :] if use_mask else None
+    want = (ref.exp_normalise(s, -1, km) @ v).transpose(1, 2).reshape(B * L, H * dk)
+    torch.testing.assert_close(ctx_tc.float(), want, atol=2e-2, rtol=2e-2)
+    torch.testing.assert_close(ctx_tc.float(), ctx_cc.float(), atol=2e-2, rtol=2e-2)
+    torch.testing.assert_close(st_tc[:, 0], st_cc[:, 0], atol=2e-3, rtol=1e-4)       # row maxima (natural-log units)
+    torch.testing.assert_close(st_tc[:, 1], st_cc[:, 1], atol=1e-4, rtol=2e-3)       # denominators
+    dctx = (torch.randn(B * L, H * dk, device=DEV, generator=g) * 0.1).bfloat16()
+    dqkv = torch.zeros_like(qkv)
+    D.ue_mha_bwd(qkv, dctx, st_tc, his.reshape(-1), dqkv, B, L, H, dk, use_mask)
+    want.backward(dctx.float())
+    torch.testing.assert_close(dqkv.float(), qf.grad, atol=3e-3, rtol=3e-2)
