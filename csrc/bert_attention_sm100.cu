@@ -504,6 +504,263 @@ __global__ void __launch_bounds__(128, 2) ue_attention_tc_kernel(const UeAttPara
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// N5 on the tensor cores: backward of the user encoder's self-attention. dctx bf16 [B*L, H*dk] -> dqkv bf16
+// [B*L, 3*H*dk], probabilities rebuilt from q, k and the forward's (row maximum, denominator). Autograd of
+// attention.py:32-45 for the click history.
+//
+// Per (two-user tile, head), every product with the two operand forms the forward already uses (A K-major x B K-major,
+// A K-major x B MN-major):
+//   S  = Q K^T                     -> P_ij = exp(s_ij - m_i) mask_j / z_i         (thread i owns row i: registers)
+//   dP = dO V^T                       dS_ij = P_ij (dP_ij - sum_j P_ij dP_ij)
+//   dQ = scale * dS K                 A = dS as written row by row (K-major),              B = K as loaded (MN-major)
+//   dK = scale * dS^T Q               A = dS^T: thread i writes its row as column i,       B = Q as loaded (MN-major)
+//   dV = P^T dO                       A = P^T, same transposed write,                      B = dO as loaded (MN-major)
+// The transposed writes are 2-byte shared-memory stores whose 32 lanes cover 64 contiguous bytes of one row: no bank
+// conflicts. Off-diagonal (other user's) blocks of dS, dS^T and P^T are zeroed once and never touched.
+// 160 KB of shared memory (Q, K, V, dO 16 KB each; dS, dS^T, P^T 32 KB each) and 448 TMEM columns: one CTA per SM.
+// ---------------------------------------------------------------------------------------------------------------------
+struct UeAttBwdParams {
+  const __nv_bfloat16* qkv;   // [B*L, 3*H*dk]
+  const __nv_bfloat16* dctx;  // [B*L, H*dk]
+  const float* stats;         // [B*H*L, 2] from the forward
+  const int* his_ids;         // [B*L] or null
+  __nv_bfloat16* dqkv;        // [B*L, 3*H*dk]
+  int B, L, H, dk, use_mask;
+  float scale;
+};
+constexpr int kUeBwdTile = 16384;                    // one 128 x 64 bf16 operand tile
+constexpr int kUeBwdMat = 32768;                     // one 128 x 128 bf16 matrix (two 64-column blocks)
+constexpr int kUeBwdBar = 4 * kUeBwdTile + 3 * kUeBwdMat;
+
+__global__ void __launch_bounds__(128, 1) ue_attention_bwd_tc_kernel(const UeAttBwdParams p) {
+  constexpr int SLOT = 64, TP = 2;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw + 1023u) & ~1023u) - raw);
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + kUeBwdTile;
+  uint8_t* sV = smem + 2 * kUeBwdTile;
+  uint8_t* sG = smem + 3 * kUeBwdTile;               // dO
+  uint8_t* sDS = smem + 4 * kUeBwdTile;              // dS   [query][key]
+  uint8_t* sDST = sDS + kUeBwdMat;                   // dS^T [key][query]
+  uint8_t* sPT = sDST + kUeBwdMat;                   // P^T  [key][query]
+  uint64_t* bar_mma = reinterpret_cast<uint64_t*>(smem + kUeBwdBar);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_mma + 1);
+  float* sKeyBias = reinterpret_cast<float*>(smem + kUeBwdBar + 64);
+  float* sKeyMul = sKeyBias + 128;
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  griddep_wait();
+  const int B = p.B, L = p.L, H = p.H, dk = p.dk;
+  const int ld = 3 * H * dk, hd = H * dk;
+  if (tid == 0) {
+    mbar_init(bar_mma, 1);
+    fence_barrier_init();
+  }
+  {
+    const uint32_t z0 = smem_u32(smem) + (uint32_t)tid * 16;
+    for (int c = 0; c < kUeBwdBar / (128 * 16); ++c)
+      asm volatile("st.shared.v4.b32 [%0], {%1, %1, %1, %1};" ::"r"(z0 + (uint32_t)c * 2048), "r"(0u) : "memory");
+  }
+  if (warp == 0) {
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+  }
+  fence_proxy_async();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  griddep_launch();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tDP = tmem + 128, tDQ = tmem + 256, tDK = tmem + 320, tDV = tmem + 384;
+  uint32_t ph_mma = 0;
+
+  const int num_tiles = (B + TP - 1) / TP;
+  const long long total_jobs = (long long)num_tiles * H;
+  const int job_begin = (int)(total_jobs * blockIdx.x / gridDim.x);
+  const int job_end = (int)(total_jobs * (blockIdx.x + 1) / gridDim.x);
+  const int my_slot = tid / SLOT, my_tok = tid - my_slot * SLOT, col0 = my_slot * SLOT;
+  const uint32_t lane_base = ((uint32_t)(warp * 32) << 16);
+  const float scale_log2 = p.scale * 1.4426950408889634f;
+  const uint32_t row_off = (uint32_t)tid * 128;
+  const uint32_t swz = (uint32_t)(tid & 7);
+  const int nquads = dk >> 2;
+  // my element (row j, column tid) of a transposed 128 x 128 matrix: 64-column block tid / 64, 16-byte chunk
+  // ((tid % 64) / 8) ^ (j % 8) of row j, bf16 (tid % 8) inside it
+  const uint32_t t_blk = (uint32_t)(tid >> 6) * 16384u, t_chunk = (uint32_t)((tid & 63) >> 3), t_in = (uint32_t)(tid & 7) * 2u;
+
+  int cur_tile = -1;
+  bool row_ok = false;
+  size_t grow = 0;
+  for (int job = job_begin; job < job_end; ++job) {
+    const int tile = job / H, h = job - tile * H;
+    if (tile != cur_tile) {
+      cur_tile = tile;
+      const int user = tile * TP + my_slot;
+      row_ok = my_tok < L && user < B;
+      grow = (size_t)user * L + my_tok;
+      sKeyBias[tid] = row_ok ? 0.f : -INFINITY;
+      sKeyMul[tid] = (row_ok && !(p.use_mask && p.his_ids[grow] == 0)) ? 1.f : 0.f;
+    }
+    // ---- my row of Q, K, V, dO ----
+    {
+      uint32_t w[4][16];
+#pragma unroll
+      for (int o = 0; o < 4; ++o)
+#pragma unroll
+        for (int j = 0; j < 16; ++j) w[o][j] = 0u;
+      if (row_ok) {
+        const uint2* src = reinterpret_cast<const uint2*>(p.qkv + grow * ld + h * dk);
+        const uint2* gsrc = reinterpret_cast<const uint2*>(p.dctx + grow * hd + h * dk);
+#pragma unroll
+        for (int o = 0; o < 4; ++o) {
+          const uint2* so = o < 3 ? src + (size_t)o * (hd >> 2) : gsrc;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            if (q < nquads) {
+              const uint2 v = __ldg(so + q);
+              w[o][2 * q] = v.x;
+              w[o][2 * q + 1] = v.y;
+            }
+          }
+        }
+      }
+      const uint32_t base[4] = {smem_u32(sQ) + row_off, smem_u32(sK) + row_off, smem_u32(sV) + row_off, smem_u32(sG) + row_off};
+#pragma unroll
+      for (int o = 0; o < 4; ++o)
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(base[o] + (((uint32_t)c ^ swz) << 4)),
+                       "r"(w[o][4 * c]), "r"(w[o][4 * c + 1]), "r"(w[o][4 * c + 2]), "r"(w[o][4 * c + 3]) : "memory");
+    }
+    float m2 = 0.f, invz = 0.f;
+    if (row_ok) {
+      const float2 st = *(reinterpret_cast<const float2*>(p.stats) + ((size_t)((tile * TP + my_slot) * H + h) * L + my_tok));
+      m2 = st.x * 1.4426950408889634f;
+      invz = 1.f / st.y;
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t id1 = att_idesc(128, 128, 0);
+      const uint32_t q = smem_u32(sQ), k = smem_u32(sK), v = smem_u32(sV), g = smem_u32(sG);
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+        umma_bf16_ss(tS, att_desc_k_sw128(q + ks * 32), att_desc_k_sw128(k + ks * 32), id1, ks > 0);
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+        umma_bf16_ss(tDP, att_desc_k_sw128(g + ks * 32), att_desc_k_sw128(v + ks * 32), id1, ks > 0);
+      umma_commit(bar_mma);
+    }
+    mbar_wait(bar_mma, ph_mma, 7);
+    ph_mma ^= 1;
+    tc_fence_after();
+    // ---- P, dP -> dS for my row (my user's 64 key columns); dS row-wise, dS^T and P^T column-wise ----
+    {
+      float pr[64];
+      float dd = 0.f;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tS + lane_base + (uint32_t)(col0 + c * 32), r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float t = fmaf(__uint_as_float(r[j]), scale_log2, sKeyBias[col0 + c * 32 + j]);
+          pr[c * 32 + j] = row_ok ? exp2f(t - m2) * sKeyMul[col0 + c * 32 + j] * invz : 0.f;
+        }
+      }
+      float dp[64];
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        tmem_ld_32x32(tDP + lane_base + (uint32_t)(col0 + c * 32), r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          dp[c * 32 + j] = __uint_as_float(r[j]);
+          dd = fmaf(pr[c * 32 + j], dp[c * 32 + j], dd);
+        }
+      }
+      const uint32_t ds_row = smem_u32(sDS) + (uint32_t)my_slot * 16384u + row_off;
+      const uint32_t dst_base = smem_u32(sDST) + t_blk + t_in, pt_base = smem_u32(sPT) + t_blk + t_in;
+#pragma unroll
+      for (int c8 = 0; c8 < 8; ++c8) {               // 8 key columns = one 16-byte chunk of my dS row
+        uint32_t packed[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int j = c8 * 8 + 2 * u;
+          const float d0 = pr[j] * (dp[j] - dd), d1 = pr[j + 1] * (dp[j + 1] - dd);
+          const __nv_bfloat162 b2 = __floats2bfloat162_rn(d0, d1);
+          packed[u] = *reinterpret_cast<const uint32_t*>(&b2);
+          const __nv_bfloat162 p2 = __floats2bfloat162_rn(pr[j], pr[j + 1]);
+          // transposed copies: element (key col0 + j, query tid)
+          const uint32_t kr0 = (uint32_t)(col0 + j), kr1 = kr0 + 1u;
+          const uint32_t o0 = kr0 * 128u + ((t_chunk ^ (kr0 & 7u)) << 4), o1 = kr1 * 128u + ((t_chunk ^ (kr1 & 7u)) << 4);
+          asm volatile("st.shared.b16 [%0], %1;" ::"r"(dst_base + o0), "h"(__bfloat16_as_ushort(b2.x)) : "memory");
+          asm volatile("st.shared.b16 [%0], %1;" ::"r"(dst_base + o1), "h"(__bfloat16_as_ushort(b2.y)) : "memory");
+          asm volatile("st.shared.b16 [%0], %1;" ::"r"(pt_base + o0), "h"(__bfloat16_as_ushort(p2.x)) : "memory");
+          asm volatile("st.shared.b16 [%0], %1;" ::"r"(pt_base + o1), "h"(__bfloat16_as_ushort(p2.y)) : "memory");
+        }
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(ds_row + (((uint32_t)c8 ^ swz) << 4)), "r"(packed[0]),
+                     "r"(packed[1]), "r"(packed[2]), "r"(packed[3]) : "memory");
+      }
+    }
+    fence_proxy_async();
+    tc_fence_before();
+    __syncthreads();
+    if (tid == 0) {
+      tc_fence_after();
+      constexpr uint32_t id2 = att_idesc(128, 64, 1);
+      const uint32_t ds = smem_u32(sDS), dst = smem_u32(sDST), pt = smem_u32(sPT);
+      const uint32_t q = smem_u32(sQ), k = smem_u32(sK), g = smem_u32(sG);
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) {
+        const uint32_t a_off = (uint32_t)(ks >> 2) * 16384u + (uint32_t)(ks & 3) * 32u;
+        umma_bf16_ss(tDQ, att_desc_k_sw128(ds + a_off), att_desc_mn_sw128(k + ks * 2048), id2, ks > 0);
+        umma_bf16_ss(tDK, att_desc_k_sw128(dst + a_off), att_desc_mn_sw128(q + ks * 2048), id2, ks > 0);
+        umma_bf16_ss(tDV, att_desc_k_sw128(pt + a_off), att_desc_mn_sw128(g + ks * 2048), id2, ks > 0);
+      }
+      umma_commit(bar_mma);
+    }
+    mbar_wait(bar_mma, ph_mma, 8);
+    ph_mma ^= 1;
+    tc_fence_after();
+    {
+      uint2* op = reinterpret_cast<uint2*>(p.dqkv + grow * ld + h * dk);
+#pragma unroll
+      for (int o = 0; o < 3; ++o) {
+        uint32_t r[32];
+        tmem_ld_32x32((o == 0 ? tDQ : (o == 1 ? tDK : tDV)) + lane_base, r);
+        tmem_ld_wait();
+        const float f = o < 2 ? p.scale : 1.f;
+        if (row_ok) {
+          uint2* oo = op + (size_t)o * (hd >> 2);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            if (q < nquads) {
+              const __nv_bfloat162 a = __floats2bfloat162_rn(__uint_as_float(r[4 * q]) * f, __uint_as_float(r[4 * q + 1]) * f);
+              const __nv_bfloat162 b = __floats2bfloat162_rn(__uint_as_float(r[4 * q + 2]) * f, __uint_as_float(r[4 * q + 3]) * f);
+              oo[q] = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+  }
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
 }  // namespace fr
 
 using namespace fr;
@@ -555,5 +812,29 @@ FR_API int fr_ue_attention_tc(const void* qkv, const int* his_ids, void* ctx, fl
   const long long jobs = (long long)((B + 1) / 2) * H;
   const int grid = jobs < 2LL * num_sms() ? (int)jobs : 2 * num_sms();
   FR_CHECK(launch_pdl(ue_attention_tc_kernel, dim3(grid), dim3(128), smem, (cudaStream_t)stream, p));
+  return 0;
+}
+
+// Backward of the user-encoder attention on the tensor cores (same contract as fr_ue_mha_bwd in user_encoder.cu, which
+// stays as the cross-check). Autograd of attention.py:32-45,69-81.
+FR_API int fr_ue_attention_bwd_tc(const void* qkv, const void* dctx, const float* stats, const int* his_ids, void* dqkv,
+                                  int B, int L, int H, int dk, int use_mask, void* stream) {
+  FR_REQUIRE(L >= 1 && L <= 64, "fr_ue_attention_bwd_tc: L=%d must be in [1,64]", L);
+  FR_REQUIRE(dk >= 4 && dk <= 32 && dk % 4 == 0, "fr_ue_attention_bwd_tc: dk=%d must be a multiple of 4 in [4,32]", dk);
+  FR_REQUIRE(!use_mask || his_ids != nullptr, "fr_ue_attention_bwd_tc: use_mask needs his_ids");
+  if (B == 0) return 0;
+  UeAttBwdParams p;
+  p.qkv = (const __nv_bfloat16*)qkv; p.dctx = (const __nv_bfloat16*)dctx; p.stats = stats; p.his_ids = his_ids;
+  p.dqkv = (__nv_bfloat16*)dqkv; p.B = B; p.L = L; p.H = H; p.dk = dk; p.use_mask = use_mask;
+  p.scale = 1.f / sqrtf((float)dk);
+  constexpr int smem = kUeBwdBar + 64 + 1024 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    FR_CHECK(cudaFuncSetAttribute(ue_attention_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  const long long jobs = (long long)((B + 1) / 2) * H;
+  const int grid = jobs < (long long)num_sms() ? (int)jobs : num_sms();
+  FR_CHECK(launch_pdl(ue_attention_bwd_tc_kernel, dim3(grid), dim3(128), smem, (cudaStream_t)stream, p));
   return 0;
 }

@@ -42,6 +42,7 @@ SIGNATURES = {
     "fr_ue_scatter_dx": (I, [P, P, P, I, I, F, c_ulonglong, F, c_ulonglong, P, P]),
     "fr_ue_mha_fwd": (I, [P, P, P, P, I, I, I, I, I, P]),
     "fr_ue_attention_tc": (I, [P, P, P, P, I, I, I, I, I, P]),
+    "fr_ue_attention_bwd_tc": (I, [P, P, P, P, P, I, I, I, I, I, P]),
     "fr_ue_mha_bwd": (I, [P, P, P, P, P, I, I, I, I, I, P]),
     "fr_ue_pool_score": (I, [P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, I, I, I, I, I, I, I, F, c_ulonglong, P, P]),
     "fr_colsum": (I, [P, I, P, I, I, I, P, I, P]),

@@ -308,10 +308,13 @@ def ue_mha_fwd(qkv, his_ids, ctx, stats, B, L, H, dk, use_mask=False, impl: Opti
     return ctx
 
 
-def ue_mha_bwd(qkv, dctx, stats, his_ids, dqkv, B, L, H, dk, use_mask=False):
+def ue_mha_bwd(qkv, dctx, stats, his_ids, dqkv, B, L, H, dk, use_mask=False, impl: Optional[str] = None):
+    """User-encoder self-attention backward; ``impl`` as in ``ue_mha_fwd`` ("tc" default, "cuda" cross-check)."""
     lib = require_native()
-    check(lib.fr_ue_mha_bwd(qkv.data_ptr(), dctx.data_ptr(), stats.data_ptr(), _p(his_ids), dqkv.data_ptr(), B, L, H, dk,
-                            int(use_mask), stream_ptr(qkv.device)), "fr_ue_mha_bwd")
+    impl = impl or os.environ.get("FEDREC_UE_ATTN", "tc")
+    fn, name = (lib.fr_ue_attention_bwd_tc, "fr_ue_attention_bwd_tc") if impl == "tc" else (lib.fr_ue_mha_bwd, "fr_ue_mha_bwd")
+    check(fn(qkv.data_ptr(), dctx.data_ptr(), stats.data_ptr(), _p(his_ids), dqkv.data_ptr(), B, L, H, dk,
+             int(use_mask), stream_ptr(qkv.device)), name)
     count_launches(1)
     return dqkv
 

@@ -147,6 +147,12 @@ int fr_ue_attention_tc(const void* qkv, const int* his_ids, void* ctx, float* st
                        int use_mask, void* stream);
 int fr_ue_mha_bwd(const void* qkv, const void* dctx, const float* stats, const int* his_ids, void* dqkv, int B, int L,
                   int H, int dk, int use_mask, void* stream);
+/* The same backward on the tensor cores (csrc/bert_attention_sm100.cu): S = QK^T and dP = dO V^T, then dQ = dS K,
+ * dK = dS^T Q, dV = P^T dO as tcgen05.mma with TMEM accumulators; dS^T and P^T are written transposed into shared
+ * memory so every product uses the operand forms of the forward kernel. Same arguments and results as fr_ue_mha_bwd;
+ * the default path of the training step. Autograd of attention.py:32-45,69-81. */
+int fr_ue_attention_bwd_tc(const void* qkv, const void* dctx, const float* stats, const int* his_ids, void* dqkv, int B,
+                           int L, int H, int dk, int use_mask, void* stream);
 
 /* Additive pooling over the history + candidate scoring + sigmoid + soft-max CE (label 0), and with train != 0 the
  * whole backward down to the GEMM operands: d_ctx_pool, d_pre (bf16), d_w2/d_b2 (+=), candidate gradients
