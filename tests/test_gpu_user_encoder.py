@@ -231,6 +231,9 @@ def test_tensor_core_user_attention_matches_the_reference_and_the_cuda_core_kern
         # bf16 probabilities / dS on the tensor cores: compare in the norm per q|k|v block plus a loose element bound
         for o, nm in enumerate("qkv"):
             a, b = dqkv.float()[:, o * H * dk:(o + 1) * H * dk], qf.grad[:, o * H * dk:(o + 1) * H * dk]
-            rel = float((a - b).norm() / b.norm().clamp_min(1e-12))
-            assert rel < (2e-2 if impl == "tc" else 1e-2), (impl, nm, rel)
+            if float(b.norm()) < 1e-6:          # a history of one click: the soft-max is constant, dQ = dK = 0
+                assert float(a.abs().max()) < 1e-4
+                continue
+            rel = float((a - b).norm() / b.norm())
+            assert rel < (2e-2 if impl == "tc" else 1e-2), (impl, nm, rel, (B, L, H, dk, use_mask))
         torch.testing.assert_close(dqkv.float(), qf.grad, atol=6e-3 if impl == "tc" else 3e-3, rtol=5e-2)
