@@ -9,7 +9,7 @@ declare -A FILTER=(
   [gemm_ffn1]=gemm_bf16_tn_kernel [gemm_ffn2]=gemm_bf16_tn_kernel [gemm_qkv]=gemm_bf16_tn_kernel [gemm_out]=gemm_bf16_tn_kernel
   [gemm_fold_ffn1]=gemm_bf16_tn_kernel [gemm_fold_ffn2]=gemm_bf16_tn_kernel [gemm_fold_qkv]=gemm_bf16_tn_kernel
   [gemm_fold_out]=gemm_bf16_tn_kernel [attention]=bert_attention_tc [gemm_grad]=gemm_grad_kernel [layernorm]=layernorm_kernel
-  [aggregate]=agg_)
+  [aggregate]=agg_ [ue_attention]=ue_attention_tc_kernel [ue_attention_bwd]=ue_attention_bwd_tc_kernel)
 declare -A COUNT=([aggregate]=7)
 declare -A SKIP=([aggregate]=14)
 for t in "$@"; do

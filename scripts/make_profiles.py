@@ -29,6 +29,10 @@ WORK = {
     "attention": (4.0 * (M // 30) * 12 * 30 * 30 * 64, M * 2304 * 2 + M * 768 * 2, f"{M // 30} titles x 12 heads, T=30"),
     "gemm_grad": (2.0 * M * 384 * 768, M * (384 + 768) * 2 + 384 * 768 * 4, f"dW[384,768] += dY^T X, K={M}"),
     "layernorm": (0.0, M * 768 * 2 * 2, f"{M} rows x 768 bf16"),
+    "ue_attention": (2.0 * 50 * 20 * 50 * 50 * 20 * 2, 2500 * 1200 * 2 + 2500 * 400 * 2 + 50 * 20 * 50 * 8,
+                     "50 users x 20 heads, L=50, dk=20 (useful FLOPs; the padded 128x128x32 tiles execute 13x more)"),
+    "ue_attention_bwd": (2.0 * 50 * 20 * 50 * 50 * 20 * 5, 2 * 2500 * 1200 * 2 + 2500 * 400 * 2 + 50 * 20 * 50 * 8,
+                         "50 users x 20 heads, L=50, dk=20, five products per (user, head)"),
     "aggregate": (0.0, 8 * 1_164_896 * 4 * 3, "8 logical ranks on one GPU, 4.66 MB each, clip + noise + mean"),
 }
 

@@ -52,6 +52,16 @@ elif what == "attention":
     out = torch.zeros(n * T, 768, device=DEV, dtype=torch.bfloat16)
     for _ in range(6):
         D.bert_attention(qkv, None, None, None, n, T, H, out)
+elif what in ("ue_attention", "ue_attention_bwd"):
+    B, L, H, dk = 50, 50, 20, 20
+    qkv = (torch.randn(B * L, 3 * H * dk, device=DEV) * 0.8).bfloat16()
+    ctx = torch.zeros(B * L, H * dk, device=DEV, dtype=torch.bfloat16)
+    stats = torch.zeros(B * H * L, 2, device=DEV)
+    dctx = (torch.randn(B * L, H * dk, device=DEV) * 0.1).bfloat16()
+    dqkv = torch.zeros_like(qkv)
+    for _ in range(6):
+        D.ue_mha_fwd(qkv, None, ctx, stats, B, L, H, dk, False, impl="tc")
+        D.ue_mha_bwd(qkv, dctx, stats, None, dqkv, B, L, H, dk, False, impl="tc")
 elif what == "layernorm":
     x = torch.randn(M, 768, device=DEV).bfloat16()
     g, b = torch.randn(768, device=DEV), torch.randn(768, device=DEV)

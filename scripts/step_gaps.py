@@ -20,18 +20,22 @@ from fedrec_b200.models import UserModel  # noqa: E402
 
 DEV = "cuda:0"
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 4
-cfg = FedRecConfig(batch_size=50, title_len=30, num_news=bench.NUM_NEWS, cuda_graph=True, clip_norm=2.0, noise_multiplier=0.05)
-model = UserModel(None, bench.synthetic_news_index(np), DEV, config=cfg)
-step = TrainStep(model, cfg)
+# the shipped single-GPU loop (bench.py): FederatedRunner in gradient mode, optimiser pipelined into the step
+from fedrec_b200.engine.federated import FederatedRunner  # noqa: E402
+cfg = FedRecConfig(mode="grad_avg", batch_size=50, title_len=30, num_news=bench.NUM_NEWS, cuda_graph=True, clip_norm=2.0,
+                   noise_multiplier=0.05, synthetic=True, snapshot_path="", log_dir="", num_train=8, num_valid=1)
+runner = FederatedRunner(cfg, news_index=bench.synthetic_news_index(np), nid2index={"<unk>": 0}, train_sam=[], valid_sam=[])
+assert runner.pipelined
+step = runner.step
 cand_h, his_h = bench.make_batches(np, 8 + N, 0)
-cand = torch.from_numpy(cand_h).to(torch.int32).to(DEV)
-his = torch.from_numpy(his_h).to(torch.int32).to(DEV)
+ids = bench.pack_ids(torch, cand_h, his_h).to(DEV)
+B, C, L = 50, 5, 50
 for i in range(8):
-    step.run(cand[i], his[i]); model.adam_step()
+    step.run_packed(ids[i], B, C, L)
 torch.cuda.synchronize()
 with profile(activities=[ProfilerActivity.CUDA]) as prof:
     for i in range(8, 8 + N):
-        step.run(cand[i], his[i]); model.adam_step()
+        step.run_packed(ids[i], B, C, L)
     torch.cuda.synchronize()
 path = os.path.join(tempfile.mkdtemp(), "trace.json")
 prof.export_chrome_trace(path)
