@@ -469,3 +469,22 @@ FR_API int fr_hostio_publish(void* out_ring_mapped, const float* value, int slot
   FR_LAUNCH_CHECK();
   return 0;
 }
+
+// Device-side timestamps (debugging / profiling without a profiler): ring[(*ctr)++ % slots] = %globaltimer (ns).
+// engine/fused.py puts one at the start and one at the end of a captured step when FEDREC_STEP_TIMESTAMPS=1, so
+// scripts/step_gaps.py can report how long the device sits idle between two graph replays in the real loop.
+namespace fr {
+__global__ void timestamp_kernel(unsigned long long* ring, int slots, unsigned long long* ctr) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  const unsigned long long i = *ctr;
+  ring[i % (unsigned long long)slots] = t;
+  *ctr = i + 1ull;
+}
+}  // namespace fr
+FR_API int fr_timestamp(unsigned long long* ring, int slots, unsigned long long* ctr, void* stream) {
+  FR_REQUIRE(slots >= 1, "fr_timestamp: slots=%d", slots);
+  timestamp_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ring, slots, ctr);
+  FR_LAUNCH_CHECK();
+  return 0;
+}

@@ -26,7 +26,7 @@ os.environ.setdefault("FEDREC_QUIET", "1")      # no per-round echo; the summary
 def run(mode: str, **kw):
     rank = int(os.environ.get("RANK", "0"))
     cfg = FedRecConfig(mode=mode, batch_size=32, title_len=30, bert_layers=2, lr=1e-4, dropout=0.2, snapshot_path="",
-                       log_dir="", seed=7, **kw)
+                       log_dir="", seed=7, steps_per_epoch=1, **kw)      # count steps, not passes over the shard
     d = make_synthetic_mind(num_news=2000, num_train=512, num_valid=128, title_len=30, seed=22, topics=4,
                             generic_frac=0.0, liked_topics=1, client=rank)
     r = FederatedRunner(cfg, news_index=d.news_index, nid2index=d.nid2index, train_sam=d.train_sam, valid_sam=d.valid_sam)
@@ -54,7 +54,8 @@ def run(mode: str, **kw):
     same = all(torch.equal(ps[0], x) for x in ps)
     if rank == 0:
         fmt = lambda v: "loss %.3f auc %.3f mrr %.3f ndcg@5 %.3f ndcg@10 %.3f" % v if v else "n/a (server rank)"  # noqa: E731
-        heap = f"{r.symm.backend}{'+nvls' if r.symm.mc_ptr else ''}" if r.symm else "collective"
+        heap = r.symm.describe() if r.symm else "collective"
+        heap += ", optimiser pipelined into the step" if r.pipelined else ""
         print(f"== {mode} {kw} | {r.W} ranks | aggregation: {heap} | {ROUNDS} local steps per client in {dt:.1f} s")
         print(f"   before: {fmt(before)}\n   after:  {fmt(after)}\n   identical parameters on every rank: {same}", flush=True)
     if r.heartbeat:

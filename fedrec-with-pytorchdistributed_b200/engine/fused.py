@@ -144,6 +144,9 @@ class FusedStep:
         self._opt_forked = False
         self._side_forked = False
         self._io = None                 # host-mapped rings for run_host / loss_of (enable_host_io)
+        self._ts = None                 # FEDREC_STEP_TIMESTAMPS=1: %globaltimer at the start and end of every step
+        if os.environ.get("FEDREC_STEP_TIMESTAMPS") == "1":
+            self._ts = (torch.zeros(8192, dtype=torch.int64, device=self.dev), torch.zeros(1, dtype=torch.int64, device=self.dev))
 
     # ---- optimiser pipelined into the step -----------------------------------------------------------------
     def attach_optimizer(self, grad_agg, lr: float, b1: float, b2: float, eps: float) -> None:
@@ -636,6 +639,8 @@ class FusedStep:
         L = his.shape[1]
         self._step_no += 1
         seed = self.cfg.seed * 1000003 + 3 * self._step_no
+        if self._ts is not None and train:
+            D.timestamp(*self._ts)
         D.counter_advance(self._seed_dev, 0x9E3779B97F4A7C15 & (2 ** 63 - 1))
         if hostio:                                           # this step's ids: host ring slot -> static id buffer
             io = self._io
@@ -670,6 +675,8 @@ class FusedStep:
             if opt is not None:
                 opt[0].symm.mark_pending(arm=not warm)       # gradients complete: arm the chain of the next step
         self.last_scores = u["score"]
+        if self._ts is not None and train:
+            D.timestamp(*self._ts)
         if hostio:
             D.hostio_publish(self._io["out_dev"], u["loss"], self._io["slots"], self._io["ctr"])
         return u["loss"].clone()

@@ -22,6 +22,7 @@ SIGNATURES = {
     "fr_dedup_static": (I, [P, I, I, P, P, P, P]),
     "fr_sq_norm": (I, [P, LL, P, P]),
     "fr_clip_noise": (I, [P, LL, P, F, F, c_ulonglong, c_uint, P]),
+    "fr_timestamp": (I, [P, I, P, P]),
     "fr_host_mapped_alloc": (I, [LL, P, P]),
     "fr_host_mapped_free": (I, [P]),
     "fr_hostio_fetch": (I, [P, P, I, I, P, P]),

@@ -259,6 +259,11 @@ def cast_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tens
 
 
 # ---- user encoder / loss / gradient GEMMs (CUDA only) -------------------------------------------------------
+def timestamp(ring: torch.Tensor, ctr: torch.Tensor) -> None:
+    check(require_native().fr_timestamp(ring.data_ptr(), ring.numel(), ctr.data_ptr(), stream_ptr(ring.device)), "fr_timestamp")
+    count_launches(1)
+
+
 def hostio_fetch(dst: torch.Tensor, ring_dev: int, n: int, slots: int, ctr: torch.Tensor) -> None:
     """``dst[:n] = ring[*ctr % slots]; *ctr += 1`` with ``ring`` in host-mapped pinned memory (engine/fused.py run_host)."""
     check(require_native().fr_hostio_fetch(dst.data_ptr(), ring_dev, n, slots, ctr.data_ptr(), stream_ptr(dst.device)),

@@ -65,6 +65,9 @@ int fr_clip_noise(float* x, long long n, const float* sq, float clip, float nois
  * increments *step_ctr; fr_hostio_publish writes {value bits, *step_ctr} into entry ((*step_ctr - 1) % slots) of
  * out_ring_mapped (slots x 4 uints), sequence number last, for the host to poll. fr_host_mapped_alloc returns both
  * addresses of a zeroed pinned allocation. Replaces the per-batch host/device copies of main.py:59-64,72-79,90. */
+/* ring[(*ctr)++ % slots] = %globaltimer in ns (one thread): device-side timestamps around a captured step, for
+ * measuring idle time between graph replays without a profiler. No upstream counterpart. */
+int fr_timestamp(unsigned long long* ring, int slots, unsigned long long* ctr, void* stream);
 int fr_host_mapped_alloc(long long bytes, void** host_out_host, void** dev_out_host);
 int fr_host_mapped_free(void* host_ptr_host);
 int fr_hostio_fetch(int* dst, const int* ring_mapped, int n, int slots, unsigned long long* step_ctr, void* stream);

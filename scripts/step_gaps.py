@@ -1,64 +1,74 @@
-"""Where a CUDA-graph step spends time that is not kernel time: idle gaps on the device timeline.
+"""How long the device sits idle between two replays of the step graph, measured in the real loop.
 
-Profiles a few graph replays with the PyTorch profiler (CUPTI), merges the kernel intervals of all streams and prints the
-idle time per step plus the largest gaps with the kernels around them.  Usage: python scripts/step_gaps.py [steps]
+A profiler cannot answer this: under CUPTI every graph launch costs the host several hundred microseconds, so the device
+waits for the host and the trace shows a gap that the unprofiled loop does not have. Instead the captured step carries
+one %globaltimer timestamp kernel as its first node and one as its last (FEDREC_STEP_TIMESTAMPS=1, engine/fused.py); the
+gap between the end of step i and the start of step i+1 is read from device memory after the loop.
+
+Three loops, the same ones bench.py times: ids already on the device (run_packed), ids pulled from host-mapped pinned
+memory by the step's first kernel with the loss pushed back by its last (run_host / loss_of), and the same with a
+synchronous read of every loss (lag 0). Usage: python scripts/step_gaps.py [steps]
 """
-import json
 import os
 import sys
-import tempfile
+from collections import deque
+
+os.environ["FEDREC_STEP_TIMESTAMPS"] = "1"
 
 import numpy as np
 import torch
-from torch.profiler import ProfilerActivity, profile
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench  # noqa: E402
 from fedrec_b200.config import FedRecConfig  # noqa: E402
-from fedrec_b200.engine import TrainStep  # noqa: E402
-from fedrec_b200.models import UserModel  # noqa: E402
+from fedrec_b200.engine.federated import FederatedRunner  # noqa: E402
 
 DEV = "cuda:0"
-N = int(sys.argv[1]) if len(sys.argv) > 1 else 4
-# the shipped single-GPU loop (bench.py): FederatedRunner in gradient mode, optimiser pipelined into the step
-from fedrec_b200.engine.federated import FederatedRunner  # noqa: E402
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 cfg = FedRecConfig(mode="grad_avg", batch_size=50, title_len=30, num_news=bench.NUM_NEWS, cuda_graph=True, clip_norm=2.0,
                    noise_multiplier=0.05, synthetic=True, snapshot_path="", log_dir="", num_train=8, num_valid=1)
 runner = FederatedRunner(cfg, news_index=bench.synthetic_news_index(np), nid2index={"<unk>": 0}, train_sam=[], valid_sam=[])
 assert runner.pipelined
-step = runner.step
+step, fused = runner.step, runner.step._fused
 cand_h, his_h = bench.make_batches(np, 8 + N, 0)
-ids = bench.pack_ids(torch, cand_h, his_h).to(DEV)
+ids_pin = bench.pack_ids(torch, cand_h, his_h).pin_memory()
+ids_d, ids_host = ids_pin.to(DEV), ids_pin.numpy()
 B, C, L = 50, 5, 50
-for i in range(8):
-    step.run_packed(ids[i], B, C, L)
-torch.cuda.synchronize()
-with profile(activities=[ProfilerActivity.CUDA]) as prof:
-    for i in range(8, 8 + N):
-        step.run_packed(ids[i], B, C, L)
+ring, ctr = fused._ts
+
+
+def report(name):
     torch.cuda.synchronize()
-path = os.path.join(tempfile.mkdtemp(), "trace.json")
-prof.export_chrome_trace(path)
-ev = [e for e in json.load(open(path))["traceEvents"] if e.get("cat") in ("kernel", "gpu_memcpy", "gpu_memset") and "dur" in e]
-ev.sort(key=lambda e: e["ts"])
-t0, t1 = ev[0]["ts"], max(e["ts"] + e["dur"] for e in ev)
-busy_end, idle, gaps = ev[0]["ts"], 0.0, []
-last = ev[0]
-for e in ev:
-    if e["ts"] > busy_end:
-        g = e["ts"] - busy_end
-        idle += g
-        gaps.append((g, last["name"][:70], e["name"][:70]))
-    if e["ts"] + e["dur"] > busy_end:
-        busy_end, last = e["ts"] + e["dur"], e
-ksum = sum(e["dur"] for e in ev)
-print(f"{N} steps: wall {(t1 - t0) / N:.1f} us/step, kernel-time sum {ksum / N:.1f} us/step, "
-      f"device idle {idle / N:.1f} us/step in {len(gaps) / N:.0f} gaps/step")
-hist = {}
-for g, a, b in gaps:
-    key = (a.split("(")[0].split("<")[0], b.split("(")[0].split("<")[0])
-    n, tot = hist.get(key, (0, 0.0))
-    hist[key] = (n + 1, tot + g)
-print("idle time by (kernel before -> kernel after), per step:")
-for (a, b), (n, tot) in sorted(hist.items(), key=lambda kv: -kv[1][1])[:25]:
-    print(f"  {tot / N:7.1f} us  x{n / N:<5.1f} avg {tot / n:5.2f} us   {a}  ->  {b}")
+    n = int(ctr.item())
+    assert n % 2 == 0 and n // 2 <= ring.numel() // 2
+    t = ring[:n].cpu().numpy().astype(np.int64).reshape(-1, 2)[-N:]
+    dur = (t[:, 1] - t[:, 0]) / 1e3
+    gap = (t[1:, 0] - t[:-1, 1]) / 1e3
+    print(f"{name:<46} step (first to last node) median {np.median(dur):7.1f} us | idle between replays: median "
+          f"{np.median(gap):6.1f} us, mean {gap.mean():6.1f} us, p95 {np.percentile(gap, 95):6.1f} us, max {gap.max():7.1f} us")
+    ctr.zero_()
+
+
+for i in range(8):
+    step.run_packed(ids_d[i], B, C, L)
+torch.cuda.synchronize()
+ctr.zero_()
+for i in range(8, 8 + N):
+    step.run_packed(ids_d[i], B, C, L)
+report("ids on the device (run_packed)")
+
+step.enable_host_io(B, C, L, slots=4)
+for i in range(3):
+    step.loss_of(step.run_host(ids_host[i]))
+for lag in (1, 0):
+    torch.cuda.synchronize()
+    ctr.zero_()
+    tickets = deque()
+    for i in range(8, 8 + N):
+        tickets.append(step.run_host(ids_host[i]))
+        if len(tickets) > lag:
+            step.loss_of(tickets.popleft())
+    while tickets:
+        step.loss_of(tickets.popleft())
+    report(f"host ids in, loss out every step (lag {lag})")
+runner.flush()
