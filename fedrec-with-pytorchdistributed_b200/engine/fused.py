@@ -486,12 +486,13 @@ class FusedStep:
         assert self._io is None, "host I/O rings are sized once"
         hp, dp = ctypes.c_void_p(), ctypes.c_void_p()
         ho, do = ctypes.c_void_p(), ctypes.c_void_p()
+        n_pad = (n_ids + 3) // 4 * 4                     # slots are read with 16-byte loads
         with torch.cuda.device(self.dev):
-            D.check(lib.fr_host_mapped_alloc(slots * n_ids * 4, ctypes.byref(hp), ctypes.byref(dp)), "fr_host_mapped_alloc")
+            D.check(lib.fr_host_mapped_alloc(slots * n_pad * 4, ctypes.byref(hp), ctypes.byref(dp)), "fr_host_mapped_alloc")
             D.check(lib.fr_host_mapped_alloc(slots * 16, ctypes.byref(ho), ctypes.byref(do)), "fr_host_mapped_alloc")
-        ring = np.ctypeslib.as_array((ctypes.c_int32 * (slots * n_ids)).from_address(hp.value)).reshape(slots, n_ids)
+        ring = np.ctypeslib.as_array((ctypes.c_int32 * (slots * n_pad)).from_address(hp.value)).reshape(slots, n_pad)
         out = np.ctypeslib.as_array((ctypes.c_uint32 * (slots * 4)).from_address(ho.value)).reshape(slots, 4)
-        self._io = {"n": n_ids, "slots": slots, "ring": ring, "ring_dev": dp.value, "out": out, "out_dev": do.value,
+        self._io = {"n": n_ids, "n_pad": n_pad, "slots": slots, "ring": ring, "ring_dev": dp.value, "out": out, "out_dev": do.value,
                     "ctr": torch.zeros(1, dtype=torch.int64, device=self.dev), "issued": 0, "confirmed": 0}
 
     def run_host(self, ids, B: int, C: int, L: int) -> int:
@@ -504,7 +505,7 @@ class FusedStep:
         if io["issued"] - io["confirmed"] >= io["slots"] - 1:
             self.loss_of(io["confirmed"] + 1)
         src = ids.numpy() if isinstance(ids, torch.Tensor) else np.asarray(ids)
-        np.copyto(io["ring"][io["issued"] % io["slots"]], src.reshape(-1), casting="no")
+        np.copyto(io["ring"][io["issued"] % io["slots"], : io["n"]], src.reshape(-1), casting="no")
         io["issued"] += 1
         if self.cfg.cuda_graph:
             self._replay(self._graph_for(B, C, L, hostio=True))
@@ -589,7 +590,7 @@ class FusedStep:
             self._count_update()
         if hostio is not None:
             B, C, L = hostio
-            ids = self._io.setdefault("ids_eager", torch.zeros(B * (L + C), dtype=torch.int32, device=self.dev))
+            ids = self._io.setdefault("ids_eager", torch.zeros(self._io["n_pad"], dtype=torch.int32, device=self.dev))[: B * (L + C)]
             loss = self._run_eager(ids[B * L:].view(B, C), ids[: B * L].view(B, L), train, ids=ids, hostio=True)
         else:
             loss = self._run_eager(cand, his, train)
@@ -606,7 +607,7 @@ class FusedStep:
 
     def _capture(self, B: int, C: int, L: int, key, hostio: bool = False):
         self.flush()                                        # no pending update may leak into the warm-up runs
-        ids = torch.ones(B * (L + C), dtype=torch.int32, device=self.dev)
+        ids = torch.ones((B * (L + C) + 3) // 4 * 4, dtype=torch.int32, device=self.dev)[: B * (L + C)]   # padded storage
         static_h, static_c = ids[: B * L].view(B, L), ids[B * L:].view(B, C)
         side = torch.cuda.Stream(device=self.dev)
         side.wait_stream(torch.cuda.current_stream(self.dev))
@@ -644,7 +645,7 @@ class FusedStep:
         D.counter_advance(self._seed_dev, 0x9E3779B97F4A7C15 & (2 ** 63 - 1))
         if hostio:                                           # this step's ids: host ring slot -> static id buffer
             io = self._io
-            D.hostio_fetch(ids, io["ring_dev"], io["n"], io["slots"], io["ctr"])
+            D.hostio_fetch(ids, io["ring_dev"], io["n_pad"], io["slots"], io["ctr"])     # ids' storage is padded to n_pad
         opt = self._opt if train else None
         cur = torch.cuda.current_stream(self.dev)
         if opt is not None:

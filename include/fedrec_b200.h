@@ -61,7 +61,7 @@ int fr_clip_noise(float* x, long long n, const float* sq, float clip, float nois
                   unsigned stream_id, void* stream);
 
 /* Host I/O of a step through host-mapped pinned rings, usable from inside a CUDA graph: fr_hostio_fetch copies slot
- * (*step_ctr % slots) of ring_mapped (slots x n ints, device-visible address of pinned host memory) into dst and
+ * (*step_ctr % slots) of ring_mapped (slots x n ints, n % 4 == 0, device-visible address of pinned host memory) into dst and
  * increments *step_ctr; fr_hostio_publish writes {value bits, *step_ctr} into entry ((*step_ctr - 1) % slots) of
  * out_ring_mapped (slots x 4 uints), sequence number last, for the host to poll. fr_host_mapped_alloc returns both
  * addresses of a zeroed pinned allocation. Replaces the per-batch host/device copies of main.py:59-64,72-79,90. */
