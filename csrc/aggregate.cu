@@ -410,7 +410,13 @@ int launch_chain(const AggParams& p, const ChainOpts& o, cudaStream_t s) {
   int sms = num_sms(), dev = 0;
   FR_CHECK(cudaGetDevice(&dev));
   FR_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  int blocks = o.blocks > 0 ? o.blocks : 64;
+  // default grid: 64 blocks for the 4.66 MB gradient (it shares the GPU with the trunk), more for buffers whose in-place pass
+  // and Adam would otherwise be bandwidth-starved (one block per 256 KB, at most two per SM)
+  int blocks = o.blocks;
+  if (blocks <= 0) {
+    const long long by_size = p.n / (64 * 1024);
+    blocks = by_size < 64 ? 64 : (by_size > 2LL * sms ? 2 * sms : (int)by_size);
+  }
   if (blocks > 2 * sms) blocks = 2 * sms;
   const bool nvls = p.mc_buf != nullptr && p.W > 1;
   const dim3 grid(blocks, p.ranks_here), block(512), one(1, p.ranks_here);
@@ -510,7 +516,7 @@ FR_API int fr_param_average(void* const* bufs_host, void* const* pads_host, void
     if (weights_host[i] != weights_host[0]) p.uniform_weights = 0;
   }
   p.timeout_ns = ms_to_ns(timeout_ms); p.err = (int*)err_mapped;
-  ChainOpts o; o.mode = 1; o.blocks = blocks > 0 ? blocks : 128;
+  ChainOpts o; o.mode = 1; o.blocks = blocks > 0 ? blocks : (n >= (32LL << 20) ? 0 : 128);
   return launch_chain(p, o, (cudaStream_t)stream);
 }
 
