@@ -204,3 +204,52 @@ def test_client_failure_is_detected_and_training_resumes_from_snapshot(tmp_path)
     [p.join(60) for p in procs]
     assert out[0]["ok"] and out[1]["ok"] and out[0]["start"] == 2 and out[1]["start"] == 2
     assert torch.load(os.path.join(str(tmp_path), "snap.pt"), weights_only=False)["EPOCHS_RUN"] == 4
+
+
+def _store_worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    import time
+    from fedrec_b200.parallel import init_distributed, shutdown_distributed
+    from fedrec_b200.parallel.comm import agree_all, agree_max, host_barrier
+    info = init_distributed("gloo", 30.0, "cpu")
+    res = {}
+    try:
+        t0 = time.monotonic()
+        if rank == 1:
+            time.sleep(0.5)                              # a late rank costs the others host time, nothing else
+        host_barrier("t", 10.0)
+        res["waited"] = time.monotonic() - t0
+        res["all_true"] = agree_all(True, "a", 10.0)
+        res["one_false"] = agree_all(rank != 1, "b", 10.0)
+        res["max"] = agree_max(10 + 3 * rank, "m", 10.0)
+        host_barrier("t", 10.0)                          # tags are reusable: every call is its own generation
+        if rank == 0:
+            try:
+                host_barrier("only-rank-0", 0.3)
+                res["timeout"] = "no error"
+            except TimeoutError as e:
+                res["timeout"] = str(e)
+    except Exception as e:  # noqa: BLE001
+        res["error"] = repr(e)
+    q.put((rank, res))
+    shutdown_distributed(info)
+
+
+def test_store_barrier_agreement_and_timeout_naming_the_missing_rank():
+    """The host-side alignment the aggregation kernels rely on (no GPU work, no collective kernel): barrier, AND, MAX over
+    the job's key-value store, and a time-out that names who did not arrive (upstream's only tool is a two-day collective
+    timeout, client.py:227)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_store_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    out = dict(q.get(timeout=120) for _ in range(2))
+    [p.join(30) for p in procs]
+    for r in range(2):
+        assert "error" not in out[r], out[r]
+        assert out[r]["all_true"] is True and out[r]["one_false"] is False and out[r]["max"] == 13
+    assert out[0]["waited"] >= 0.45
+    assert "rank(s) [1]" in out[0]["timeout"], out[0]["timeout"]
