@@ -123,6 +123,25 @@ __device__ __forceinline__ uint32_t box_off(int r, int j) {
 // inside a slice the producer's M2 = sum v^2 - (sum v)^2 / 64 loses about mean^2 / var * 1e-7 of relative accuracy, far
 // below bf16 for any stream LayerNorm is usable on (mean 50, std 1: 3e-4).
 __device__ __forceinline__ void merge_row_stats(const float2* sp, int ns, float& mean, float& var) {
+  if (ns == 12) {
+    // 768-wide rows (every LayerNorm of this trunk): all twelve loads are issued before the first is consumed. With a
+    // run-time trip count the compiler keeps one load in flight per iteration, a chain of twelve L2 round trips per row
+    // (the hottest stall of the short-K GEMMs in profiles/ncu_gemm_fold_out.md before this).
+    float2 t[12];
+#pragma unroll
+    for (int k = 0; k < 12; ++k) t[k] = __ldg(sp + k);
+    mean = t[0].x * (1.f / 64.f);
+    float m2 = t[0].y;
+#pragma unroll
+    for (int k = 1; k < 12; ++k) {
+      const float d = fmaf(t[k].x, 1.f / 64.f, -mean);
+      const float w = 1.f / (float)(k + 1);
+      mean = fmaf(d, w, mean);
+      m2 += fmaf(d * d, 64.f * (float)k * w, t[k].y);
+    }
+    var = fmaxf(m2 * (1.f / 768.f), 0.f);
+    return;
+  }
   float2 t = __ldg(sp);
   mean = t.x * (1.f / 64.f);
   float m2 = t.y;
