@@ -317,6 +317,7 @@ class FederatedRunner:
 
     def run_client_server(self) -> float:
         """Both roles; ``global_epochs`` rounds of ``total_epochs`` local steps (client.py:258-292, server.py:72-105)."""
+        from ..parallel.symm import AggregationError
         cfg = self.cfg
         flag = torch.zeros(1, device=self.device)
         weights = self.fedavg_weights()
@@ -338,24 +339,30 @@ class FederatedRunner:
                 flag.zero_()
             if int(flag.item()) == 0:
                 break
-            self.faults.maybe_fire(self.rank, rnd)
-            self.param_agg.broadcast_(self.model.flat.param, src)  # X8 model sync
-            if not self.is_server:
-                for _ in range(max(cfg.total_epochs, 1) * self.steps_per_epoch()):   # client.py:284: local epochs per round
-                    loss = self.local_step()
-                    self._local_adam()
-                self.flush()
-                v = self.validate()
-                rec = {"round": rnd, "training_loss": float(loss)}
-                if v:
-                    rec.update({"validation_loss": v[0], "valid_auc": v[1], "valid_mrr": v[2],
-                                "val_ndcg@5": v[3], "val_ndcg@10": v[4]})
-                self.logger.log(rec, step=rnd)
-            with self.tracer.span("aggregate"):
-                if cfg.transport == "tcp" and self.W > 1:
-                    self._tcp_upload_and_average(src, weights)            # X9 + K23 the upstream way (other hosts)
-                else:
-                    self.param_agg.average_(self.model.flat.param, weights)   # X9 + K23 in one kernel
+            try:
+                self.faults.maybe_fire(self.rank, rnd)
+                self.param_agg.broadcast_(self.model.flat.param, src)  # X8 model sync
+                if not self.is_server:
+                    for _ in range(max(cfg.total_epochs, 1) * self.steps_per_epoch()):   # client.py:284: local epochs per round
+                        loss = self.local_step()
+                        self._local_adam()
+                    self.flush()
+                    v = self.validate()
+                    rec = {"round": rnd, "training_loss": float(loss)}
+                    if v:
+                        rec.update({"validation_loss": v[0], "valid_auc": v[1], "valid_mrr": v[2],
+                                    "val_ndcg@5": v[3], "val_ndcg@10": v[4]})
+                    self.logger.log(rec, step=rnd)
+                with self.tracer.span("aggregate"):
+                    if cfg.transport == "tcp" and self.W > 1:
+                        self._tcp_upload_and_average(src, weights)            # X9 + K23 the upstream way (other hosts)
+                    else:
+                        self.param_agg.average_(self.model.flat.param, weights)   # X9 + K23 in one kernel chain
+                        if self.symm is not None and not self.degraded:
+                            self.symm.check(sync=True)            # rounds are long: find out now, not a round later
+            except AggregationError as e:
+                rnd = self._degrade(e, rnd)                       # every rank lands here; the round is repeated over NCCL
+                continue
             rnd += 1
             self.round = rnd
             if self.heartbeat:
