@@ -193,28 +193,47 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    from collections import deque
+    from fedrec_b200.parallel.symm import AggregationError
+
+    def settle():
+        """Everything queued has run; an aggregation that gave up on a peer raises here, on every rank, before any rank
+        enters a collective the others would never reach."""
+        runner.step.flush()
+        torch.cuda.synchronize()
+        if runner.symm is not None:
+            runner.symm.check()
+
+    def guarded(fn):
+        try:
+            return fn()
+        except AggregationError as e:          # a peer was late beyond --agg_timeout_s: finish the measurement over NCCL
+            runner._degrade(e, 0)
+            return fn()
+
     # ---- device-timed: ids already on the device ----
-    for i in range(args.warmup):
-        one_step(ids_d[i])
-    runner.flush()
-    barrier()
+    def timed_device():
+        for i in range(args.warmup):
+            one_step(ids_d[i])
+        settle()
+        barrier()
+        l0 = D.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.warmup, total):
+            one_step(ids_d[i])
+        runner.step.flush()                             # the last step's update belongs to the timed region
+        e1.record()
+        settle()
+        barrier()
+        return e0.elapsed_time(e1) / args.steps, D.launch_count() - l0
+
     sampler = ClockSampler(local_rank).start() if rank == 0 else None
-    l0 = D.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.warmup, total):
-        loss = one_step(ids_d[i])
-    runner.step.flush()                                 # the last step's update belongs to the timed region
-    e1.record()
-    barrier()
-    runner.flush()
-    launches = D.launch_count() - l0
-    ms = e0.elapsed_time(e1) / args.steps
+    ms, launches = guarded(timed_device)
     # ---- end to end through the public API (TrainStep.run_host / loss_of): every step the ids travel from pinned host
     #      memory to the device (pulled over PCIe by the step's first kernel) and the step's loss travels back into host
     #      memory (pushed by its last kernel) where the host reads it. The host reads the loss of step i while step
     #      i + e2e_lag is already queued, so it never drains the launch queue ----
-    from collections import deque
     ids_host = ids_pin.numpy()
     step = runner.step
     step.enable_host_io(B, C, L, slots=max(4, args.e2e_lag + 2))
@@ -235,27 +254,30 @@ def run_ours(args):
                     runner._average_frozen(weights)
         return t
 
-    for i in range(min(args.warmup, 3)):                # captures the host-I/O variant of the graph
-        step.loss_of(one_step_host(i))
-    runner.flush()
-    barrier()
-    tickets = deque()
-    t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
-    t0.record()
-    host_loss, n_read = 0.0, 0
-    for i in range(args.warmup, total):
-        tickets.append(one_step_host(i))
-        if len(tickets) > args.e2e_lag:
+    def timed_e2e():
+        for i in range(min(args.warmup, 3)):            # captures the host-I/O variant of the graph
+            step.loss_of(one_step_host(i))
+        settle()
+        barrier()
+        tickets = deque()
+        t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
+        t0.record()
+        host_loss, n_read = 0.0, 0
+        for i in range(args.warmup, total):
+            tickets.append(one_step_host(i))
+            if len(tickets) > args.e2e_lag:
+                host_loss, n_read = step.loss_of(tickets.popleft()), n_read + 1
+        runner.step.flush()
+        while tickets:
             host_loss, n_read = step.loss_of(tickets.popleft()), n_read + 1
-    runner.step.flush()
-    while tickets:
-        host_loss, n_read = step.loss_of(tickets.popleft()), n_read + 1
-    t1.record()
-    barrier()
-    runner.flush()
-    assert n_read == args.steps
+        t1.record()
+        settle()
+        barrier()
+        assert n_read == args.steps
+        return t0.elapsed_time(t1) / args.steps, host_loss
+
+    e2e_ms, host_loss = guarded(timed_e2e)
     clocks = sampler.stop() if sampler else None
-    e2e_ms = t0.elapsed_time(t1) / args.steps
     h2d = ids_pin[0].numel() * 4
     symm = runner.symm
     finish(args, "ours", rank, world, ms, e2e_ms, h2d, 8, launches, clocks,
