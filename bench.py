@@ -172,7 +172,12 @@ def run_ours(args):
     weights = runner.fedavg_weights()
     state = {"n": 0}
 
+    fault = [int(x) for x in args.fault.split(":")] if args.fault else None      # rank:call:seconds, fires once
+
     def one_step(ids):
+        state["calls"] = state.get("calls", 0) + 1
+        if fault and rank == fault[0] and state["calls"] == fault[1]:
+            time.sleep(fault[2])                        # testing only: this rank goes silent (see --fault)
         loss = runner.step.run_packed(ids, B, C, L)
         if args.mode == "grad_avg":                     # BASELINE.json config 2/4: average gradients, then Adam
             if not runner.pipelined:                    # pipelined: the step itself applies the previous update
@@ -454,6 +459,8 @@ def main():
     ap.add_argument("--graph", choices=["on", "off"], default="on", help="replay the step from a CUDA graph")
     ap.add_argument("--e2e_lag", type=int, default=1, help="steps between queuing a loss read-back and consuming it")
     ap.add_argument("--agg_timeout_s", type=float, default=30.0)
+    ap.add_argument("--fault", default="", help="testing: RANK:CALL:SECONDS makes one rank sleep before its CALL-th step, to "
+                                                "exercise the time-out report and the fall-back to NCCL")
     ap.add_argument("--transport", default="nvlink", choices=["nvlink", "collective"])
     ap.add_argument("--mode", default="grad_avg", choices=["grad_avg", "param_avg"],
                     help="grad_avg = BASELINE.json configs 2/4 (default, the headline); param_avg = config 3")
