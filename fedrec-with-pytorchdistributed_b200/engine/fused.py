@@ -164,6 +164,13 @@ class FusedStep:
         self.flush()
         self._opt = None
 
+    def sync_step(self) -> None:
+        """The host-side Adam step count changed behind the pipeline's back (a snapshot was loaded): copy it into the
+        device-side counter the chain's bias corrections use."""
+        if self._opt is not None:
+            self.flush()
+            self._opt[0].symm.set_step(self.model.flat.step)
+
     def _opt_chain(self, count: bool) -> None:
         agg, lr, b1, b2, eps = self._opt
         if count:

@@ -69,6 +69,9 @@ def load_snapshot(path: str, model: torch.nn.Module, map_location="cpu", strict:
             flat.exp_avg_sq.copy_(opt["exp_avg_sq"])
     if hasattr(model, "on_weights_changed"):
         model.on_weights_changed()
+    fused = getattr(model, "_fused", None)
+    if fused is not None and hasattr(fused, "sync_step"):
+        fused.sync_step()                    # a pipelined optimiser keeps the Adam step count on the device
     out = {"EPOCHS_RUN": int(snap.get("EPOCHS_RUN", 0)) if isinstance(snap, dict) else 0}
     for k in ("ROUND", "RNG_STATE"):
         if isinstance(snap, dict) and k in snap:
