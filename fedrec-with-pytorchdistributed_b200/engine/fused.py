@@ -623,10 +623,11 @@ class FusedStep:
                 self._run_eager(static_c, static_h, True, warm=True, ids=ids if hostio else None, hostio=hostio)
         torch.cuda.current_stream(self.dev).wait_stream(side)
         torch.cuda.synchronize(self.dev)
-        if hostio:      # the warm-up passes consumed ring slots and published results: put the counter back
-            self._io["ctr"].fill_(self._io["issued"] - 1)
-            self._io["out"][:, 1] = 0
+        if hostio:      # the warm-up passes consumed ring slots and published results: put the counter back and forget
+            io = self._io   # what they published (results of earlier steps that the caller has not read yet stay)
+            io["ctr"].fill_(io["issued"] - 1)
             torch.cuda.synchronize(self.dev)
+            io["out"][io["out"][:, 1] >= (io["issued"] & 0xFFFFFFFF), 1] = 0
         graph = torch.cuda.CUDAGraph()
         n0 = D.launch_count()
         with torch.cuda.graph(graph):
