@@ -26,3 +26,25 @@ def test_kernel_switches(monkeypatch):
     assert not FedRecConfig.from_argv(["--ln_fold", "false"], []).ln_fold
     monkeypatch.setenv("FEDREC_LN_FOLD", "0")
     assert not FedRecConfig.from_env().ln_fold
+
+
+def test_an_epoch_is_a_pass_over_the_shard(tiny_bert):
+    """total_epochs counts passes over the client's shard like upstream's DataLoader loop (main.py:55-91,135-139):
+    ceil(impressions / batch_size) steps per epoch, every step an update; --steps_per_epoch overrides."""
+    import torch
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    cfg = FedRecConfig(mode="grad_avg", synthetic=True, num_news=120, num_train=10, num_valid=2, title_len=8, batch_size=4,
+                       total_epochs=2, dropout=0.0, device="cpu", backend="gloo", snapshot_path="", log_dir="")
+    r = FederatedRunner(cfg, bert_config=tiny_bert)
+    assert r.steps_per_epoch() == 3                       # ceil(10 / 4)
+    r.run_gradient_averaging()
+    assert r.model.flat.step == 2 * 3 and r.round == 6
+    cfg2 = FedRecConfig(mode="param_avg", synthetic=True, num_news=120, num_train=10, num_valid=2, title_len=8, batch_size=4,
+                        total_epochs=2, steps_per_epoch=1, local_steps=2, dropout=0.0, device="cpu", backend="gloo",
+                        snapshot_path="", log_dir="")
+    r2 = FederatedRunner(cfg2, bert_config=tiny_bert)
+    assert r2.steps_per_epoch() == 1
+    r2.run_parameter_averaging()
+    assert r2.model.flat.step == 2 * 1 * 2                # epochs x rounds per epoch x local steps
+    assert torch.isfinite(r2.model.flat.param).all()
