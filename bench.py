@@ -115,20 +115,22 @@ def finish(args, impl, rank, world, ms_per_step, e2e_ms, h2d, d2h, launches, clo
         return
     value = world * B_USERS / (ms_per_step * 1e-3)
     e2e_val = world * B_USERS / (e2e_ms * 1e-3)
+    # `config` names the workload only and is identical in every arm; what an arm does on top of it goes to `details`
     cfg = {"model": "FedRec joint DistilBERT-base text encoder + user encoder (MHA 20x20 + additive attention)",
-           "mode": ("Gradient_Averaging_main: per-round gradient averaging" +
-                    (", clip C=%g + LDP sigma=%g" % (CLIP, SIGMA) if impl != "reference" else " (upstream: no clip, no noise)")),
+           "mode": "Gradient_Averaging_main: per-round gradient averaging",
            "global_batch": world * B_USERS, "users_per_client_per_round": B_USERS, "seq_len": TITLE_LEN,
            "history_len": HIS_LEN, "negatives_per_positive": NPRATIO, "num_news": NUM_NEWS,
            "parallelism": f"dp{world} (one federated client per GPU)",
            "l2_policy": "working set per step (>1 GB activations + 130 MB bf16 weights) exceeds the 126 MB L2; "
                         "a fresh batch of ids every step"}
-    cfg.update(extra_cfg)
+    details = {"privacy": ("per-client L2 clip C=%g + LDP Gaussian noise sigma=%g inside the aggregation" % (CLIP, SIGMA)
+                           if impl != "reference" else "none (upstream as is: no clip, no noise)")}
+    details.update(extra_cfg)
     out = {"metric": "training impressions/sec/box", "value": round(value, 2), "unit": "impressions/s",
            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_per_step, 4),
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp32" if impl == "reference" else "bf16",
            "data": "synthetic MIND-shaped impressions (Zipf news popularity), random-init weights",
-           "impl": impl, "config": cfg, "clocks": clocks,
+           "impl": impl, "config": cfg, "details": details, "clocks": clocks,
            "e2e": {"value": round(e2e_val, 2), "unit": "impressions/s", "ms_per_step": round(e2e_ms, 4),
                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
            "gpu_launches": int(launches)}

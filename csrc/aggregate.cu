@@ -126,7 +126,10 @@ __device__ __forceinline__ void multimem_st_v4(float* mc, float4 v) {
 }
 
 // true when this launch has nothing to do: a failed aggregation is pending on the host, or a gated chain without
-// pending gradients. Uniform over the grid: both words only change in kernels that are alone on the stream.
+// pending gradients. The pending word only changes in kernels that are alone on the stream, so it is uniform over the
+// grid. The abort word can be raised by a peer's waiter at any moment: a launch that some blocks skipped leaves a
+// half-written buffer and an unreleased flag behind, which is fine because nothing after an abort is used - the waiters
+// report, the host resets the pads (fr_agg_pad_reset) and re-synchronises the state (FederatedRunner._degrade).
 __device__ __forceinline__ bool chain_idle(const AggParams& p, const uint32_t* my_pad) {
   if (ld_relaxed_sys(my_pad + kPadAbort) != 0u) return true;
   return p.gated && ld_relaxed_sys(my_pad + kPadPending) == 0u;

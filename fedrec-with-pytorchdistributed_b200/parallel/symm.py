@@ -315,6 +315,14 @@ class SymmetricHeap:
     def _err_arg(self):
         return self._err_dev
 
+    def _padded_len(self, t: torch.Tensor) -> int:
+        """The kernels move float4s. A heap allocation is 256-byte aligned, so rounding its length up stays inside it;
+        any other buffer has to hold a multiple of 4 floats itself."""
+        n = (t.numel() + 3) // 4 * 4
+        if n != t.numel() and (self.W == 1 or self.offset_of(t) + n * 4 > self.heap_bytes):
+            raise ValueError(f"aggregation buffer of {t.numel()} floats: the length must be a multiple of 4")
+        return n
+
     def mark_pending(self, ranks_here: int = 1, arm: bool = True) -> None:
         """The step's gradients are complete: arm the next gated chain (one tiny kernel on the current stream).
         ``arm=False`` launches the kernel without arming (warm-up before a graph capture: every kernel a capture
@@ -330,7 +338,7 @@ class SymmetricHeap:
                         ranks_here: int = 1, blocks: int = 0, gated: bool = False) -> torch.Tensor:
         assert self.peer_ptrs, "call finalize() first"
         bufs, pads, mc = self._ptr_arrays(g)
-        n = (g.numel() + 3) // 4 * 4
+        n = self._padded_len(g)
         check(self.lib.fr_grad_allreduce(bufs, pads, mc, self.W, self.rank if ranks_here == 1 else 0, ranks_here, n,
                                          float(clip), float(noise_std), float(scale), int(seed) & (2 ** 64 - 1),
                                          int(gated), blocks, self.timeout_ms, self._err_arg(), stream_ptr(self.device)),
@@ -347,7 +355,7 @@ class SymmetricHeap:
         device-side counter (``set_step``; required for chains replayed from a CUDA graph)."""
         assert self.peer_ptrs, "call finalize() first"
         bufs, pads, mc = self._ptr_arrays(g)
-        n = (g.numel() + 3) // 4 * 4
+        n = self._padded_len(g)
 
         def arr(x):
             xs = x if isinstance(x, (list, tuple)) else [x]
@@ -369,7 +377,7 @@ class SymmetricHeap:
         assert self.peer_ptrs, "call finalize() first"
         bufs, pads, mc = self._ptr_arrays(buf)
         w = (ctypes.c_float * self.W)(*[float(x) for x in weights])
-        n = (buf.numel() + 3) // 4 * 4
+        n = self._padded_len(buf)
         check(self.lib.fr_param_average(bufs, pads, mc, w, self.W, self.rank if ranks_here == 1 else 0, ranks_here, n,
                                         blocks, self.timeout_ms, self._err_arg(), stream_ptr(self.device)),
               "fr_param_average")

@@ -14,7 +14,7 @@ run() {   # label, extra bench args, env...
   rc=$?
   line=$(grep '"metric"' gpurun_out/sc.out | tail -1 | python -c 'import sys,json
 for l in sys.stdin:
-    d=json.loads(l); c=d["config"]; print(json.dumps({"value":d["value"],"ms":d["ms_per_step"],"e2e":d["e2e"]["value"],"heap":c.get("peer_heap"),"transport":c.get("transport"),"opt":c.get("optimizer","")[:9],"degraded":c.get("degraded")}))')
+    d=json.loads(l); c=d.get("details") or d["config"]; print(json.dumps({"value":d["value"],"ms":d["ms_per_step"],"e2e":d["e2e"]["value"],"heap":c.get("peer_heap"),"transport":c.get("transport"),"opt":c.get("optimizer","")[:9],"degraded":c.get("degraded")}))')
   echo "N=$N $label rc=$rc $line" | tee -a $OUT
   if [ $rc -ne 0 ]; then
     cp gpurun_out/sc.err gpurun_out/scale_check_${N}_${label}.err
