@@ -34,23 +34,44 @@ CLIP, SIGMA = 2.0, 0.05
 
 # ---- clocks -----------------------------------------------------------------------------------------
 class ClockSampler:
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi polled in a child process (no thread of ours competes with the launch loop). ``window()`` brackets a
+    timed region on the wall clock; the reported median covers only samples that fall inside such windows (all samples
+    when none was marked or none fell inside), so idle time between two loops does not flatter the figure."""
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
+    def __init__(self, gpu_index: int, period_ms: int = 25):
         self.path = tempfile.mktemp(prefix="fedrec_clocks_", suffix=".csv")
         self.proc = None
         self.idx = gpu_index
+        self.period_ms = period_ms
+        self.windows = []
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.idx)], stdout=open(self.path, "w"),
+                                          "-lms", str(self.period_ms), "-i", str(self.idx)], stdout=open(self.path, "w"),
                                          stderr=subprocess.DEVNULL)
         except OSError:
             self.proc = None
         return self
+
+    @contextlib.contextmanager
+    def window(self):
+        t0 = time.time()
+        try:
+            yield
+        finally:
+            self.windows.append((t0, time.time()))
+
+    @staticmethod
+    def _stamp(text: str):
+        import datetime
+        try:
+            return datetime.datetime.strptime(text, "%Y/%m/%d %H:%M:%S.%f").timestamp()
+        except ValueError:
+            return None
 
     def stop(self):
         if self.proc is None:
@@ -61,7 +82,7 @@ class ClockSampler:
             self.proc.wait(5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        rows, mx = [], []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         try:
             for line in open(self.path):
@@ -69,18 +90,27 @@ class ClockSampler:
                 if len(f) < 9:
                     continue
                 try:
-                    sm.append(float(f[1])); mx.append(float(f[2]))
+                    rows.append((self._stamp(f[0]), float(f[1]), [nm for nm, val in zip(names, f[5:9])
+                                                                   if val.lower().startswith("active")]))
+                    mx.append(float(f[2]))
                 except ValueError:
                     continue
-                for nm, val in zip(names, f[5:9]):
-                    if val.lower().startswith("active"):
-                        reasons.add(nm)
             os.remove(self.path)
         except OSError:
             pass
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        inside = [r for r in rows if r[0] is not None and any(a <= r[0] <= b for a, b in self.windows)]
+        used = inside or rows
+        sm = sorted(r[1] for r in used)
+        reasons = sorted({nm for r in used for nm in r[2]})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm), "samples_total": len(rows),
+                "scope": "inside the timed regions" if inside else "whole run (no sample fell inside a timed region)"}
+
+
+class _NoWindow:
+    @contextlib.contextmanager
+    def window(self):
+        yield
 
 
 def dist_env():
@@ -226,16 +256,18 @@ def run_ours(args):
         barrier()
         l0 = D.launch_count()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(args.warmup, total):
-            one_step(ids_d[i])
-        runner.step.flush()                             # the last step's update belongs to the timed region
-        e1.record()
-        settle()
+        with win():
+            e0.record()
+            for i in range(args.warmup, total):
+                one_step(ids_d[i])
+            runner.step.flush()                         # the last step's update belongs to the timed region
+            e1.record()
+            settle()
         barrier()
         return e0.elapsed_time(e1) / args.steps, D.launch_count() - l0
 
     sampler = ClockSampler(local_rank).start() if rank == 0 else None
+    win = (sampler or _NoWindow()).window
     # ---- end to end through the public API (TrainStep.run_host / loss_of): every step the ids travel from pinned host
     #      memory to the device (pulled over PCIe by the step's first kernel) and the step's loss travels back into host
     #      memory (pushed by its last kernel) where the host reads it. The host reads the loss of step i while step
@@ -267,23 +299,26 @@ def run_ours(args):
         barrier()
         tickets = deque()
         t0 = torch.cuda.Event(enable_timing=True); t1 = torch.cuda.Event(enable_timing=True)
-        t0.record()
-        host_loss, n_read = 0.0, 0
-        for i in range(args.warmup, total):
-            tickets.append(one_step_host(i))
-            if len(tickets) > args.e2e_lag:
+        with win():
+            t0.record()
+            host_loss, n_read = 0.0, 0
+            for i in range(args.warmup, total):
+                tickets.append(one_step_host(i))
+                if len(tickets) > args.e2e_lag:
+                    host_loss, n_read = step.loss_of(tickets.popleft()), n_read + 1
+            runner.step.flush()
+            while tickets:
                 host_loss, n_read = step.loss_of(tickets.popleft()), n_read + 1
-        runner.step.flush()
-        while tickets:
-            host_loss, n_read = step.loss_of(tickets.popleft()), n_read + 1
-        t1.record()
-        settle()
+            t1.record()
+            settle()
         barrier()
         assert n_read == args.steps
         return t0.elapsed_time(t1) / args.steps, host_loss
 
     # the end-to-end loop is the headline and runs first; the device-timed loop (ids resident on the device) follows
     e2e_ms, host_loss = guarded(timed_e2e)
+    if args.cooldown_s > 0:                             # let the board's power average recover: both loops then start alike
+        time.sleep(args.cooldown_s)
     ms, launches = guarded(timed_device)
     clocks = sampler.stop() if sampler else None
     h2d = ids_pin[0].numel() * 4
@@ -293,8 +328,8 @@ def run_ours(args):
             "optimizer": ("pipelined into the next step's graph (aggregation + Adam beside the frozen trunk)"
                           if runner.pipelined else "after the step"),
             "e2e_loss_read_lag_steps": args.e2e_lag, "last_loss": host_loss,
-            "order": "end-to-end loop first, device-timed loop second (under the 1 kW power cap whichever loop runs second sees "
-                     "lower clocks: expect e2e >= value on short runs)",
+            "order": "end-to-end loop first, %g s idle, device-timed loop second (under the 1 kW power cap a loop that "
+                     "follows another back to back sees lower clocks)" % args.cooldown_s,
             "degraded": runner.degraded,
             "peer_heap": (symm.describe() if symm else "none"),
             **({"trunk_cache": "ON — trunk outputs cached across steps; not comparable with the headline number"}
@@ -464,6 +499,7 @@ def main():
     ap.add_argument("--graph", choices=["on", "off"], default="on", help="replay the step from a CUDA graph")
     ap.add_argument("--e2e_lag", type=int, default=1, help="steps between queuing a loss read-back and consuming it")
     ap.add_argument("--agg_timeout_s", type=float, default=30.0)
+    ap.add_argument("--cooldown_s", type=float, default=1.0, help="idle time between the end-to-end and the device-timed loop")
     ap.add_argument("--fault", default="", help="testing: RANK:CALL:SECONDS makes one rank sleep before its CALL-th step, to "
                                                 "exercise the time-out report and the fall-back to NCCL")
     ap.add_argument("--transport", default="nvlink", choices=["nvlink", "collective"])
