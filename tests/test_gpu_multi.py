@@ -27,7 +27,6 @@ def _worker(rank, world, port, q):
     import torch.distributed as dist
     from fedrec_b200.config import FedRecConfig
     from fedrec_b200.engine.federated import FederatedRunner
-    from fedrec_b200.data import make_synthetic_mind
     res = {}
     try:
         cfg = FedRecConfig(mode="grad_avg", synthetic=True, num_news=2000, num_train=64, num_valid=8, title_len=30,

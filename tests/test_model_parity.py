@@ -5,7 +5,6 @@ import torch
 from conftest import load_reference_module
 from fedrec_b200.models import (AdditiveAttention, DistilBertTrunk, MultiHeadAttention, ScaledDotProductAttention,
                                 UserEncoder, UserModel)
-from fedrec_b200.models.distilbert import DistilBertConfigLite
 from fedrec_b200.ops import reference as ref
 
 
