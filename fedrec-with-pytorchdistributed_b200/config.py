@@ -37,6 +37,8 @@ class FedRecConfig:
     bert_ffn: int = 3072
     vocab_size: int = 30522
     max_positions: int = 512
+    bert_path: str = ""            # local HF-format DistilBERT directory (config.json + model.safetensors / pytorch_model.bin);
+                                   # empty: random-init trunk of the shape above (upstream downloads distilbert-base-uncased, encoder.py:19)
     # ---- data constants ------------------------------------------------------
     npratio: int = 4               # dataset.py:8
     max_his_len: int = 50          # dataset.py:9

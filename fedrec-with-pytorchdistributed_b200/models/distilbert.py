@@ -150,22 +150,90 @@ class DistilBertTrunk(nn.Module):
 
     @classmethod
     def from_pretrained(cls, name_or_path: str = "distilbert-base-uncased", **_):
-        """Load a local HF-format directory if one exists, else random-init from config.
+        """A local HuggingFace-format directory (``config.json`` + ``model.safetensors`` or ``pytorch_model.bin``) if
+        there is one, else random-init from the default config.
 
-        There is no network here; the reference's ``from_pretrained`` download
-        (encoder.py:19) becomes "use local weights when the user has them".
+        There is no network here; the reference's ``from_pretrained`` download (encoder.py:19) becomes "use local
+        weights when the user has them" (``FedRecConfig.bert_path``). Every trunk tensor has to be in the file with the
+        right shape; heads the trunk does not have (``vocab_*`` of the masked-LM checkpoint) are ignored.
         """
         import os
-        model = cls()
-        for fname in ("pytorch_model.bin", "model.pt"):
-            p = os.path.join(name_or_path, fname)
-            if os.path.isfile(p):
-                sd = torch.load(p, map_location="cpu", weights_only=True)
-                sd = {k.removeprefix("distilbert."): v for k, v in sd.items()}
-                model.load_state_dict(sd, strict=False)
-                break
+        if not os.path.isdir(name_or_path):
+            return cls()
+        model = cls(read_hf_config(os.path.join(name_or_path, "config.json")))
+        sd = None
+        if os.path.isfile(os.path.join(name_or_path, "model.safetensors")):
+            sd = read_safetensors(os.path.join(name_or_path, "model.safetensors"))
+        else:
+            for fname in ("pytorch_model.bin", "model.pt"):
+                if os.path.isfile(os.path.join(name_or_path, fname)):
+                    sd = torch.load(os.path.join(name_or_path, fname), map_location="cpu", weights_only=True)
+                    break
+        if sd is None:
+            raise FileNotFoundError(f"{name_or_path}: no model.safetensors, pytorch_model.bin or model.pt")
+        sd = {k.removeprefix("distilbert."): v for k, v in sd.items()}
+        want = model.state_dict()
+        missing = [k for k in want if k not in sd]
+        wrong = [k for k in want if k in sd and tuple(sd[k].shape) != tuple(want[k].shape)]
+        if missing or wrong:
+            raise ValueError(f"{name_or_path}: {len(missing)} trunk tensors missing (e.g. {missing[:3]}), {len(wrong)} with "
+                             f"a different shape (e.g. {wrong[:3]}) - is config.json the one of these weights?")
+        model.load_state_dict({k: sd[k].to(want[k].dtype) for k in want})
+        model.loaded_from = name_or_path
         return model
 
     def forward(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None):
         x = self.embeddings(input_ids)
         return (self.transformer(x, attention_mask),)
+
+
+def read_hf_config(path: str) -> DistilBertConfigLite:
+    """``config.json`` of a DistilBERT checkpoint → the fields this trunk uses (defaults = distilbert-base-uncased)."""
+    import json
+    import os
+    c = DistilBertConfigLite()
+    if not os.path.isfile(path):
+        return c
+    with open(path, encoding="utf-8") as f:
+        j = json.load(f)
+    mt = j.get("model_type", "distilbert")
+    if mt != "distilbert":
+        raise ValueError(f"{path}: model_type {mt!r}; this trunk implements DistilBERT")
+    for name in ("vocab_size", "max_position_embeddings", "n_layers", "n_heads", "dim", "hidden_dim", "dropout",
+                 "attention_dropout", "pad_token_id", "initializer_range"):
+        if name in j:
+            setattr(c, name, type(getattr(c, name))(j[name]))
+    if j.get("activation", "gelu") != "gelu" or j.get("sinusoidal_pos_embds", False):
+        raise ValueError(f"{path}: only the GELU / learned-position DistilBERT variant is implemented")
+    c.hidden_size = c.dim
+    return c
+
+
+_ST_DTYPES = {"F64": torch.float64, "F32": torch.float32, "F16": torch.float16, "BF16": torch.bfloat16,
+              "I64": torch.int64, "I32": torch.int32, "I16": torch.int16, "I8": torch.int8, "U8": torch.uint8,
+              "BOOL": torch.bool}
+
+
+def read_safetensors(path: str) -> dict:
+    """The safetensors container: u64 little-endian header length, a JSON header ``name → {dtype, shape, data_offsets}``,
+    then the raw little-endian tensor bytes. Read with numpy's memmap, so only what is copied out is paged in."""
+    import json
+    import numpy as np
+    with open(path, "rb") as f:
+        n = int.from_bytes(f.read(8), "little")
+        if n <= 0 or n > 100 << 20:
+            raise ValueError(f"{path}: not a safetensors file (header length {n})")
+        header = json.loads(f.read(n).decode("utf-8"))
+    raw = np.memmap(path, dtype=np.uint8, mode="r", offset=8 + n)
+    out = {}
+    for name, meta in header.items():
+        if name == "__metadata__":
+            continue
+        dt = _ST_DTYPES.get(meta["dtype"])
+        if dt is None:
+            raise ValueError(f"{path}: tensor {name} has unsupported dtype {meta['dtype']}")
+        lo, hi = meta["data_offsets"]
+        shape = tuple(meta["shape"])
+        t = torch.frombuffer(bytearray(raw[lo:hi]), dtype=dt) if hi > lo else torch.empty(0, dtype=dt)
+        out[name] = t.reshape(shape)
+    return out

@@ -22,6 +22,7 @@ Reference defects that are *not* reproduced: gradient doubling i
 """
 from __future__ import annotations
 
+import os
 import time
 
 from typing import Dict, List, Optional, Tuple, Union
@@ -52,12 +53,17 @@ class UserModel(nn.Module):
         super().__init__()
         self.cfg = config or FedRecConfig()
         self.device = torch.device(device) if device is not None else self.cfg.resolved_device()
-        if bert_config is None:
+        # cfg.bert_path: a local HuggingFace-format DistilBERT directory (upstream downloads the pretrained weights,
+        # encoder.py:19; here they are read from disk when given, else the trunk is random-init from the config)
+        pretrained = self.cfg.bert_path if (bert_config is None and self.cfg.bert_path) else None
+        if pretrained is not None and not os.path.isdir(pretrained):
+            raise FileNotFoundError(f"bert_path={pretrained!r} is not a directory")
+        if bert_config is None and pretrained is None:
             bert_config = DistilBertConfigLite(
                 vocab_size=self.cfg.vocab_size, max_position_embeddings=self.cfg.max_positions,
                 n_layers=self.cfg.bert_layers, n_heads=self.cfg.bert_heads, dim=self.cfg.bert_dim,
                 hidden_dim=self.cfg.bert_ffn, hidden_size=self.cfg.bert_dim)
-        self.text_encoder = TextEncoder(news_embedding_dim, bert_config=bert_config,
+        self.text_encoder = TextEncoder(news_embedding_dim, bert_config=bert_config, pretrained=pretrained or "",
                                         mask_padding=self.cfg.mask_padding).to(self.device)
         self.user_encoder = UserEncoder(news_embedding_dim, num_attention_heads, query_vector_dim,
                                         head_dim=news_embedding_dim // num_attention_heads,

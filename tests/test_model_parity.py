@@ -99,3 +99,49 @@ def test_user_encoder_functional_reference():
                            sd["additive_attention.att_fc1.weight"], sd["additive_attention.att_fc1.bias"],
                            sd["additive_attention.att_fc2.weight"], sd["additive_attention.att_fc2.bias"], 20)
     torch.testing.assert_close(got, ue(x), atol=1e-5, rtol=1e-4)
+
+
+def test_pretrained_directory_is_loaded_through_bert_path(tmp_path, tiny_bert):
+    """A HuggingFace-format directory (what upstream downloads, encoder.py:19) read from disk: config.json +
+    model.safetensors (own reader) or pytorch_model.bin; outputs equal the transformers model's."""
+    tr = pytest.importorskip("transformers")
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.models import UserModel
+    from fedrec_b200.models.distilbert import read_safetensors
+    hf_cfg = tr.DistilBertConfig(vocab_size=500, n_layers=2, n_heads=4, dim=64, hidden_dim=128, max_position_embeddings=40)
+    torch.manual_seed(3)
+    hf = tr.DistilBertModel(hf_cfg).eval()
+    d1 = tmp_path / "st"
+    hf.save_pretrained(str(d1))                                   # config.json + model.safetensors
+    assert (d1 / "model.safetensors").is_file()
+    sd = read_safetensors(str(d1 / "model.safetensors"))
+    for k, v in hf.state_dict().items():
+        assert torch.equal(sd[k], v), k
+    d2 = tmp_path / "bin"
+    d2.mkdir()
+    (d2 / "config.json").write_text((d1 / "config.json").read_text())
+    torch.save({"distilbert." + k: v for k, v in hf.state_dict().items()}, str(d2 / "pytorch_model.bin"))   # MLM-style prefix
+    ids = torch.randint(1, 500, (3, 9))
+    mask = torch.ones(3, 9, dtype=torch.long)
+    mask[1, 5:] = 0
+    with torch.no_grad():
+        want = hf(ids, attention_mask=mask)[0]
+    news_index = torch.zeros(8, 2, 9, dtype=torch.long).numpy()
+    for d in (d1, d2):
+        trunk = DistilBertTrunk.from_pretrained(str(d)).eval()
+        assert trunk.config.n_layers == 2 and trunk.config.dim == 64 and trunk.config.hidden_size == 64
+        with torch.no_grad():
+            torch.testing.assert_close(trunk(ids, attention_mask=mask)[0], want, atol=2e-5, rtol=1e-4)
+        m = UserModel(None, news_index, "cpu", config=FedRecConfig(bert_path=str(d), title_len=9, device="cpu"))
+        for k, v in hf.state_dict().items():
+            assert torch.equal(m.state_dict()["text_encoder.DistillBert." + k], v), k
+        assert not any(p.requires_grad for p in m.text_encoder.DistillBert.parameters())
+    # wrong weights for the config are refused, not half-loaded
+    bad = tmp_path / "bad"
+    bad.mkdir()
+    (bad / "config.json").write_text((d1 / "config.json").read_text().replace('"n_layers": 2', '"n_layers": 3'))
+    torch.save(hf.state_dict(), str(bad / "pytorch_model.bin"))
+    with pytest.raises(ValueError, match="missing"):
+        DistilBertTrunk.from_pretrained(str(bad))
+    with pytest.raises(FileNotFoundError):
+        UserModel(None, news_index, "cpu", config=FedRecConfig(bert_path=str(tmp_path / "nope"), device="cpu"))
