@@ -50,3 +50,22 @@ def tiny_bert():
 def tiny_data():
     from fedrec_b200.data import make_synthetic_mind
     return make_synthetic_mind(num_news=300, num_train=48, num_valid=12, title_len=12, seed=3)
+
+
+@pytest.fixture()
+def solo_group(monkeypatch):
+    """For tests that build a FederatedRunner inside the pytest process: a private rendezvous port, and the process group
+    is gone afterwards, so the default port stays free for tests that launch the entrypoints as subprocesses."""
+    import socket
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    monkeypatch.setenv("MASTER_ADDR", "127.0.0.1")
+    monkeypatch.setenv("MASTER_PORT", str(port))
+    monkeypatch.setenv("RANK", "0")
+    monkeypatch.setenv("LOCAL_RANK", "0")
+    monkeypatch.setenv("WORLD_SIZE", "1")
+    yield port
+    import torch.distributed as dist
+    if dist.is_initialized():
+        dist.destroy_process_group()

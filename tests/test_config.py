@@ -28,7 +28,7 @@ def test_kernel_switches(monkeypatch):
     assert not FedRecConfig.from_env().ln_fold
 
 
-def test_an_epoch_is_a_pass_over_the_shard(tiny_bert):
+def test_an_epoch_is_a_pass_over_the_shard(tiny_bert, solo_group):
     """total_epochs counts passes over the client's shard like upstream's DataLoader loop (main.py:55-91,135-139):
     ceil(impressions / batch_size) steps per epoch, every step an update; --steps_per_epoch overrides."""
     import torch

@@ -92,7 +92,7 @@ def test_sharding_keeps_a_user_on_one_client_and_files_load(tmp_path, vocab_file
         mind.prepare([news_path], beh_path, None, vocab_file, str(tmp_path / "flat"), num_clients=2)
 
 
-def test_command_line_and_a_training_step_on_the_result(tmp_path, vocab_file, tiny_bert):
+def test_command_line_and_a_training_step_on_the_result(tmp_path, vocab_file, tiny_bert, solo_group):
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
     import prepare_mind
     news_path, beh_path = _write_mind(tmp_path)
