@@ -225,16 +225,28 @@ class BatchSampler:
         cand_np[:, 0] = t.pos[idx]
         lo = t.neg_ptr[idx]
         cnt = t.neg_ptr[idx + 1] - lo
-        # distinct negatives per row when there are enough, else all of them + <unk>(0) padding
-        for j in range(self.B):
-            n = int(cnt[j])
-            if n >= self.npratio:
-                pick = self.rng.choice(n, size=self.npratio, replace=False) if n < 64 else \
-                    _floyd_sample(self.rng, n, self.npratio)
-                cand_np[j, 1:] = t.neg_idx[lo[j] + pick]
-            else:
-                cand_np[j, 1: 1 + n] = t.neg_idx[lo[j]: lo[j] + n]
-                cand_np[j, 1 + n:] = 0
+        # distinct negatives per row when there are enough, else all of them + <unk>(0) padding. Floyd's sampling run on
+        # all rows at once: draw k picks t from [0, n-K+k]; a value already taken is replaced by n-K+k, which no
+        # earlier draw can have produced (K numpy passes per batch instead of one generator call per impression)
+        K = self.npratio
+        enough = cnt >= K
+        picks = np.zeros((self.B, K), dtype=np.int64)
+        u = self.rng.random((self.B, K))
+        for k in range(K):
+            top = np.maximum(cnt - K + k, 0)
+            tk = np.minimum((u[:, k] * (top + 1)).astype(np.int64), top)
+            if k:
+                tk = np.where((picks[:, :k] == tk[:, None]).any(axis=1), top, tk)
+            picks[:, k] = tk
+        if K:
+            order = self.rng.random((self.B, K)).argsort(axis=1)       # Floyd's output order is biased; shuffle the picks
+            picks = np.take_along_axis(picks, order, axis=1)
+        few = np.arange(K)[None, :] < cnt[:, None]
+        off = np.where(enough[:, None], picks, np.arange(K)[None, :])
+        valid = enough[:, None] | few
+        src = np.minimum(lo[:, None] + off, max(len(t.neg_idx) - 1, 0))
+        vals = t.neg_idx[src] if len(t.neg_idx) else np.zeros_like(src, dtype=np.int32)
+        cand_np[:, 1:] = np.where(valid, vals, 0)
         his.numpy()[:] = t.his[idx]
         return cand, his
 

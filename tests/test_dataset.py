@@ -83,3 +83,30 @@ def test_device_prefetcher_yields_the_sampler_sequence(tiny_data):
         c0, h0 = ref.next()
         c1, h1 = pre.next()
         assert torch.equal(c0, c1) and torch.equal(h0, h1)
+
+
+def test_negative_sampling_is_distinct_uniform_and_pads_short_lists():
+    """Vectorised Floyd sampling in BatchSampler: every negative equally likely in every slot, no repeats within an
+    impression; fewer than npratio negatives → all of them, then <unk> (newsample, dataset.py:10-14)."""
+    from collections import Counter
+    from fedrec_b200.data import BatchSampler, ImpressionTable
+    sam = [(0, "a", [f"n{i}" for i in range(6)], ["a"], "u"), (1, "a", ["n0", "n1"], ["a"], "u"), (2, "a", [], ["a"], "u")]
+    n2i = {"<unk>": 0, "a": 1, **{f"n{i}": 2 + i for i in range(6)}}
+    s = BatchSampler(ImpressionTable(sam, n2i), 3, seed=1, pin=False)
+    any_slot, first_slot, rounds = Counter(), Counter(), 6000
+    for _ in range(rounds):
+        cand, _ = s.next()
+        for row in cand.numpy().tolist():
+            assert row[0] == 1
+            negs = row[1:]
+            if 0 not in negs:
+                assert len(set(negs)) == 4 and all(2 <= x <= 7 for x in negs)
+                any_slot.update(negs)
+                first_slot[negs[0]] += 1
+            elif negs.count(0) == 2:
+                assert negs[:2] == [2, 3]
+            else:
+                assert negs == [0, 0, 0, 0]
+    assert sum(first_slot.values()) == rounds
+    for v in range(2, 8):
+        assert abs(any_slot[v] / rounds - 4 / 6) < 0.03 and abs(first_slot[v] / rounds - 1 / 6) < 0.02
