@@ -22,6 +22,7 @@ shard, runs ``local_steps`` fused steps, and then one aggregation kernel runs:
 from __future__ import annotations
 
 import os
+import time
 from typing import List, Optional
 
 import torch
@@ -254,6 +255,7 @@ class FederatedRunner:
         while epoch < cfg.total_epochs:
             try:
                 self.faults.maybe_fire(self.rank, epoch)
+                self._epoch_started(spe)
                 for _ in range(spe):
                     loss = self.local_step()                  # pipelined: also applies the previous step's update
                     if not self.pipelined:
@@ -289,6 +291,7 @@ class FederatedRunner:
         while epoch < cfg.total_epochs:
             try:
                 self.faults.maybe_fire(self.rank, epoch)
+                self._epoch_started(spe * max(cfg.local_steps, 1))
                 for it in range(spe):
                     for _ in range(max(cfg.local_steps, 1)):
                         loss = self.local_step()
@@ -390,9 +393,18 @@ class FederatedRunner:
             transport.send_state_dict(ckpt.model_state_fp32_cpu(self.model), cfg.server_host, cfg.server_port,
                                       client_id=self.rank, timeout_s=cfg.timeout_s)
 
+    def _epoch_started(self, steps: int) -> None:
+        self._epoch_t0, self._epoch_steps = time.perf_counter(), steps
+
     def _end_of_epoch(self, epoch: int, loss: torch.Tensor, reduce_loss: bool, save: bool = True) -> None:
         cfg = self.cfg
-        rec = {"epoch": epoch, "training_loss": float(loss)}
+        rec = {"epoch": epoch, "training_loss": float(loss)}        # float(): the device has finished the epoch
+        t0 = getattr(self, "_epoch_t0", None)
+        if t0 is not None:                                          # upstream shows tqdm's it/s (main.py:57)
+            dt = max(time.perf_counter() - t0, 1e-9)
+            rec["epoch_time_s"] = round(dt, 4)
+            rec["impressions_per_s"] = round(self._epoch_steps * cfg.batch_size * (1 if self.is_server else self.W) / dt, 1)
+            self._epoch_t0 = None
         if reduce_loss and self.W > 1:
             tot = loss.detach().clone()
             dist.all_reduce(tot)                                   # GA:146
