@@ -405,6 +405,17 @@ class FederatedRunner:
             rec["epoch_time_s"] = round(dt, 4)
             rec["impressions_per_s"] = round(self._epoch_steps * cfg.batch_size * (1 if self.is_server else self.W) / dt, 1)
             self._epoch_t0 = None
+        if cfg.clip_norm > 0 and cfg.noise_multiplier > 0 and cfg.mode in ("ddp", "grad_avg") and self.train_sam \
+                and self.model.flat.step > 0:
+            # what the clipped + noised client gradients have cost so far (RDP accountant, sampled Gaussian mechanism
+            # with q = batch / shard size); upstream only ever computes a sigma for a target epsilon (client.py:217-226)
+            from ..utils.privacy import compute_epsilon
+            q = min(1.0, cfg.batch_size / max(len(self.train_sam), 1))
+            try:
+                rec["dp_epsilon_spent"] = round(compute_epsilon(cfg.noise_multiplier, q, int(self.model.flat.step), cfg.dp_delta), 4)
+                rec["dp_delta"] = cfg.dp_delta
+            except (OverflowError, ValueError, ZeroDivisionError):
+                pass                                                # sigma too small for the accountant's orders: no figure
         if reduce_loss and self.W > 1:
             tot = loss.detach().clone()
             dist.all_reduce(tot)                                   # GA:146

@@ -27,3 +27,22 @@ def test_calibration_hits_target():
     eps = compute_epsilon(sigma, 0.0125, math.ceil(50 / 0.0125), 1e-5)
     assert eps <= 10.0 and eps > 9.5
     assert get_noise_multiplier(1.0, 1e-5, 0.0125, epochs=50) > sigma
+
+
+def test_the_run_log_reports_the_privacy_spent(tiny_bert, solo_group):
+    """Clipped + noised gradient averaging logs the (epsilon, delta) its steps have cost so far, per epoch."""
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    from fedrec_b200.utils.privacy import compute_epsilon
+    cfg = FedRecConfig(mode="grad_avg", synthetic=True, num_news=120, num_train=40, num_valid=2, title_len=8, batch_size=4,
+                       total_epochs=2, steps_per_epoch=3, dropout=0.0, device="cpu", backend="gloo", clip_norm=2.0,
+                       noise_multiplier=1.0, snapshot_path="", log_dir="")
+    r = FederatedRunner(cfg, bert_config=tiny_bert)
+    seen = []
+    log = r.logger.log
+    r.logger.log = lambda rec, step=None: (seen.append(dict(rec)), log(rec, step=step))[1]
+    r.run_gradient_averaging()
+    eps = [x["dp_epsilon_spent"] for x in seen if "dp_epsilon_spent" in x]
+    assert len(eps) == 2 and eps[0] < eps[1]
+    assert abs(eps[1] - compute_epsilon(1.0, 4 / 40, 6, cfg.dp_delta)) < 1e-3
+    assert all("impressions_per_s" in x and x["epoch_time_s"] > 0 for x in seen if "epoch" in x)
