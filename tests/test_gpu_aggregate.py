@@ -1,4 +1,4 @@
-"""Aggregation kernels, all logical ranks emulated inside one cooperative launch on one GPU.
+"""The aggregation chain with all logical ranks emulated on one GPU (blockIdx.y slices of every launch of the chain).
 
 Oracle: the closed-form mean of the per-rank tensors computed with PyTorch (what an NCCL all-reduce
 followed by a divide returns)."""
