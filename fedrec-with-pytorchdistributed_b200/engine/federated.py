@@ -7,7 +7,8 @@ broadcast, per-tensor model broadcast, local epochs, state_dict upload over TCP,
 mean; client.py:256-292, server.py:72-105).
 
 Here a *round* is: every client draws a batch of ``batch_size`` impressions from its own
-shard, runs ``local_steps`` fused steps, and then one aggregation kernel runs:
+shard, runs ``local_steps`` fused steps, and then one aggregation chain runs (in the gradient modes inside the next
+step's CUDA graph, beside the frozen trunk):
 
 ``ddp`` / ``grad_avg``  gradients of all 16 trainable tensors are averaged (optionally
                         clipped and noised per client) **before** Adam (SURVEY.md §9.1);

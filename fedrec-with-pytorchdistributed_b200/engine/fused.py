@@ -11,9 +11,13 @@ Pipeline (reference call sites in parentheses):
   news-gradient segment-sum                  (main.py:20-42)
   text-head backward with the injected per-news gradient          (model.py:72-90)
 
-All GEMMs are ``fr_gemm_bf16`` (tcgen05 + TMEM + TMA). Buffers are allocated once for the
-worst case (every id distinct) and the de-dup count stays on the device, so the whole step is
-free of host synchronisation and can be captured in a CUDA graph.
+All GEMMs are ``fr_gemm_bf16`` / ``fr_gemm_bf16_fold`` (tcgen05 + TMEM + TMA); with ``cfg.ln_fold`` 11 of the trunk's 12
+LayerNorms live in the epilogues of the GEMMs around them. Buffers are allocated once for the worst case (every id
+distinct) and the de-dup count stays on the device, so the whole step is free of host synchronisation and is captured in a
+CUDA graph (``_capture``). Two things ride in that graph besides the step itself: the optimiser chain of the *previous*
+step (``attach_optimizer``: clip + noise + cross-client mean + Adam on a side branch beside the frozen trunk), and the
+step's host I/O (``enable_host_io``: ids pulled from a host-mapped pinned ring by the first kernel, the loss pushed into
+another by the last; ``run_host`` / ``loss_of``).
 """
 from __future__ import annotations
 
