@@ -95,3 +95,21 @@ def test_on_the_gpu_the_table_comes_from_the_sm100_kernels(tiny_data):
     want = torch.topk(full, 10, dim=1)
     torch.testing.assert_close(sc, want.values, atol=1e-5, rtol=1e-4)
     assert idx.shape == (2, 10) and not (set(idx[1].tolist()) & set(range(30, 80)))
+
+
+def test_json_lines_front_end(tmp_path, tiny_data):
+    import io
+    import json
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+    import recommend
+    cfg = FedRecConfig(synthetic=True, num_news=200, title_len=8, device="cpu", batch_size=2, bert_layers=1, bert_dim=64,
+                       bert_heads=4, bert_ffn=128, snapshot_path="")
+    d = __import__("fedrec_b200.data", fromlist=["make_synthetic_mind"]).make_synthetic_mind(200, 8, 2, 8, 50, seed=cfg.seed)
+    nids = [n for n in d.nid2index if n != "<unk>"]
+    reqs = [{"user": "a", "history": nids[:3], "k": 4}, {"user": "b", "history": ["nope"], "k": 2}, {"user": "c", "history": nids[5:40]}]
+    out = io.StringIO()
+    n = recommend.serve([json.dumps(r) for r in reqs] + [""], out, cfg, default_k=3)
+    rows = [json.loads(l) for l in out.getvalue().splitlines()]
+    assert n == 3 and [r["user"] for r in rows] == ["a", "b", "c"] and [len(r["news"]) for r in rows] == [4, 2, 3]
+    assert not set(rows[0]["news"]) & set(nids[:3]) and "<unk>" not in rows[1]["news"]
+    assert all(rows[i]["scores"] == sorted(rows[i]["scores"], reverse=True) for i in range(3))
