@@ -109,11 +109,19 @@ class FederatedRunner:
                                          timeout_s=cfg.timeout_s)
         self.local_opt = None
         self.sampler = None
+        self._native = None
         if not self.is_server and train_sam:
             table = ImpressionTable(train_sam, nid2index, cfg.max_his_len)
             self.sampler = BatchSampler(table, cfg.batch_size, cfg.npratio, seed=cfg.seed + 101 * self.rank,
                                         pin=self.device.type == "cuda")
             self.prefetch = DevicePrefetcher(self.sampler, self.device)
+            if cfg.native_loader:
+                # batches come from the C++ producer thread (csrc/host_loader.cu) in the step's packed layout and enter
+                # the step through its host-mapped ring (TrainStep.run_host): no sampler work, staging copy or prefetch
+                # stream on the launch path
+                from ..data.native_loader import NativeBatchLoader
+                self._native = NativeBatchLoader(table, cfg.batch_size, cfg.npratio, seed=cfg.seed + 101 * self.rank)
+                self.step.enable_host_io(cfg.batch_size, 1 + cfg.npratio, cfg.max_his_len)
         self.logger = MetricsLogger(cfg.log_dir, cfg.run_name, self.rank, enabled=bool(cfg.log_dir))
         self.tracer = Tracer(enabled=os.environ.get("FEDREC_TRACE") == "1", device=self.device)
         self.faults = FaultInjector()
@@ -211,6 +219,10 @@ class FederatedRunner:
         return self.prefetch.next()
 
     def local_step(self) -> torch.Tensor:
+        if self._native is not None:
+            with self.tracer.span("step"):
+                ticket = self.step.run_host(self._native.next_packed())
+            return _HostLoss(self.step, ticket, self.device)
         cand, his = self.next_batch()
         with self.tracer.span("step"):
             return self.step.run(cand, his, train=True)
@@ -449,6 +461,9 @@ class FederatedRunner:
             pass
         if self.heartbeat:
             self.heartbeat.stop()
+        if self._native is not None:
+            self._native.close()
+            self._native = None
         if self.tracer.enabled:
             os.makedirs(self.cfg.log_dir or ".", exist_ok=True)
             self.tracer.export_chrome(os.path.join(self.cfg.log_dir or ".", f"trace.rank{self.rank}.json"))
@@ -458,6 +473,24 @@ class FederatedRunner:
         if self._tcp_server is not None:
             self._tcp_server.close()
         shutdown_distributed(self.info)
+
+
+class _HostLoss:
+    """Loss of a step that ran through ``TrainStep.run_host``: read from host memory when (and if) somebody asks."""
+
+    def __init__(self, step, ticket: int, device):
+        self._step, self._ticket, self._device, self._value = step, ticket, device, None
+
+    def __float__(self) -> float:
+        if self._value is None:
+            self._value = float(self._step.loss_of(self._ticket))
+        return self._value
+
+    def item(self) -> float:
+        return float(self)
+
+    def detach(self) -> torch.Tensor:
+        return torch.tensor(float(self), device=self._device)
 
 
 _POSITIONAL = {

@@ -69,6 +69,11 @@ SIGNATURES = {
     "fr_symm_export": (I, [P, P]),
     "fr_symm_import": (I, [P, P]),
     "fr_symm_close": (I, [P]),
+    # host_loader.cu (host code only)
+    "fr_loader_create": (P, [P, P, P, P, LL, I, I, I, c_ulonglong, I]),
+    "fr_loader_next": (I, [P, P, P]),
+    "fr_loader_batch_ints": (LL, [P]),
+    "fr_loader_destroy": (None, [P]),
     # gemm_sm100.cu
     "fr_gemm_bf16": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, I, P]),
     "fr_gemm_bf16_ex": (I, [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, I, I, I, P]),

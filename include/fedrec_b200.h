@@ -275,6 +275,21 @@ int fr_gemm_bf16_fold(const void* A, const void* W, const float* bias, const voi
 int fr_gemm_grad_bf16(const void* A, const void* B, float* out, int M1, int N1, int K, int lda, int ldb, int ldo,
                       const int* k_dev, int k_scale, int splits, void* stream);
 
+/* ---- host-side batch producer (csrc/host_loader.cu; no CUDA, callable on a CPU-only box) ------------------------- */
+
+/* A client's impression shard (pos [S], his [S, L] 0-padded, negatives as CSR neg_ptr [S+1] / neg_idx) -> packed id
+ * batches on a background thread: B impressions per batch in a fresh permutation per pass, K distinct sampled negatives
+ * each (all of them + <unk> = 0 when an impression has fewer), `depth` batches prepared ahead. The arrays are copied.
+ * fr_loader_next blocks until a batch is ready and copies its B*L + B*(1+K) int32 news rows into out (histories first,
+ * then candidates with the clicked news in column 0: the layout fr_hostio_fetch feeds to the step); *epoch_out = pass
+ * over the shard (1-based) the batch ended in. Replaces the DataLoader over TrainDataset (dataset.py:69-86, :10-14;
+ * main.py:55-64). Returns NULL / non-zero with fr_last_error() set on bad arguments. */
+void* fr_loader_create(const int* pos, const int* his, const long long* neg_ptr, const int* neg_idx, long long S, int L,
+                       int B, int K, unsigned long long seed, int depth);
+int fr_loader_next(void* loader, int* out, long long* epoch_out);
+long long fr_loader_batch_ints(void* loader);
+void fr_loader_destroy(void* loader);
+
 #ifdef __cplusplus
 }
 #endif
