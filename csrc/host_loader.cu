@@ -62,6 +62,7 @@ struct Loader {
   std::mutex mu;
   std::condition_variable not_empty, not_full;
   std::deque<Batch> queue;
+  std::vector<std::vector<int32_t>> spare;           // buffers handed back by the consumer
   bool stop = false;
   std::thread worker;
 
@@ -80,7 +81,7 @@ struct Loader {
 
   void fill(Batch& b) {
     const int C = 1 + K;
-    b.ids.assign((size_t)B * (L + C), 0);
+    b.ids.resize((size_t)B * (L + C));                // histories are copied whole; candidate rows are zeroed below
     int32_t* h_out = b.ids.data();
     int32_t* c_out = b.ids.data() + (size_t)B * L;
     int64_t pick[64];
@@ -89,6 +90,7 @@ struct Loader {
       std::memcpy(h_out + (size_t)j * L, his.data() + (size_t)s * L, sizeof(int32_t) * (size_t)L);
       int32_t* c = c_out + (size_t)j * C;
       c[0] = pos[(size_t)s];
+      for (int k = 1; k < C; ++k) c[k] = 0;
       const int64_t lo = neg_ptr[(size_t)s], n = neg_ptr[(size_t)s + 1] - lo;
       if (n >= K) {
         // Floyd: K distinct values of [0, n); then a shuffle, because Floyd's output order is not uniform
@@ -110,6 +112,10 @@ struct Loader {
   void run() {
     for (;;) {
       Batch b;
+      {
+        std::lock_guard<std::mutex> lk(mu);
+        if (!spare.empty()) { b.ids = std::move(spare.back()); spare.pop_back(); }
+      }
       fill(b);
       std::unique_lock<std::mutex> lk(mu);
       not_full.wait(lk, [&] { return stop || (int)queue.size() < depth; });
@@ -162,6 +168,10 @@ FR_API int fr_loader_next(void* handle, int32_t* out, long long* epoch_out) {
   }
   std::memcpy(out, b.ids.data(), sizeof(int32_t) * b.ids.size());
   if (epoch_out) *epoch_out = b.epoch;
+  {
+    std::lock_guard<std::mutex> lk(ld->mu);
+    if ((int)ld->spare.size() < ld->depth + 2) ld->spare.push_back(std::move(b.ids));
+  }
   return 0;
 }
 
