@@ -47,6 +47,14 @@ def init_distributed(backend: str = "auto", timeout_s: float = 1800.0, device: O
                       timeout=datetime.timedelta(seconds=timeout_s))
         if backend == "nccl":
             kwargs["device_id"] = dev
+        attempt = int(os.environ.get("TORCHELASTIC_RESTART_COUNT", "0") or 0)
+        if attempt > 0 and os.environ.get("TORCHELASTIC_USE_AGENT_STORE") == "True":
+            # relaunched by `torchrun --max-restarts`: the agent's key-value store outlives the workers, and with a static
+            # rendezvous the previous incarnation's transport addresses are still in it under the same keys; a restarted
+            # rank that reads one of those connects to a dead process. Give every incarnation its own key space.
+            base = dist.TCPStore(os.environ["MASTER_ADDR"], int(os.environ["MASTER_PORT"]), world, False,
+                                 datetime.timedelta(seconds=timeout_s))
+            kwargs["store"] = dist.PrefixStore(f"fedrec/attempt_{attempt}", base)
         dist.init_process_group(**kwargs)
         owns = True
     return DistInfo(rank, local_rank, world, backend, dev, owns)

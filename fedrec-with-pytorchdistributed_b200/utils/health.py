@@ -84,6 +84,8 @@ class FaultInjector:
     def maybe_fire(self, rank: int, rnd: int) -> None:
         if self.kind is None or rank != self.rank or rnd != self.round:
             return
+        if int(os.environ.get("TORCHELASTIC_RESTART_COUNT", "0") or 0) > 0:
+            return          # the fault belongs to the first incarnation: after torchrun --max-restarts relaunched the job it runs clean
         if self.kind == "kill":
             print(f"[fedrec] fault injection: rank {rank} exits at round {rnd}", flush=True)
             os._exit(17)
