@@ -429,6 +429,11 @@ class FederatedRunner:
                 rec["dp_delta"] = cfg.dp_delta
             except (OverflowError, ValueError, ZeroDivisionError):
                 pass                                                # sigma too small for the accountant's orders: no figure
+        if cfg.validate_every > 0 and (epoch + 1) % cfg.validate_every == 0:
+            v = self.validate()      # every rank over its own validation shard, like the client role (client.py:180)
+            if v:
+                rec.update({"validation_loss": v[0], "valid_auc": v[1], "valid_mrr": v[2], "val_ndcg@5": v[3],
+                            "val_ndcg@10": v[4]})
         if reduce_loss and self.W > 1:
             tot = loss.detach().clone()
             dist.all_reduce(tot)                                   # GA:146

@@ -48,3 +48,17 @@ def test_an_epoch_is_a_pass_over_the_shard(tiny_bert, solo_group):
     r2.run_parameter_averaging()
     assert r2.model.flat.step == 2 * 1 * 2                # epochs x rounds per epoch x local steps
     assert torch.isfinite(r2.model.flat.param).all()
+
+
+def test_validate_every_adds_ranking_metrics_to_the_epoch_log(tiny_bert, solo_group):
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    cfg = FedRecConfig(mode="grad_avg", synthetic=True, num_news=120, num_train=8, num_valid=6, title_len=8, batch_size=4,
+                       total_epochs=3, validate_every=2, dropout=0.0, device="cpu", backend="gloo", snapshot_path="", log_dir="")
+    r = FederatedRunner(cfg, bert_config=tiny_bert)
+    seen = []
+    log = r.logger.log
+    r.logger.log = lambda rec, step=None: (seen.append(dict(rec)), log(rec, step=step))[1]
+    r.run_gradient_averaging()
+    with_val = [x["epoch"] for x in seen if "valid_auc" in x]
+    assert with_val == [1] and all(0.0 <= x["valid_auc"] <= 1.0 for x in seen if "valid_auc" in x)
