@@ -185,6 +185,31 @@ def build_samples(behaviors_path: str, nid2index: Optional[Dict[str, int]] = Non
     return out
 
 
+def read_impressions(behaviors_path: str, nid2index: Optional[Dict[str, int]] = None):
+    """``behaviors.tsv`` kept as impressions (for ranking a released split): a list of
+    ``(impression_id, user, history, candidates, labels or None)``; labels are None when the file has none (MIND test).
+    Unknown history ids are dropped; unknown candidates stay (they rank as the ``<unk>`` news) so that every impression
+    keeps its candidate count."""
+    known = (lambda n: True) if nid2index is None else nid2index.__contains__
+    out = []
+    with open(behaviors_path, encoding="utf-8") as f:
+        for line in f:
+            cols = line.rstrip("\n").split("\t")
+            if len(cols) < 5:
+                continue
+            cands, labels = [], []
+            for item in cols[4].split():
+                nid, sep, label = item.rpartition("-")
+                if sep and label in ("0", "1"):
+                    cands.append(nid)
+                    labels.append(int(label))
+                else:
+                    cands.append(item)
+            out.append((cols[0], cols[1], [n for n in cols[3].split() if known(n)], cands,
+                        labels if len(labels) == len(cands) and cands else None))
+    return out
+
+
 def client_of(user: str, num_clients: int) -> int:
     """Stable across processes and Python versions (unlike ``hash``)."""
     return zlib.crc32(user.encode("utf-8")) % max(num_clients, 1)

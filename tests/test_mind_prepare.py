@@ -111,3 +111,27 @@ def test_command_line_and_a_training_step_on_the_result(tmp_path, vocab_file, ti
     r = FederatedRunner(cfg, bert_config=tiny_bert)
     loss = r.run_gradient_averaging()
     assert np.isfinite(loss) and r.model.flat.step == 1
+
+
+def test_prediction_file_in_the_leaderboard_format(tmp_path, vocab_file):
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+    import predict_mind
+    news_path, beh_path = _write_mind(tmp_path)
+    out = str(tmp_path / "shard")
+    mind.prepare([news_path], beh_path, None, vocab_file, out, title_len=8)
+    imps = mind.read_impressions(beh_path, load_user_data(out)[0])
+    assert [i[0] for i in imps] == ["1", "2", "3", "4"] and imps[0][3] == ["N3", "N4", "N2"] and imps[0][4] == [1, 0, 0]
+    assert imps[0][2] == ["N1", "N2"] and imps[3][3] == ["N9", "N1"]           # unknown history id dropped, candidates kept
+    unl = tmp_path / "test_behaviors.tsv"
+    unl.write_text("9\tU1\tt\tN1\tN3 N4 N2\n", encoding="utf-8")
+    assert mind.read_impressions(str(unl))[0][3:] == (["N3", "N4", "N2"], None)
+    pred = str(tmp_path / "prediction.txt")
+    rc = predict_mind.main(["--behaviors", beh_path, "--out", pred, "--data_dir", out, "--title_len", "8", "--device", "cpu",
+                            "--bert_layers", "1", "--bert_dim", "64", "--bert_heads", "4", "--bert_ffn", "128",
+                            "--snapshot_path", ""])
+    assert rc == 0
+    lines = open(pred).read().splitlines()
+    assert len(lines) == 4 and lines[0].startswith("1 [") and lines[1].startswith("2 [")
+    for line, n in zip(lines, (3, 4, 2, 2)):
+        ranks = [int(x) for x in line.split(" ", 1)[1].strip("[]").split(",")]
+        assert sorted(ranks) == list(range(1, n + 1))
