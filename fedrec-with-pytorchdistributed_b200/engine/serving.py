@@ -10,6 +10,7 @@ training-time ones (``sigmoid(news . user)``, model.py:118-119), so ranking a ca
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Sequence, Tuple
 
 import torch
@@ -41,6 +42,19 @@ class Recommender:
         self.news_vecs = v
         self._table = v.to(self.table_dtype)
         self.version += 1
+        return self
+
+    def save_table(self, path: str) -> None:
+        """The encoded table as a file, so a serving process starts without running the text encoder."""
+        self._need_table()
+        tmp = path + ".tmp"
+        torch.save({"news_vecs": self.news_vecs.cpu(), "version": self.version}, tmp)
+        os.replace(tmp, path)
+
+    def load_table(self, path: str) -> "Recommender":
+        blob = torch.load(path, map_location="cpu", weights_only=True)
+        self.refresh(blob["news_vecs"])
+        self.version = int(blob.get("version", self.version))
         return self
 
     def _need_table(self) -> None:

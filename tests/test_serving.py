@@ -113,3 +113,13 @@ def test_json_lines_front_end(tmp_path, tiny_data):
     assert n == 3 and [r["user"] for r in rows] == ["a", "b", "c"] and [len(r["news"]) for r in rows] == [4, 2, 3]
     assert not set(rows[0]["news"]) & set(nids[:3]) and "<unk>" not in rows[1]["news"]
     assert all(rows[i]["scores"] == sorted(rows[i]["scores"], reverse=True) for i in range(3))
+
+
+def test_the_table_round_trips_through_a_file(served, tmp_path):
+    m, rec = served
+    p = str(tmp_path / "news_vecs.pt")
+    rec.save_table(p)
+    other = Recommender(m).load_table(p)
+    assert other.version == rec.version and torch.equal(other.news_vecs, rec.news_vecs)
+    his = rec.pad_histories([[3, 4, 5]])
+    assert torch.equal(other.recommend(his, k=5)[0], rec.recommend(his, k=5)[0])
