@@ -87,6 +87,7 @@ class FedRecConfig:
     agg_blocks: int = 0            # grid of the aggregation kernels (0 = default)
     pipeline_optimizer: bool = True  # apply step i's aggregation + Adam at the start of step i+1, beside the frozen trunk
     steps_per_epoch: int = 0       # 0 = one pass over the client's shard per epoch (upstream main.py:55-91)
+    participation: float = 1.0     # param_avg / client_server: fraction of the clients that train in a round (FedAvg's C); the rest enter the average with weight 0
     validate_every: int = 0        # ddp / grad_avg / param_avg: validate every N epochs (0 = never, as upstream; the client role always does)
     native_loader: bool = False    # batches from the C++ producer thread (csrc/host_loader.cu) through TrainStep.run_host
     heartbeat_s: float = 5.0       # straggler/failure detector period when world_size > 1 (0 = off)

@@ -239,6 +239,24 @@ class FederatedRunner:
             w[cfg.server_rank] = 0.0
         return w
 
+    def active_clients(self, rnd: int) -> List[int]:
+        """The clients that train in aggregation round ``rnd`` (FedAvg's client fraction; ``cfg.participation`` < 1). The
+        draw is a function of (seed, round), so every rank computes the same set without talking. Everybody still takes
+        part in the aggregation itself: the others enter with weight 0 and receive the result."""
+        cfg = self.cfg
+        clients = [r for r in range(self.W) if not (cfg.mode == "client_server" and self.W > 1 and r == cfg.server_rank)]
+        if cfg.participation >= 1.0 or len(clients) <= 1:
+            return clients
+        import numpy as np
+        m = max(1, int(round(cfg.participation * len(clients))))
+        g = np.random.default_rng([int(cfg.seed) & 0xFFFFFFFF, 7919, int(rnd)])
+        return sorted(int(x) for x in g.choice(clients, size=m, replace=False))
+
+    @staticmethod
+    def _round_weights(weights: List[float], active: List[int]) -> List[float]:
+        w = [x if r in active else 0.0 for r, x in enumerate(weights)]
+        return w if sum(w) > 0 else [1.0 if r in active else 0.0 for r in range(len(weights))]
+
     def validate(self):
         if self.is_server or not self.valid_sam:
             return None
@@ -306,16 +324,19 @@ class FederatedRunner:
                 self.faults.maybe_fire(self.rank, epoch)
                 self._epoch_started(spe * max(cfg.local_steps, 1))
                 for it in range(spe):
-                    for _ in range(max(cfg.local_steps, 1)):
-                        loss = self.local_step()
-                        self._local_adam()
+                    active = self.active_clients(self.round)
+                    if self.rank in active:
+                        for _ in range(max(cfg.local_steps, 1)):
+                            loss = self.local_step()
+                            self._local_adam()
                     self.flush()
                     if it == spe - 1 and (epoch + 1) % cfg.save_every == 0 and cfg.snapshot_path:
                         self.save(epoch)                              # saved before averaging, as PA:140-141
                     with self.tracer.span("aggregate"):
-                        self.param_agg.average_(self.model.flat.param, weights)
+                        w_round = self._round_weights(weights, active)
+                        self.param_agg.average_(self.model.flat.param, w_round)
                         if cfg.average_frozen and self.W > 1:
-                            self._average_frozen(weights)
+                            self._average_frozen(w_round)
                     self.round += 1
                     if self.heartbeat:
                         self.heartbeat.beat(self.round)
@@ -358,7 +379,8 @@ class FederatedRunner:
             try:
                 self.faults.maybe_fire(self.rank, rnd)
                 self.param_agg.broadcast_(self.model.flat.param, src)  # X8 model sync
-                if not self.is_server:
+                active = self.active_clients(rnd)
+                if not self.is_server and self.rank in active:
                     for _ in range(max(cfg.total_epochs, 1) * self.steps_per_epoch()):   # client.py:284: local epochs per round
                         loss = self.local_step()
                         self._local_adam()
@@ -371,9 +393,9 @@ class FederatedRunner:
                     self.logger.log(rec, step=rnd)
                 with self.tracer.span("aggregate"):
                     if cfg.transport == "tcp" and self.W > 1:
-                        self._tcp_upload_and_average(src, weights)            # X9 + K23 the upstream way (other hosts)
+                        self._tcp_upload_and_average(src, self._round_weights(weights, active))   # X9 + K23 the upstream way (other hosts)
                     else:
-                        self.param_agg.average_(self.model.flat.param, weights)   # X9 + K23 in one kernel chain
+                        self.param_agg.average_(self.model.flat.param, self._round_weights(weights, active))   # X9 + K23 in one kernel chain
                         if self.symm is not None and not self.degraded:
                             self.symm.check(sync=True)            # rounds are long: find out now, not a round later
             except AggregationError as e:

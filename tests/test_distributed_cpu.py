@@ -281,3 +281,52 @@ def test_torchrun_restarts_the_job_after_a_client_died_and_it_resumes(tmp_path):
     assert "Resuming training from snapshot at Epoch 2" in out
     assert "epoch=3" in out
     assert torch.load(snap, weights_only=False)["EPOCHS_RUN"] == 4
+
+
+def _run_partial(rank, world, port, mode, q):
+    sys.path.insert(0, ROOT)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
+    torch.set_num_threads(2)
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.engine.federated import FederatedRunner
+    from fedrec_b200.models.distilbert import DistilBertConfigLite
+    bert = DistilBertConfigLite(n_layers=1, dim=32, hidden_dim=64, n_heads=2, hidden_size=32)
+    cfg = FedRecConfig(mode=mode, synthetic=True, num_news=128, num_train=16, num_valid=4, title_len=8, batch_size=4,
+                       total_epochs=2 if mode == "param_avg" else 1, global_epochs=5, steps_per_epoch=3, local_steps=2,
+                       dropout=0.0, device="cpu", backend="gloo", snapshot_path="", log_dir="", lr=1e-2,
+                       participation=0.5, server_rank=world - 1, heartbeat_s=0.0)
+    r = FederatedRunner(cfg, bert_config=bert)
+    n_rounds = 6 if mode == "param_avg" else 5
+    sets = [r.active_clients(k) for k in range(n_rounds)]
+    r.run_parameter_averaging() if mode == "param_avg" else r.run_client_server()
+    p = r.model.flat.param.clone()
+    ps = [torch.zeros_like(p) for _ in range(world)]
+    dist.all_gather(ps, p)
+    res = {"sets": sets, "steps": int(r.model.flat.step), "equal": all(torch.equal(ps[0], x) for x in ps)}
+    r.close()
+    q.put((rank, res))
+
+
+@pytest.mark.parametrize("mode", ["param_avg", "client_server"])
+def test_client_sampling_trains_a_fraction_of_the_clients_per_round(mode):
+    """``participation`` (FedAvg's client fraction): every rank draws the same active set per round, only those clients
+    train, everybody ends the round with the same model."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    world = 3 if mode == "param_avg" else 4                     # client_server: 3 clients + the server (last rank)
+    procs = [ctx.Process(target=_run_partial, args=(r, world, port, mode, q)) for r in range(world)]
+    [p.start() for p in procs]
+    out = dict(q.get(timeout=300) for _ in range(world))
+    [p.join(60) for p in procs]
+    sets = out[0]["sets"]
+    assert all(out[r]["sets"] == sets for r in range(world))                  # no communication needed to agree
+    assert all(len(s) == 2 and all(c < 3 for c in s) for s in sets) and len({tuple(s) for s in sets}) > 1
+    per_round = 2 if mode == "param_avg" else 3 * 1                          # local_steps | steps_per_epoch x total_epochs
+    for r in range(3):
+        assert out[r]["steps"] == per_round * sum(r in s for s in sets), (r, out[r]["steps"], sets)
+    if mode == "client_server":
+        assert out[3]["steps"] == 0
+    if mode == "param_avg":
+        assert all(out[r]["equal"] for r in range(world))
