@@ -11,7 +11,7 @@ on the device (one sort per metric), which is what ``Trainer.validate`` uses.
 """
 from __future__ import annotations
 
-from typing import Dict, Tuple
+from typing import Optional, Dict, Tuple
 
 import numpy as np
 import torch
@@ -84,17 +84,27 @@ def evaluation_split(news_vecs, user_vecs, samples, nid2index, progress: bool = 
 
 
 @torch.no_grad()
-def batched_ranking_metrics(scores: torch.Tensor, labels: torch.Tensor) -> Dict[str, torch.Tensor]:
-    """``scores``/``labels`` are ``[S, C]``; returns per-impression ``auc, mrr, ndcg5, ndcg10`` ``[S]``."""
+def batched_ranking_metrics(scores: torch.Tensor, labels: torch.Tensor,
+                            valid: Optional[torch.Tensor] = None) -> Dict[str, torch.Tensor]:
+    """``scores``/``labels`` are ``[S, C]``; returns per-impression ``auc, mrr, ndcg5, ndcg10`` ``[S]``.
+
+    ``valid`` (bool ``[S, C]``, true entries first in every row) makes the rows ragged: impressions with different
+    candidate counts padded to a common width (full-ranking evaluation, evaluation_functions.py:33-46)."""
     scores = scores.float()
     labels = labels.to(scores.dtype)
     S, C = scores.shape
+    if valid is not None:
+        v = valid.to(scores.dtype)
+        labels = labels * v
+        scores = scores.masked_fill(~valid.bool(), float("-inf"))      # padding ranks after every real candidate
     n_pos = labels.sum(1)
-    n_neg = C - n_pos
+    n_neg = (C if valid is None else v.sum(1)) - n_pos
     # AUC with ties counted 1/2: pairwise comparison (C is small: 5 in training, ≤ ~300 in eval)
     diff = scores[:, :, None] - scores[:, None, :]
     win = (diff > 0).to(scores.dtype) + 0.5 * (diff == 0).to(scores.dtype)
     pair = labels[:, :, None] * (1 - labels[:, None, :])
+    if valid is not None:
+        pair = pair * v[:, None, :]                                      # padding is nobody's negative
     auc = (win * pair).sum((1, 2)) / (n_pos * n_neg).clamp_min(1)
     # rank order of the reference: np.argsort(y_score)[::-1] (evaluation_functions.py:6,20), i.e. among equal scores the
     # HIGHER column comes first. Validation puts the positive in column 0, so a model whose scores saturate to equal

@@ -108,6 +108,31 @@ def test_evaluate_script_runs(tmp_path):
     assert "auc=" in r.stdout and "ndcg@10=" in r.stdout
 
 
+def test_device_batched_evaluation_equals_the_per_impression_loop(tiny_bert, tiny_data):
+    """evaluate.py ranks padded batches with a validity mask; upstream's loop (evaluation_functions.py:33-46) ranks one
+    impression at a time on the host. Same numbers."""
+    import importlib.util
+    import numpy as np
+    from fedrec_b200.config import FedRecConfig
+    from fedrec_b200.models import UserModel
+    from fedrec_b200.utils.metrics import evaluation_split
+    spec = importlib.util.spec_from_file_location("_evaluate_script", os.path.join(ROOT, "evaluate.py"))
+    ev = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(ev)
+    torch.manual_seed(0)
+    m = UserModel(None, tiny_data.news_index, "cpu", config=FedRecConfig(title_len=12, device="cpu"), bert_config=tiny_bert)
+    sam = list(tiny_data.valid_sam) + list(tiny_data.train_sam[:20])
+    sam = [(s[0], [s[1]] if not isinstance(s[1], (list, tuple)) else list(s[1]), list(s[2])[: 3 + i % 9], s[3], s[4])
+           for i, s in enumerate(sam)]
+    sam.append((999, ["N100001"], [], [], "u"))                    # single-class impression: skipped by both
+    nv = m.encode_all_news()
+    uv = m.encode_users(sam, tiny_data.nid2index, nv)
+    a = ev.ranked_on_device(nv, uv, sam, tiny_data.nid2index, batch=7)
+    b = evaluation_split(nv.numpy(), uv.numpy(), sam, tiny_data.nid2index)
+    assert a.shape == b.shape == (len(sam) - 1, 4)
+    np.testing.assert_allclose(a, b, atol=2e-5)
+
+
 def test_upstream_toy_shard_loads_and_trains(tiny_bert):
     """The four files upstream ships in UserData/ (T=50 titles, 76-click history) load and drive a step unchanged."""
     import pytest

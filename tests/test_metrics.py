@@ -78,3 +78,36 @@ def test_tied_scores_rank_like_the_reference():
     ref = compute_amn(y2, s2)
     m2 = batched_ranking_metrics(torch.tensor([s2]), torch.tensor([y2]))
     assert [float(m2[k][0]) for k in ("auc", "mrr", "ndcg5", "ndcg10")] == pytest.approx(list(ref))
+
+
+def test_ragged_rows_match_the_per_impression_numpy_metrics():
+    """``valid`` mask: impressions with different candidate counts padded to one width give, row by row, what
+    ``compute_amn`` gives on the unpadded lists (ties and several positives included)."""
+    import numpy as np
+    import torch
+    from fedrec_b200.utils.metrics import batched_ranking_metrics, compute_amn
+    rng = np.random.default_rng(0)
+    rows = []
+    for n in (2, 3, 7, 12, 30, 5):
+        y = np.zeros(n, dtype=np.int64)
+        y[rng.choice(n, size=rng.integers(1, max(2, n // 3)), replace=False)] = 1
+        if y.all():
+            y[0] = 0
+        s = np.round(rng.random(n), 1)                     # coarse scores: plenty of ties
+        rows.append((y, s))
+    C = max(len(y) for y, _ in rows)
+    scores = torch.full((len(rows), C), 0.77)              # padding carries a real-looking score on purpose
+    labels = torch.ones(len(rows), C)                      # ... and a positive label: the mask must neutralise both
+    valid = torch.zeros(len(rows), C, dtype=torch.bool)
+    for i, (y, s) in enumerate(rows):
+        scores[i, : len(y)] = torch.from_numpy(s).float()
+        labels[i, : len(y)] = torch.from_numpy(y).float()
+        valid[i, : len(y)] = True
+    m = batched_ranking_metrics(scores, labels, valid)
+    for i, (y, s) in enumerate(rows):
+        want = compute_amn(y, s.astype(np.float32))
+        got = [float(m[k][i]) for k in ("auc", "mrr", "ndcg5", "ndcg10")]
+        assert np.allclose(got, want, atol=1e-5), (i, got, want)
+    full = batched_ranking_metrics(scores[:, :2], labels[:, :2] * torch.tensor([1.0, 0.0]))
+    same = batched_ranking_metrics(scores[:, :2], labels[:, :2] * torch.tensor([1.0, 0.0]), torch.ones(len(rows), 2, dtype=torch.bool))
+    assert all(torch.equal(full[k], same[k]) for k in full)
